@@ -1,0 +1,162 @@
+/*
+ * ngp_b200.h -- C ABI of libngp_b200.so, the B200 (sm_100a) implementation of torch-ngp's
+ * Instant-NGP hot path.  This is the drop-in boundary: one `extern "C"` entry point for each
+ * free function that the reference's three pybind11 modules export
+ *   gridencoder : /root/reference/gridencoder/src/gridencoder.h:12-15 , bindings.cpp:5-9
+ *   raymarching : /root/reference/raymarching/src/raymarching.h:7-18 , bindings.cpp:5-18
+ *   ffmlp       : /root/reference/ffmlp/src/ffmlp.h:8-14             , bindings.cpp:5-10
+ * with `at::Tensor` arguments replaced by raw DEVICE pointers (caller-allocated, caller-owned,
+ * contiguous, exactly the shapes/dtypes the reference documents) and the CUDA stream made an
+ * explicit last argument (the reference launches on the legacy default stream).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative NGP_E* code otherwise; the message for the
+ *     calling thread's last failure is ngp_last_error().
+ *   - no allocation, no host synchronisation and no hidden streams inside the library: all work
+ *     is enqueued on `stream` and is CUDA-graph capturable.
+ *   - `dtype` selects the table / activation element type where the reference dispatches with
+ *     AT_DISPATCH_FLOATING_TYPES_AND_HALF.
+ *   - `void *stream` is a cudaStream_t (0 == legacy default stream).
+ */
+#ifndef NGP_B200_H
+#define NGP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define NGP_API __attribute__((visibility("default")))
+#else
+#define NGP_API
+#endif
+
+#define NGP_OK 0
+#define NGP_EINVAL (-1)      /* bad argument (unsupported D/C/hidden_dim, null pointer, ...) */
+#define NGP_ECUDA (-2)       /* a CUDA runtime call / launch failed                           */
+#define NGP_EUNSUPPORTED (-3)
+
+#define NGP_DTYPE_F32 0
+#define NGP_DTYPE_F16 1
+#define NGP_DTYPE_F64 2
+
+/* Memory layout of the encoder's per-point feature matrix (outputs / grad):
+ *   NGP_LAYOUT_LBC : [L, B, C] level-major -- what the reference kernels use (gridencoder.cu:385)
+ *   NGP_LAYOUT_BLC : [B, L*C]  point-major -- what GridEncoder.forward returns (grid.py:69); using it
+ *                    removes the two transposing copies of grid.py:69 and grid.py:87.            */
+#define NGP_LAYOUT_LBC 0
+#define NGP_LAYOUT_BLC 1
+
+NGP_API const char *ngp_last_error(void);
+NGP_API int ngp_abi_version(void);
+/* Tuning knobs used by bench/tests (e.g. "hashgrid_fwd_variant"); unknown keys -> NGP_EINVAL. */
+NGP_API int ngp_set_option(const char *key, int value);
+NGP_API int ngp_get_option(const char *key, int *value);
+
+/* ---------------------------------------------------------------------------------------------
+ * gridencoder  (replaces gridencoder.h:12-15)
+ * ------------------------------------------------------------------------------------------- */
+/* grid_encode_forward (gridencoder.cu:445-468).  inputs [B,D] f32 in [0,1]; embeddings [T,C] dtype;
+ * offsets [L+1] i32 (device); offsets_host: the same L+1 values in HOST memory, or NULL -- lets the
+ * library plan the shared-memory-resident coarse levels and wide accesses without a device read
+ * (NULL selects the generic kernels); outputs dtype in `layout`; dy_dx [B,L,D,C] dtype or NULL.
+ * D in {2,3,4,5}, C in {1,2,4,8} ("GridEncoding: C must be 1, 2, 4, or 8." otherwise). */
+NGP_API int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const int *offsets, const int *offsets_host,
+                            void *outputs, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
+                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream);
+/* grid_encode_backward (gridencoder.cu:470-500).  grad dtype in `layout`; grad_embeddings [T,C] dtype,
+ * ACCUMULATED into (caller zero-fills, grid.py:89); dy_dx/grad_inputs ([B,D] dtype) both NULL or both set. */
+NGP_API int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int *offsets,
+                             const int *offsets_host, void *grad_embeddings, uint32_t B, uint32_t D, uint32_t C, uint32_t L,
+                             float S, uint32_t H, const void *dy_dx, void *grad_inputs, uint32_t gridtype, int align_corners,
+                             uint32_t interp, int dtype, int layout, void *stream);
+/* grad_total_variation (gridencoder.cu:636-642).  inputs [B,D] in the TABLE dtype (sic, :505). */
+NGP_API int ngp_grad_total_variation(const void *inputs, const void *embeddings, void *grad, const int *offsets,
+                             float weight, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
+                             uint32_t gridtype, int align_corners, int dtype, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * raymarching  (replaces raymarching.h:7-18).  All floating tensors are f32 (the Python layer
+ * forces it: raymarching.py:21,54,131,163,240,300,354).
+ * ------------------------------------------------------------------------------------------- */
+NGP_API int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, uint32_t N, float min_near,
+                           float *nears, float *fars, void *stream);
+NGP_API int ngp_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uint32_t N, float *coords, void *stream);
+NGP_API int ngp_morton3D(const int *coords, uint32_t N, int *indices, void *stream);
+NGP_API int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *stream);
+/* N = number of output BYTES = C*H^3/8 (raymarching.cu:292) */
+NGP_API int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream);
+
+/* march_rays_train (raymarching.cu:482-490).  Differences from the reference, by design:
+ *   - sample placement is canonical instead of atomicAdd-ordered (:405-406): rays[n] = (n, offset_n, count_n)
+ *     with offset_n = counter[0] + exclusive prefix sum of the counts in ray order (per-ray content is
+ *     bit-identical; counter[0] += total, counter[1] += N exactly as the reference leaves them);
+ *   - needs `workspace` of ngp_march_rays_train_workspace_bytes(N) bytes (chained-scan state). */
+NGP_API size_t ngp_march_rays_train_workspace_bytes(uint32_t N);
+NGP_API int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                         uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
+                         const float *fars, float *xyzs, float *dirs, float *deltas, int *rays, int *counter,
+                         const float *noises, void *workspace, size_t workspace_bytes, void *stream);
+NGP_API int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int *rays,
+                                     uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth,
+                                     float *image, void *stream);
+NGP_API int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float *grad_depth, const float *grad_image,
+                                      const float *sigmas, const float *rgbs, const float *deltas, const int *rays,
+                                      const float *weights_sum, const float *depth, const float *image, uint32_t M,
+                                      uint32_t N, float T_thresh, float *grad_sigmas, float *grad_rgbs, void *stream);
+/* march_rays / composite_rays (raymarching.cu:817-824, :917-923).  n_alive_dev (nullable): device int that
+ * further clamps n_alive inside the kernel, so a render loop can run without reading the alive count back. */
+NGP_API int ngp_march_rays(uint32_t n_alive, const int *n_alive_dev, uint32_t n_step, const int *rays_alive, const float *rays_t,
+                   const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                   uint32_t H, const uint8_t *grid, const float *nears, const float *fars, float *xyzs, float *dirs,
+                   float *deltas, const float *noises, void *stream);
+NGP_API int ngp_composite_rays(uint32_t n_alive, const int *n_alive_dev, uint32_t n_step, float T_thresh, int *rays_alive,
+                       float *rays_t, const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum,
+                       float *depth, float *image, void *stream);
+/* Device-side replacement of `rays_alive = rays_alive[rays_alive >= 0]` (nerf/renderer.py:416): stable
+ * compaction of the non-negative ids of in[0..min(n,*n_dev)) into `out` (!= in); count -> *n_out (device
+ * int, may alias n_dev). */
+NGP_API size_t ngp_compact_alive_workspace_bytes(uint32_t n);
+NGP_API int ngp_compact_alive(const int *in, uint32_t n, const int *n_dev, int *out, int *n_out, void *workspace,
+                      size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * ffmlp  (replaces ffmlp.h:8-14).  fp16 storage, fp32 accumulation on tcgen05 tensor cores.
+ * Row-major [B, dim] activations (== the reference's "col-major [dim, B]"), weights flat, each
+ * layer row-major [out, in] (ffmlp.cu:631-634).  B % 128 == 0 (FFMLP.forward pads, ffmlp.py:157-159).
+ * ------------------------------------------------------------------------------------------- */
+NGP_API int ngp_ffmlp_forward(const void *inputs, const void *weights, uint32_t B, uint32_t input_dim, uint32_t output_dim,
+                      uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
+                      void *forward_buffer, void *outputs, void *stream);
+NGP_API int ngp_ffmlp_inference(const void *inputs, const void *weights, uint32_t B, uint32_t input_dim, uint32_t output_dim,
+                        uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
+                        void *inference_buffer, void *outputs, void *stream);
+/* grad_weights is fp16 like the reference when grad_weights_dtype == NGP_DTYPE_F16, or an fp32 buffer
+ * (NGP_DTYPE_F32, no K=2^20 reduction in half precision).  Both are OVERWRITTEN, not accumulated. */
+NGP_API int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, const void *forward_buffer,
+                       uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers,
+                       uint32_t activation, uint32_t output_activation, int calc_grad_inputs, void *backward_buffer,
+                       void *grad_inputs, void *grad_weights, int grad_weights_dtype, void *workspace,
+                       size_t workspace_bytes, void *stream);
+NGP_API size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
+                                          uint32_t num_layers);
+/* The reference's process-global split-k stream pool (ffmlp.cu:711-740) has no equivalent: no-ops. */
+NGP_API int ngp_allocate_splitk(size_t size);
+NGP_API int ngp_free_splitk(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * "next" rows of the scope table (callers either side of the path)
+ * ------------------------------------------------------------------------------------------- */
+/* SH direction encoding, /root/reference/shencoder/src/shencoder.cu:27-383 (degree 1..4 here).
+ * inputs [B,3] f32; outputs [B, out_stride] dtype (first degree^2 columns written; out_stride >= degree^2
+ * lets the caller encode straight into a wider, padded MLP input). */
+NGP_API int ngp_sh_encode_forward(const float *inputs, void *outputs, uint32_t B, uint32_t degree, uint32_t out_stride,
+                          int dtype, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGP_B200_H */

@@ -1,0 +1,291 @@
+"""CPU tests of the oracle (oracle/ngp_oracle.c + oracle/cpu_ref.py).
+
+These re-run the reference's own self-checks against the restatement:
+  * fp64 finite-difference gradcheck of the grid encoder w.r.t. the table, with the exact
+    configuration of /root/reference/testing/test_hashgrid_grad.py:24-61;
+  * the vertex-lookup index identity of /root/reference/test_torch_ngp.py:159-184;
+plus structural properties (Morton round trip, packbits == numpy little-endian packbits, the
+inference march/composite loop reproducing the training marcher/compositor).
+"""
+import numpy as np
+import pytest
+
+import scenes
+
+
+# ---------------------------------------------------------------------------- hash grid
+def _hashgrid_grad_cfg():
+    # test_hashgrid_grad.py:24-34 -- un-rounded offsets, D=3 L=4 C=2 pls=2 H=4 log2T=8
+    D, L, C, H, pls, log2T = 3, 4, 2, 4, 2.0, 8
+    offsets, off = [], 0
+    for i in range(L):
+        res = int(np.ceil(H * pls ** i))
+        n = min(2 ** log2T, (res + 1) ** D)
+        offsets.append(off)
+        off += n
+    offsets.append(off)
+    return D, L, C, H, pls, np.array(offsets, np.int32)
+
+
+@pytest.mark.parametrize("interp", [0, 1])
+@pytest.mark.parametrize("gridtype", [0, 1])
+def test_hashgrid_gradcheck_fp64(oracle, gridtype, interp):
+    D, L, C, H, pls, offsets = _hashgrid_grad_cfg()
+    rng = np.random.default_rng(0)
+    x = rng.random((5, D)).astype(np.float32)
+    emb = (rng.random((offsets[-1], C)) * 0.1).astype(np.float64)
+    gout = rng.standard_normal((L, 5, C))
+    out, _ = oracle.grid_encode_forward(x, emb, offsets, pls, H, False, gridtype, False, interp)
+    g_emb, _ = oracle.grid_encode_backward(gout, x, emb, offsets, pls, H, None, gridtype, False, interp)
+    # the encoder is linear in the table: directional finite differences are exact up to rounding
+    for _ in range(8):
+        dirn = rng.standard_normal(emb.shape)
+        out2, _ = oracle.grid_encode_forward(x, emb + 1e-2 * dirn, offsets, pls, H, False, gridtype, False, interp)
+        fd = ((out2 - out) * gout).sum() / 1e-2
+        assert np.isclose(fd, (g_emb * dirn).sum(), rtol=1e-8, atol=1e-10)
+
+
+@pytest.mark.parametrize("interp", [0, 1])
+def test_hashgrid_input_grad_fp64(oracle, interp):
+    D, L, C, H, pls, offsets = _hashgrid_grad_cfg()
+    rng = np.random.default_rng(1)
+    x = (rng.random((6, D)) * 0.9 + 0.05).astype(np.float32)
+    emb = rng.standard_normal((offsets[-1], C))
+    gout = rng.standard_normal((L, 6, C))
+    out, dy_dx = oracle.grid_encode_forward(x, emb, offsets, pls, H, True, 0, False, interp)
+    _, g_in = oracle.grid_encode_backward(gout, x, emb, offsets, pls, H, dy_dx, 0, False, interp)
+    eps = 2.0 ** -12  # exactly representable step; stays inside one cell for almost every point
+    for d in range(D):
+        xp, xm = x.copy(), x.copy()
+        xp[:, d] += eps
+        xm[:, d] -= eps
+        op, _ = oracle.grid_encode_forward(xp, emb, offsets, pls, H)
+        om, _ = oracle.grid_encode_forward(xm, emb, offsets, pls, H) if interp == 0 else (None, None)
+        if interp == 1:
+            op, _ = oracle.grid_encode_forward(xp, emb, offsets, pls, H, False, 0, False, 1)
+            om, _ = oracle.grid_encode_forward(xm, emb, offsets, pls, H, False, 0, False, 1)
+        fd = ((op - om) * gout).sum(axis=(0, 2)) / (2 * eps)
+        # piecewise (tri)linear / cubic: compare where no cell boundary was crossed
+        ok = np.isclose(fd, g_in[:, d], rtol=2e-3, atol=2e-3)
+        assert ok.mean() >= 0.8, (fd, g_in[:, d])
+
+
+def test_hashgrid_vertex_index_identity(oracle):
+    # test_torch_ngp.py:159-184: one level, C=1, pls=1, align_corners, embeddings[i] = i, queried at
+    # grid vertices -> returns the dense index x + y*R + z*R^2 exactly.
+    R = 8
+    offsets = np.array([0, R ** 3], np.int32)
+    emb = np.arange(R ** 3, dtype=np.float32)[:, None]
+    idx = np.arange(R)
+    X, Y, Z = np.meshgrid(idx, idx, idx, indexing="ij")
+    pts = np.stack([X.ravel(), Y.ravel(), Z.ravel()], -1).astype(np.float32) / (R - 1)
+    out, _ = oracle.grid_encode_forward(pts, emb, offsets, 1.0, R, False, 0, True, 0)
+    expect = (X.ravel() + Y.ravel() * R + Z.ravel() * R * R).astype(np.float32)
+    assert np.array_equal(np.round(out[0, :, 0]), expect)
+    assert np.abs(out[0, :, 0] - expect).max() < 1e-3
+
+
+def test_hashgrid_oob_and_empty(oracle):
+    offsets, pls = oracle.make_offsets(num_levels=4, log2_hashmap_size=10, desired_resolution=64)
+    emb = np.random.default_rng(0).standard_normal((offsets[-1], 2)).astype(np.float32)
+    x = np.array([[0.5, 0.5, 0.5], [-0.1, 0.5, 0.5], [0.5, 1.5, 0.5], [1.0, 1.0, 1.0], [0.0, 0.0, 0.0]], np.float32)
+    out, dy = oracle.grid_encode_forward(x, emb, offsets, pls, 16, True)
+    assert np.all(out[:, 1] == 0) and np.all(out[:, 2] == 0) and np.all(dy[1:3] == 0)
+    assert np.any(out[:, 0] != 0) and np.any(out[:, 3] != 0) and np.any(out[:, 4] != 0)
+    out0, _ = oracle.grid_encode_forward(np.zeros((0, 3), np.float32), emb, offsets, pls, 16)
+    assert out0.shape == (4, 0, 2)
+
+
+def test_make_offsets_matches_survey(oracle):
+    offsets, pls = oracle.make_offsets(desired_resolution=2048)
+    sizes = np.diff(offsets)
+    assert list(sizes[:5]) == [4920, 13824, 32768, 85184, 216000]
+    assert all(s == 524288 for s in sizes[5:]) and offsets[-1] == 6119864
+    assert abs(pls - 1.381913) < 1e-6
+
+
+# ---------------------------------------------------------------------------- raymarching utils
+def test_morton_roundtrip_and_known_values(oracle):
+    rng = np.random.default_rng(0)
+    c = rng.integers(0, 1024, size=(4096, 3)).astype(np.int32)
+    m = oracle.morton3D(c)
+    assert np.array_equal(oracle.morton3D_invert(m), c)
+    assert np.array_equal(m.astype(np.uint32), scenes.morton3d(c[:, 0], c[:, 1], c[:, 2]))
+    assert list(oracle.morton3D(np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [3, 3, 3], [127, 127, 127]], np.int32))) == [1, 2, 4, 63, 2 ** 21 - 1]
+
+
+def test_packbits_matches_numpy(oracle):
+    rng = np.random.default_rng(0)
+    g = rng.standard_normal(8 * 1000).astype(np.float32)
+    g[:16] = 0.25  # strict '>' at the threshold
+    bits = oracle.packbits(g, 0.25)
+    assert np.array_equal(bits, np.packbits(g > 0.25, bitorder="little"))
+    assert bits[0] == 0 and bits[1] == 0
+
+
+def test_near_far(oracle):
+    aabb = np.array([-1, -1, -1, 1, 1, 1], np.float32)
+    o = np.array([[0, 0, -3], [0, 0, -3], [0, 0, 0], [5, 5, -3]], np.float32)
+    d = np.array([[0, 0, 1], [0, 1, 0], [0, 0, 1], [0, 0, 1]], np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        n, f = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    assert n[0] == 2 and f[0] == 4
+    assert n[1] == np.finfo(np.float32).max and f[1] == np.finfo(np.float32).max  # miss
+    assert n[2] == np.float32(0.2) and f[2] == 1  # origin inside: near clamped to min_near
+    assert n[3] == np.finfo(np.float32).max
+
+
+# ---------------------------------------------------------------------------- marching / compositing
+@pytest.fixture(scope="module")
+def scene(oracle):
+    grid = scenes.density_grid(H=64, cascade=1)
+    bits = oracle.packbits(grid, 0.01)
+    o, d = scenes.camera_rays(512, seed=3)
+    aabb = np.array([-1, -1, -1, 1, 1, 1], np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    return dict(bits=bits, o=o, d=d, nears=nears, fars=fars, H=64, C=1, bound=1.0)
+
+
+def test_march_train_structure(oracle, scene):
+    s = scene
+    N = s["o"].shape[0]
+    M = N * 1024
+    xyzs, dirs, deltas, rays, counter = oracle.march_rays_train(s["o"], s["d"], s["bound"], s["bits"], s["C"], s["H"], s["nears"],
+                                                                s["fars"], M, None, 0.0, 1024)
+    assert counter[1] == N and counter[0] == rays[:, 2].sum() and counter[0] > N  # a non-trivial scene
+    assert np.array_equal(rays[:, 0], np.arange(N))
+    assert np.array_equal(rays[:, 1], np.concatenate([[0], np.cumsum(rays[:, 2])[:-1]]))
+    m = counter[0]
+    # every emitted sample sits in an occupied cell and inside the box; deltas are positive; dirs copy the ray
+    pts = xyzs[:m]
+    assert np.all(np.abs(pts) <= 1.0)
+    cell = np.clip((0.5 * (pts + 1) * s["H"]).astype(np.int64), 0, s["H"] - 1)
+    idx = scenes.morton3d(cell[:, 0], cell[:, 1], cell[:, 2]).astype(np.int64)
+    assert np.all((s["bits"][idx // 8] >> (idx % 8)) & 1)
+    assert np.all(deltas[:m] > 0) and np.all(xyzs[m:] == 0)
+    ray_of = np.repeat(np.arange(N), rays[:, 2])
+    assert np.array_equal(dirs[:m], s["d"][ray_of])
+    # dt_gamma = 0: every step is dt_min = 2*sqrt(3)/max_steps
+    assert np.all(deltas[:m, 0] == np.float32(np.float32(2 * 1.7320508075688772) / np.float32(1024)))
+
+
+def test_march_train_overflow_drops_rays(oracle, scene):
+    s = scene
+    N = s["o"].shape[0]
+    full = oracle.march_rays_train(s["o"], s["d"], s["bound"], s["bits"], s["C"], s["H"], s["nears"], s["fars"], N * 1024)
+    M = int(full[4][0] // 2)
+    xyzs, dirs, deltas, rays, counter = oracle.march_rays_train(s["o"], s["d"], s["bound"], s["bits"], s["C"], s["H"], s["nears"],
+                                                                s["fars"], M)
+    assert np.array_equal(rays, full[3]) and counter[0] == full[4][0]  # counts are unaffected by the budget
+    kept = (rays[:, 2] > 0) & (rays[:, 1] + rays[:, 2] <= M)
+    for n in np.nonzero(kept)[0][:50]:
+        a, c = rays[n, 1], rays[n, 2]
+        assert np.array_equal(xyzs[a:a + c], full[0][a:a + c])
+    first_dropped = np.nonzero(~kept & (rays[:, 2] > 0))[0][0]
+    a = rays[first_dropped, 1]
+    assert np.all(xyzs[a:M] == 0)
+
+
+def test_inference_loop_reproduces_training_march(oracle, scene):
+    """march_rays in n_step chunks + composite_rays == march_rays_train + composite_rays_train (same samples)."""
+    s = scene
+    N = s["o"].shape[0]
+    xyzs, dirs, deltas, rays, counter = oracle.march_rays_train(s["o"], s["d"], s["bound"], s["bits"], s["C"], s["H"], s["nears"],
+                                                                s["fars"], N * 1024)
+    sig = scenes.density(xyzs)
+    rgb = scenes.colour(xyzs)
+    ws_t, dep_t, img_t = oracle.composite_rays_train_forward(sig, rgb, deltas, rays, 1e-4)
+
+    ws, dep, img = np.zeros(N, np.float32), np.zeros(N, np.float32), np.zeros((N, 3), np.float32)
+    alive = np.arange(N, dtype=np.int32)
+    rays_t = s["nears"].copy()
+    collected = [[] for _ in range(N)]
+    step = 0
+    while step < 1024 and alive.size:
+        n_alive = alive.size
+        n_step = max(min(N // n_alive, 8), 1)
+        x, dd, dl = oracle.march_rays(n_alive, n_step, alive, rays_t, s["o"], s["d"], s["bound"], s["bits"], s["C"], s["H"],
+                                      s["nears"], s["fars"])
+        for k, rid in enumerate(alive):
+            blk = slice(k * n_step, (k + 1) * n_step)
+            valid = dl[blk, 0] != 0
+            collected[rid].append((x[blk][valid], dl[blk][valid]))
+        oracle.composite_rays(n_alive, n_step, alive, rays_t, scenes.density(x), scenes.colour(x), dl, ws, dep, img, 1e-4)
+        alive = np.ascontiguousarray(alive[alive >= 0])
+        step += n_step
+    # The first chunk starts from `nears` exactly like the training marcher: bit-identical samples.  Later
+    # chunks resume from rays_t accumulated by the compositor (t += delta, :881), which drifts by ulps.
+    first_exact, close, total = 0, 0, 0
+    for n in range(N):
+        a, c = rays[n, 1], rays[n, 2]
+        if c == 0 or not collected[n]:
+            continue
+        p0 = collected[n][0][0]
+        k0 = min(len(p0), c)
+        assert np.array_equal(p0[:k0], xyzs[a:a + k0])
+        first_exact += k0
+        got = np.concatenate([p for p, _ in collected[n]])
+        k = min(len(got), c)
+        total += 1
+        close += bool(np.allclose(got[:k], xyzs[a:a + k], atol=1e-4))
+    assert first_exact > N // 2 and close >= 0.95 * total
+    # composited colour agrees up to the (1 - sum w) vs prod(1 - alpha) formulation difference
+    assert np.allclose(img, img_t, atol=2e-3) and np.allclose(ws, ws_t, atol=2e-3)
+
+
+def test_composite_backward_matches_finite_differences(oracle, scene):
+    s = scene
+    N = 64
+    xyzs, dirs, deltas, rays, counter = oracle.march_rays_train(s["o"][:N], s["d"][:N], s["bound"], s["bits"], s["C"], s["H"],
+                                                                s["nears"][:N], s["fars"][:N], N * 1024)
+    m = int(counter[0])
+    rng = np.random.default_rng(0)
+    sig = (rng.random(m) * 3).astype(np.float32)          # low density: no early termination inside the segment
+    rgb = rng.random((m, 3)).astype(np.float32)
+    deltas = deltas[:m]
+    ws, dep, img = oracle.composite_rays_train_forward(sig, rgb, deltas, rays, 0.0)
+    g_ws, g_dep, g_img = rng.standard_normal(N).astype(np.float32), np.zeros(N, np.float32), rng.standard_normal((N, 3)).astype(np.float32)
+    g_sig, g_rgb = oracle.composite_rays_train_backward(g_ws, g_dep, g_img, sig, rgb, deltas, rays, ws, dep, img, 0.0)
+
+    def loss(sg, cl):
+        a, b, c = oracle.composite_rays_train_forward(sg, cl, deltas, rays, 0.0)
+        return (a.astype(np.float64) * g_ws).sum() + (c.astype(np.float64) * g_img).sum()
+
+    picks = rng.choice(m, 40, replace=False)
+    for i in picks:
+        e = np.zeros(m, np.float32)
+        e[i] = 1e-2
+        fd = (loss(sig + e, rgb) - loss(sig - e, rgb)) / 2e-2
+        assert np.isclose(fd, g_sig[i], rtol=5e-2, atol=2e-3), (i, fd, g_sig[i])
+        e3 = np.zeros((m, 3), np.float32)
+        e3[i, 1] = 1e-2
+        fd = (loss(sig, rgb + e3) - loss(sig, rgb - e3)) / 2e-2
+        assert np.isclose(fd, g_rgb[i, 1], rtol=5e-2, atol=2e-3)
+
+
+# ---------------------------------------------------------------------------- MLP / SH
+def test_ffmlp_numpy_backward_matches_finite_differences(oracle):
+    rng = np.random.default_rng(0)
+    B, din, dout, hid, nl = 16, 32, 16, 64, 2
+    nw = hid * (din + hid * (nl - 1) + dout)
+    w = rng.uniform(-1, 1, nw) * np.sqrt(3 / hid)
+    x = rng.standard_normal((B, din))
+    g = rng.standard_normal((B, dout))
+    y, _ = oracle.ffmlp_forward(x, w, din, dout, hid, nl)
+    gx, gw = oracle.ffmlp_backward(g, x, w, din, dout, hid, nl)
+    for _ in range(5):
+        dw = rng.standard_normal(nw)
+        y2, _ = oracle.ffmlp_forward(x, w + 1e-6 * dw, din, dout, hid, nl)
+        assert np.isclose(((y2 - y) * g).sum() / 1e-6, (gw * dw).sum(), rtol=1e-3, atol=1e-6)
+        dx = rng.standard_normal(x.shape)
+        y2, _ = oracle.ffmlp_forward(x + 1e-6 * dx, w, din, dout, hid, nl)
+        assert np.isclose(((y2 - y) * g).sum() / 1e-6, (gx * dx).sum(), rtol=1e-3, atol=1e-6)
+
+
+def test_sh_encode_orthonormal(oracle):
+    rng = np.random.default_rng(0)
+    d = rng.standard_normal((200000, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    y = oracle.sh_encode(d, 4)
+    gram = 4 * np.pi * (y.T @ y) / d.shape[0]  # Monte-Carlo <Y_i, Y_j> over the sphere
+    assert np.allclose(gram, np.eye(16), atol=0.03)

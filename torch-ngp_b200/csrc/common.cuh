@@ -1,0 +1,46 @@
+// common.cuh -- shared host/device helpers of libngp_b200.so (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ngp_b200.h"
+
+namespace ngp {
+
+void set_error(const char *fmt, ...);
+int get_option(const char *key, int dflt);
+int sm_count();  // SMs of the current device (148 on B200), cached
+
+template <typename T>
+__host__ __device__ inline T div_round_up(T a, T b) { return (a + b - 1) / b; }
+
+#define NGP_CHECK_ARG(cond, ...)                 \
+    do {                                         \
+        if (!(cond)) {                           \
+            ngp::set_error(__VA_ARGS__);         \
+            return NGP_EINVAL;                   \
+        }                                        \
+    } while (0)
+
+#define NGP_CHECK_CUDA(expr)                                                                  \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            ngp::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return NGP_ECUDA;                                                                 \
+        }                                                                                     \
+    } while (0)
+
+// Launch-error check: cudaPeekAtLastError is capture-safe and does not synchronise.
+#define NGP_CHECK_LAUNCH()                                                                    \
+    do {                                                                                      \
+        cudaError_t _e = cudaPeekAtLastError();                                               \
+        if (_e != cudaSuccess) {                                                              \
+            ngp::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return NGP_ECUDA;                                                                 \
+        }                                                                                     \
+    } while (0)
+
+}  // namespace ngp

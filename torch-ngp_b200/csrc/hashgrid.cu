@@ -1,0 +1,344 @@
+// hashgrid.cu -- multi-resolution hash / tiled grid encoding for sm_100a.
+//
+// Implements the contract of /root/reference/gridencoder/src/gridencoder.cu (kernel_grid :87-242,
+// kernel_grid_backward :245-337, kernel_input_backward :340-366, kernel_grad_tv :503-607) behind
+// the C ABI of include/ngp_b200.h.  Two tiers:
+//
+//   generic  : every (dtype in {f32,f16,f64}) x (D in 2..5) x (C in {1,2,4,8}) the reference
+//              dispatches, any gridtype / align_corners / interpolation, optional dy_dx.  Same
+//              operation order as the reference so fp32/fp64 outputs are bit-identical.
+//   d3c2 fast: D=3, C=2, f32/f16 -- the Instant-NGP configuration (L=16, F=2).  x-adjacent
+//              corner pairs are fetched / reduced as one 16 B (f32) or 8 B (f16) transaction
+//              when they share an aligned pair slot (always for even x on hashed levels because
+//              prime[0]==1, and for even base index on dense levels), coarse levels whose slice
+//              fits shared memory are gathered from / accumulated in shared memory, and the
+//              backward collapses warp-uniform cells with a shuffle reduction before touching L2.
+//
+// fp16 tables accumulate in fp32 registers (the reference accumulates in half, :161).
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace ngp {
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// element helpers
+// ------------------------------------------------------------------------------------------
+template <typename T> struct acc_of { using type = float; };
+template <> struct acc_of<double> { using type = double; };
+
+template <typename T> __device__ __forceinline__ typename acc_of<T>::type to_acc(T v) { return (typename acc_of<T>::type)v; }
+template <> __device__ __forceinline__ float to_acc<__half>(__half v) { return __half2float(v); }
+template <typename T, typename A> __device__ __forceinline__ T from_acc(A v) { return (T)v; }
+template <> __device__ __forceinline__ __half from_acc<__half, float>(float v) { return __float2half_rn(v); }
+
+template <typename T, uint32_t C> struct alignas(sizeof(T) * C <= 16 ? sizeof(T) * C : 16) vec_t { T v[C]; };
+
+template <typename T, uint32_t C>
+__device__ __forceinline__ vec_t<T, C> load_vec(const T *p) { return *reinterpret_cast<const vec_t<T, C> *>(p); }
+template <typename T, uint32_t C>
+__device__ __forceinline__ void store_vec(T *p, const vec_t<T, C> &v) { *reinterpret_cast<vec_t<T, C> *>(p) = v; }
+
+__device__ __forceinline__ float smoothstep_f(float v) { return v * v * (3.0f - 2.0f * v); }
+__device__ __forceinline__ float smoothstep_df(float v) { return 6 * v * (1.0f - v); }
+
+// per-level constants: reference gridencoder.cu:137-139 (device exp2f, fused *H-1)
+struct level_t {
+    uint32_t offset, size, resolution;
+    float scale;
+};
+__device__ __forceinline__ level_t level_consts(const int *__restrict__ offsets, uint32_t level, float S, uint32_t H) {
+    level_t lv;
+    lv.offset = (uint32_t)offsets[level];
+    lv.size = (uint32_t)offsets[level + 1] - lv.offset;
+    lv.scale = exp2f(level * S) * H - 1.0f;
+    lv.resolution = (uint32_t)ceilf(lv.scale) + 1;
+    return lv;
+}
+
+template <uint32_t D>
+__device__ __forceinline__ uint32_t hash_coords(const uint32_t p[D]) {
+    constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+    uint32_t r = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < D; ++i) r ^= p[i] * primes[i];
+    return r;
+}
+
+// entry index inside the level (reference get_grid_index :66-84, without the *C + ch)
+template <uint32_t D>
+__device__ __forceinline__ uint32_t grid_index(uint32_t gridtype, bool align_corners, uint32_t size, uint32_t resolution,
+                                               const uint32_t p[D]) {
+    uint32_t stride = 1, index = 0;
+#pragma unroll
+    for (uint32_t d = 0; d < D && stride <= size; ++d) {
+        index += p[d] * stride;
+        stride *= align_corners ? resolution : (resolution + 1);
+    }
+    if (gridtype == 0 && stride > size) index = hash_coords<D>(p);
+    return index % size;
+}
+
+template <uint32_t D>
+__device__ __forceinline__ bool out_of_bounds(const float *x) {
+    bool oob = false;
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) oob |= (x[d] < 0 || x[d] > 1);
+    return oob;
+}
+
+// ------------------------------------------------------------------------------------------
+// generic forward: one thread = one (point, level)
+// ------------------------------------------------------------------------------------------
+template <typename T, uint32_t D, uint32_t C>
+__global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restrict__ inputs, const T *__restrict__ grid,
+                                                          const int *__restrict__ offsets, T *__restrict__ outputs,
+                                                          uint32_t B, uint32_t L, float S, uint32_t H,
+                                                          T *__restrict__ dy_dx, uint32_t gridtype, bool align_corners,
+                                                          uint32_t interp, int layout) {
+    using A = typename acc_of<T>::type;
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint32_t level = blockIdx.y;
+    const level_t lv = level_consts(offsets, level, S, H);
+    grid += (size_t)lv.offset * C;
+    T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * C : ((size_t)b * L + level) * C);
+    if (dy_dx) dy_dx += ((size_t)b * L + level) * D * C;
+
+    float x[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) x[d] = inputs[(size_t)b * D + d];
+
+    if (out_of_bounds<D>(x)) {
+        vec_t<T, C> z;
+#pragma unroll
+        for (uint32_t c = 0; c < C; ++c) z.v[c] = from_acc<T, A>((A)0);
+        store_vec<T, C>(out, z);
+        if (dy_dx) {
+#pragma unroll
+            for (uint32_t d = 0; d < D; ++d) store_vec<T, C>(dy_dx + d * C, z);
+        }
+        return;
+    }
+
+    float pos[D], pos_deriv[D];
+    uint32_t pg[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) {
+        pos[d] = x[d] * lv.scale + (align_corners ? 0.0f : 0.5f);
+        pg[d] = (uint32_t)floorf(pos[d]);
+        pos[d] -= (float)pg[d];
+        pos_deriv[d] = 1.0f;
+        if (interp == 1) {
+            pos_deriv[d] = smoothstep_df(pos[d]);
+            pos[d] = smoothstep_f(pos[d]);
+        }
+    }
+
+    A res[C];
+#pragma unroll
+    for (uint32_t c = 0; c < C; ++c) res[c] = 0;
+#pragma unroll
+    for (uint32_t idx = 0; idx < (1u << D); ++idx) {
+        float w = 1;
+        uint32_t pl[D];
+#pragma unroll
+        for (uint32_t d = 0; d < D; ++d) {
+            if ((idx & (1u << d)) == 0) { w *= 1 - pos[d]; pl[d] = pg[d]; }
+            else { w *= pos[d]; pl[d] = pg[d] + 1; }
+        }
+        const uint32_t e = grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pl);
+        const vec_t<T, C> g = load_vec<T, C>(grid + (size_t)e * C);
+#pragma unroll
+        for (uint32_t c = 0; c < C; ++c) res[c] += (A)w * to_acc<T>(g.v[c]);
+    }
+    vec_t<T, C> o;
+#pragma unroll
+    for (uint32_t c = 0; c < C; ++c) o.v[c] = from_acc<T, A>(res[c]);
+    store_vec<T, C>(out, o);
+
+    if (!dy_dx) return;
+    // analytic d(out)/d(x) (reference :198-241)
+#pragma unroll
+    for (uint32_t gd = 0; gd < D; ++gd) {
+        A rg[C];
+#pragma unroll
+        for (uint32_t c = 0; c < C; ++c) rg[c] = 0;
+#pragma unroll
+        for (uint32_t idx = 0; idx < (1u << (D - 1)); ++idx) {
+            float w = lv.scale;
+            uint32_t pl[D];
+#pragma unroll
+            for (uint32_t nd = 0; nd < D - 1; ++nd) {
+                const uint32_t d = (nd >= gd) ? (nd + 1) : nd;
+                if ((idx & (1u << nd)) == 0) { w *= 1 - pos[d]; pl[d] = pg[d]; }
+                else { w *= pos[d]; pl[d] = pg[d] + 1; }
+            }
+            pl[gd] = pg[gd];
+            const uint32_t el = grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pl);
+            pl[gd] = pg[gd] + 1;
+            const uint32_t er = grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pl);
+            const vec_t<T, C> gl = load_vec<T, C>(grid + (size_t)el * C), gr = load_vec<T, C>(grid + (size_t)er * C);
+#pragma unroll
+            for (uint32_t c = 0; c < C; ++c) rg[c] += (A)w * (to_acc<T>(gr.v[c]) - to_acc<T>(gl.v[c])) * (A)pos_deriv[gd];
+        }
+        vec_t<T, C> o2;
+#pragma unroll
+        for (uint32_t c = 0; c < C; ++c) o2.v[c] = from_acc<T, A>(rg[c]);
+        store_vec<T, C>(dy_dx + gd * C, o2);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// atomics
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add(float *p, float v) { atomicAdd(p, v); }
+__device__ __forceinline__ void red_add(double *p, double v) { atomicAdd(p, v); }
+__device__ __forceinline__ void red_add(__half *p, __half v) { atomicAdd(p, v); }
+__device__ __forceinline__ void red_add_v2(float *p, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float *p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+__device__ __forceinline__ void red_add_h2(__half *p, float a, float b) {
+    asm volatile("red.global.add.noftz.f16x2 [%0], %1;" ::"l"(p), "r"(pack_h2(a, b)) : "memory");
+}
+__device__ __forceinline__ void red_add_h2x2(__half *p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(p), "r"(pack_h2(a, b)), "r"(pack_h2(c, d)) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------
+// generic backward: one thread = (point, level, channel pair) like the reference (:245-337)
+// ------------------------------------------------------------------------------------------
+template <typename T, uint32_t D, uint32_t C>
+__global__ void __launch_bounds__(256) k_grid_bwd_generic(const T *__restrict__ grad, const float *__restrict__ inputs,
+                                                          const int *__restrict__ offsets, T *__restrict__ grad_grid,
+                                                          uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
+                                                          bool align_corners, uint32_t interp, int layout) {
+    using A = typename acc_of<T>::type;
+    constexpr uint32_t N_C = C < 2 ? C : 2;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t b = t * N_C / C;
+    if (b >= B) return;
+    const uint32_t level = blockIdx.y;
+    const uint32_t ch = t * N_C - b * C;
+    const level_t lv = level_consts(offsets, level, S, H);
+    grad_grid += (size_t)lv.offset * C;
+
+    float x[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) x[d] = inputs[(size_t)b * D + d];
+    if (out_of_bounds<D>(x)) return;
+
+    float pos[D];
+    uint32_t pg[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) {
+        pos[d] = x[d] * lv.scale + (align_corners ? 0.0f : 0.5f);
+        pg[d] = (uint32_t)floorf(pos[d]);
+        pos[d] -= (float)pg[d];
+        if (interp == 1) pos[d] = smoothstep_f(pos[d]);
+    }
+    const T *g = grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * C : ((size_t)b * L + level) * C) + ch;
+    A gc[N_C];
+#pragma unroll
+    for (uint32_t c = 0; c < N_C; ++c) gc[c] = to_acc<T>(g[c]);
+
+#pragma unroll
+    for (uint32_t idx = 0; idx < (1u << D); ++idx) {
+        float w = 1;
+        uint32_t pl[D];
+#pragma unroll
+        for (uint32_t d = 0; d < D; ++d) {
+            if ((idx & (1u << d)) == 0) { w *= 1 - pos[d]; pl[d] = pg[d]; }
+            else { w *= pos[d]; pl[d] = pg[d] + 1; }
+        }
+        const uint32_t e = grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pl);
+        T *dst = grad_grid + (size_t)e * C + ch;
+        if constexpr (std::is_same<T, __half>::value && N_C == 2) {
+            red_add_h2(dst, w * gc[0], w * gc[1]);
+        } else if constexpr (std::is_same<T, float>::value && N_C == 2) {
+            red_add_v2(dst, w * gc[0], w * gc[1]);
+        } else {
+#pragma unroll
+            for (uint32_t c = 0; c < N_C; ++c) red_add(dst + c, from_acc<T, A>((A)w * gc[c]));
+        }
+    }
+}
+
+// grad_inputs[b,d] = sum_{l,c} grad[l,b,c] * dy_dx[b,l,d,c]   (reference :340-366)
+template <typename T, uint32_t D, uint32_t C>
+__global__ void __launch_bounds__(256) k_input_bwd(const T *__restrict__ grad, const T *__restrict__ dy_dx,
+                                                   T *__restrict__ grad_inputs, uint32_t B, uint32_t L, int layout) {
+    using A = typename acc_of<T>::type;
+    const uint32_t t = threadIdx.x + blockIdx.x * blockDim.x;
+    if (t >= B * D) return;
+    const uint32_t b = t / D, d = t - b * D;
+    dy_dx += (size_t)b * L * D * C;
+    A r = 0;
+    for (uint32_t l = 0; l < L; ++l) {
+        const T *g = grad + (layout == NGP_LAYOUT_LBC ? ((size_t)l * B + b) * C : ((size_t)b * L + l) * C);
+#pragma unroll
+        for (uint32_t c = 0; c < C; ++c) r += to_acc<T>(g[c]) * to_acc<T>(dy_dx[(size_t)l * D * C + d * C + c]);
+    }
+    grad_inputs[t] = from_acc<T, A>(r);
+}
+
+// total-variation gradient (reference :503-607)
+template <typename T, uint32_t D, uint32_t C>
+__global__ void __launch_bounds__(256) k_grad_tv(const T *__restrict__ inputs, const T *__restrict__ grid, T *__restrict__ grad,
+                                                 const int *__restrict__ offsets, float weight, uint32_t B, uint32_t L, float S,
+                                                 uint32_t H, uint32_t gridtype, bool align_corners) {
+    using A = typename acc_of<T>::type;
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint32_t level = blockIdx.y;
+    const level_t lv = level_consts(offsets, level, S, H);
+    grid += (size_t)lv.offset * C;
+    grad += (size_t)lv.offset * C;
+    float x[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) x[d] = (float)to_acc<T>(inputs[(size_t)b * D + d]);
+    if (out_of_bounds<D>(x)) return;
+    uint32_t pg[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) pg[d] = (uint32_t)floorf(x[d] * lv.scale + (align_corners ? 0.0f : 0.5f));
+
+    A res[C], idl[C];
+#pragma unroll
+    for (uint32_t c = 0; c < C; ++c) { res[c] = 0; idl[c] = 0; }
+    const uint32_t e0 = grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pg);
+    const vec_t<T, C> g0 = load_vec<T, C>(grid + (size_t)e0 * C);
+    const A w = (A)(weight / (2 * D));
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) {
+        const uint32_t cur = pg[d];
+        if (cur < lv.resolution) {
+            pg[d] = cur + 1;
+            const vec_t<T, C> g1 = load_vec<T, C>(grid + (size_t)grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pg) * C);
+#pragma unroll
+            for (uint32_t c = 0; c < C; ++c) { const A v = to_acc<T>(g0.v[c]) - to_acc<T>(g1.v[c]); res[c] += v; idl[c] += v * v; }
+        }
+        if (cur > 0) {
+            pg[d] = cur - 1;
+            const vec_t<T, C> g1 = load_vec<T, C>(grid + (size_t)grid_index<D>(gridtype, align_corners, lv.size, lv.resolution, pg) * C);
+#pragma unroll
+            for (uint32_t c = 0; c < C; ++c) { const A v = to_acc<T>(g0.v[c]) - to_acc<T>(g1.v[c]); res[c] += v; idl[c] += v * v; }
+        }
+        pg[d] = cur;
+    }
+#pragma unroll
+    for (uint32_t c = 0; c < C; ++c) red_add(grad + (size_t)e0 * C + c, from_acc<T, A>(w * res[c] * (A)rsqrtf((float)idl[c] + 1e-9f)));
+}
+
+}  // namespace
+}  // namespace ngp
+
+#include "hashgrid_fast.cuh"
+#include "hashgrid_host.cuh"

@@ -1,0 +1,217 @@
+// raymarch.cu -- occupancy-bitfield ray marcher, compositors and helpers for sm_100a.
+//
+// Contract: /root/reference/raymarching/src/raymarching.cu (utils :91-289, training :311-702,
+// inference :709-923) behind the C ABI of include/ngp_b200.h.
+//
+// Bit-exactness.  Sample positions, deltas, counts and bitfields must equal the reference's.
+// Every float operation of the stepping rule is therefore spelled with explicit rounding
+// intrinsics (__fmaf_rn / __fmul_rn / __fadd_rn / __fdiv_rn) in exactly the shape nvcc's default
+// -fmad=true contraction gives the reference source, so the result does not depend on this
+// file's compile flags.  The reference's FP64 islands (`0.5 * (x*rb + 1) * H`, `dt * H * 0.5`)
+// are exact products followed by one rounding to float; they are reproduced in fp32 as
+// RN(f * H) * 0.5f, which is identical for H < 2^24 (no DMUL / F2F on the hot loop).
+//
+// Placement.  The reference reserves output segments with atomicAdd in arrival order
+// (:405-406).  Here: pass 1 counts per ray and block-scans, the last block to finish scans the
+// block totals (threadfence pattern), pass 2 writes -- so rays[n] = (n, offset_n, count_n) with
+// offsets in ray order, deterministic, and each block's samples form one contiguous range.
+#include <float.h>
+
+#include "common.cuh"
+
+namespace ngp {
+namespace {
+
+constexpr float kSqrt3 = 1.7320508075688772f;
+constexpr float kRPi = 0.3183098861837907f;
+constexpr int kMarchBlock = 128;
+
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }
+__device__ __forceinline__ float signf(float x) { return copysignf(1.0f, x); }
+
+__host__ __device__ __forceinline__ uint32_t expand_bits(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__host__ __device__ __forceinline__ uint32_t morton3D_1(uint32_t x, uint32_t y, uint32_t z) {
+    return expand_bits(x) | (expand_bits(y) << 1) | (expand_bits(z) << 2);
+}
+__host__ __device__ __forceinline__ uint32_t compact_bits(uint32_t x) {
+    x = x & 0x49249249;
+    x = (x | (x >> 2)) & 0xc30c30c3;
+    x = (x | (x >> 4)) & 0x0f00f00f;
+    x = (x | (x >> 8)) & 0xff0000ff;
+    x = (x | (x >> 16)) & 0x0000ffff;
+    return x;
+}
+
+// exponent of frexpf clamped to [0, max_cascade-1] (reference :42-54)
+__device__ __forceinline__ int mip_of(float mx, float max_cascade) {
+    int e;
+    frexpf(mx, &e);
+    return (int)fminf(max_cascade - 1, fmaxf(0.0f, (float)e));
+}
+
+struct ray_t {
+    float ox, oy, oz, dx, dy, dz, rdx, rdy, rdz;
+};
+struct march_consts_t {
+    float bound, dt_gamma, dt_min, dt_max, rH, H3, Hf, Cf, Hm1;
+    const uint8_t *grid;
+};
+
+__device__ __forceinline__ march_consts_t make_consts(float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t H,
+                                                      const uint8_t *grid) {
+    march_consts_t c;
+    c.bound = bound;
+    c.dt_gamma = dt_gamma;
+    c.dt_min = __fdiv_rn(2 * kSqrt3, (float)max_steps);
+    c.dt_max = __fdiv_rn(__fmul_rn(2 * kSqrt3, (float)(1 << (C - 1))), (float)H);
+    c.rH = __fdiv_rn(1.0f, (float)H);
+    c.H3 = (float)(H * H * H);
+    c.Hf = (float)H;
+    c.Cf = (float)C;
+    c.Hm1 = (float)(H - 1);
+    c.grid = grid;
+    return c;
+}
+__device__ __forceinline__ ray_t load_ray(const float *__restrict__ rays_o, const float *__restrict__ rays_d, uint32_t n) {
+    ray_t r;
+    r.ox = rays_o[3 * (size_t)n]; r.oy = rays_o[3 * (size_t)n + 1]; r.oz = rays_o[3 * (size_t)n + 2];
+    r.dx = rays_d[3 * (size_t)n]; r.dy = rays_d[3 * (size_t)n + 1]; r.dz = rays_d[3 * (size_t)n + 2];
+    r.rdx = __fdiv_rn(1.0f, r.dx); r.rdy = __fdiv_rn(1.0f, r.dy); r.rdz = __fdiv_rn(1.0f, r.dz);
+    return r;
+}
+
+__device__ __forceinline__ int cell_of(float p, float mip_rbound, const march_consts_t &c) {
+    // (int)clamp(0.5 * (p*rb + 1) * H, 0, H-1) with the double island folded (see file header)
+    const float v = __fmul_rn(0.5f, __fmul_rn(__fmaf_rn(p, mip_rbound, 1.0f), c.Hf));
+    return (int)clampf(v, 0.0f, c.Hm1);
+}
+__device__ __forceinline__ float exit_t(int n, float d, float rd, float p, float mip_bound, const march_consts_t &c) {
+    // (((n + 0.5 + 0.5*sign(d)) * rH * 2 - 1) * mip_bound - p) * rd     (reference :390-392)
+    const float a = __fadd_rn(__fadd_rn((float)n, 0.5f), __fmul_rn(0.5f, signf(d)));
+    const float q = __fmaf_rn(__fmul_rn(a, c.rH), 2.0f, -1.0f);
+    return __fmul_rn(__fmaf_rn(q, mip_bound, -p), rd);
+}
+
+// One iteration of the marching loop (reference :360-399).  Returns true when the cell at t is
+// occupied (x,y,z,dt valid, t untouched); otherwise advances t beyond the empty voxel.
+__device__ __forceinline__ bool probe(const ray_t &r, const march_consts_t &c, float &t, float &x, float &y, float &z, float &dt) {
+    x = clampf(__fmaf_rn(t, r.dx, r.ox), -c.bound, c.bound);
+    y = clampf(__fmaf_rn(t, r.dy, r.oy), -c.bound, c.bound);
+    z = clampf(__fmaf_rn(t, r.dz, r.oz), -c.bound, c.bound);
+    dt = clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max);
+
+    const int level = max(mip_of(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), c.Cf),
+                          mip_of(__fmul_rn(__fmul_rn(dt, c.Hf), 0.5f), c.Cf));
+    const float mip_bound = fminf(scalbnf(1.0f, level), c.bound);
+    const float mip_rbound = __fdiv_rn(1.0f, mip_bound);
+
+    const int nx = cell_of(x, mip_rbound, c), ny = cell_of(y, mip_rbound, c), nz = cell_of(z, mip_rbound, c);
+    // the reference forms the bit index in FLOAT: level * H3 + morton (:339,378)
+    const uint32_t index = (uint32_t)__fmaf_rn((float)level, c.H3, (float)morton3D_1((uint32_t)nx, (uint32_t)ny, (uint32_t)nz));
+    const bool occ = __ldg(c.grid + (index >> 3)) & (1u << (index & 7u));
+    if (occ) return true;
+
+    const float tx = exit_t(nx, r.dx, r.rdx, x, mip_bound, c);
+    const float ty = exit_t(ny, r.dy, r.rdy, y, mip_bound, c);
+    const float tz = exit_t(nz, r.dz, r.rdz, z, mip_bound, c);
+    const float tt = __fadd_rn(t, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    do {
+        t = __fadd_rn(t, clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max));
+    } while (t < tt);
+    return false;
+}
+
+// ------------------------------------------------------------------------------------------
+// utils
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_near_far(const float *__restrict__ rays_o, const float *__restrict__ rays_d,
+                                                  const float *__restrict__ aabb, uint32_t N, float min_near,
+                                                  float *__restrict__ nears, float *__restrict__ fars) {
+    const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N) return;
+    const ray_t r = load_ray(rays_o, rays_d, n);
+    float near = __fmul_rn(__fsub_rn(aabb[0], r.ox), r.rdx), far = __fmul_rn(__fsub_rn(aabb[3], r.ox), r.rdx), tmp;
+    if (near > far) { tmp = near; near = far; far = tmp; }
+    float ny = __fmul_rn(__fsub_rn(aabb[1], r.oy), r.rdy), fy = __fmul_rn(__fsub_rn(aabb[4], r.oy), r.rdy);
+    if (ny > fy) { tmp = ny; ny = fy; fy = tmp; }
+    if (near > fy || ny > far) { nears[n] = fars[n] = FLT_MAX; return; }
+    if (ny > near) near = ny;
+    if (fy < far) far = fy;
+    float nz = __fmul_rn(__fsub_rn(aabb[2], r.oz), r.rdz), fz = __fmul_rn(__fsub_rn(aabb[5], r.oz), r.rdz);
+    if (nz > fz) { tmp = nz; nz = fz; fz = tmp; }
+    if (near > fz || nz > far) { nears[n] = fars[n] = FLT_MAX; return; }
+    if (nz > near) near = nz;
+    if (fz < far) far = fz;
+    if (near < min_near) near = min_near;
+    nears[n] = near;
+    fars[n] = far;
+}
+
+__global__ void __launch_bounds__(256) k_sph_from_ray(const float *__restrict__ rays_o, const float *__restrict__ rays_d,
+                                                      float radius, uint32_t N, float *__restrict__ coords) {
+    const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N) return;
+    const float ox = rays_o[3 * (size_t)n], oy = rays_o[3 * (size_t)n + 1], oz = rays_o[3 * (size_t)n + 2];
+    const float dx = rays_d[3 * (size_t)n], dy = rays_d[3 * (size_t)n + 1], dz = rays_d[3 * (size_t)n + 2];
+    const float A = dx * dx + dy * dy + dz * dz;
+    const float Bh = ox * dx + oy * dy + oz * dz;
+    const float Cc = ox * ox + oy * oy + oz * oz - radius * radius;
+    const float t = (-Bh + sqrtf(Bh * Bh - A * Cc)) / A;
+    const float x = ox + t * dx, y = oy + t * dy, z = oz + t * dz;
+    const float theta = atan2f(sqrtf(x * x + z * z), y);
+    const float phi = atan2f(z, x);
+    coords[2 * (size_t)n] = 2 * theta * kRPi - 1;
+    coords[2 * (size_t)n + 1] = phi * kRPi;
+}
+
+__global__ void __launch_bounds__(256) k_morton3D(const int *__restrict__ coords, uint32_t N, int *__restrict__ indices) {
+    const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N) return;
+    indices[n] = (int)morton3D_1((uint32_t)coords[3 * (size_t)n], (uint32_t)coords[3 * (size_t)n + 1], (uint32_t)coords[3 * (size_t)n + 2]);
+}
+
+__global__ void __launch_bounds__(256) k_morton3D_invert(const int *__restrict__ indices, uint32_t N, int *__restrict__ coords) {
+    const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N) return;
+    const int ind = indices[n];
+    coords[3 * (size_t)n] = (int)compact_bits((uint32_t)(ind >> 0));
+    coords[3 * (size_t)n + 1] = (int)compact_bits((uint32_t)(ind >> 1));
+    coords[3 * (size_t)n + 2] = (int)compact_bits((uint32_t)(ind >> 2));
+}
+
+// one thread packs 32 cells (128 B in, 4 B out): 8x float4 loads, one 32-bit store.
+// N4 = number of whole 4-byte groups; the (< 4) trailing bytes go through k_packbits_tail.
+__global__ void __launch_bounds__(256) k_packbits32(const float4 *__restrict__ grid4, uint32_t N4, float thresh,
+                                                    uint32_t *__restrict__ bitfield32) {
+    const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N4) return;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float4 v = __ldg(grid4 + 8 * (size_t)n + i);
+        bits |= (v.x > thresh ? 1u : 0u) << (4 * i) | (v.y > thresh ? 1u : 0u) << (4 * i + 1) |
+                (v.z > thresh ? 1u : 0u) << (4 * i + 2) | (v.w > thresh ? 1u : 0u) << (4 * i + 3);
+    }
+    bitfield32[n] = bits;  // little-endian: byte k of the word == cells 8k..8k+7, LSB first
+}
+__global__ void k_packbits_tail(const float *__restrict__ grid, uint32_t n_begin, uint32_t N, float thresh, uint8_t *__restrict__ bitfield) {
+    const uint32_t n = n_begin + threadIdx.x + blockIdx.x * blockDim.x;
+    if (n >= N) return;
+    uint8_t bits = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) bits |= (grid[8 * (size_t)n + i] > thresh) ? (uint8_t)(1u << i) : 0;
+    bitfield[n] = bits;
+}
+
+}  // namespace
+}  // namespace ngp
+
+#include "raymarch_train.cuh"
+#include "raymarch_infer.cuh"
+#include "raymarch_host.cuh"
