@@ -45,6 +45,25 @@ def lib():
     return _lib
 
 
+def set_pos_deriv_quirk(on):
+    """1: restate the reference's `pos_deriv[D] = {1.0f}` initialisation bug (see ngp_oracle.c); 0: correct."""
+    lib().orc_set_pos_deriv_quirk(_i32(int(on)))
+
+
+_exp2_keepalive = None
+
+
+def set_level_exp2(values):
+    """Per-level exp2f(level * S) as evaluated by the GPU (float32 array), or None for libm (see ngp_oracle.c)."""
+    global _exp2_keepalive
+    if values is None:
+        _exp2_keepalive = None
+        lib().orc_set_level_exp2(None, _u32(0))
+    else:
+        _exp2_keepalive = np.ascontiguousarray(values, dtype=np.float32)
+        lib().orc_set_level_exp2(_exp2_keepalive.ctypes.data_as(_p), _u32(_exp2_keepalive.size))
+
+
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(_p)
 

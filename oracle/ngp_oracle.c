@@ -59,9 +59,16 @@ static uint32_t orc_grid_index(uint32_t gridtype, int align_corners, uint32_t D,
     return index % hashmap_size;
 }
 
+/* The reference evaluates exp2f(level * S) with the DEVICE math library (<= 2 ulp, not correctly rounded), libm's
+ * exp2f can differ in the last bit, which moves fine-level positions by ~1e-4 of a cell.  Tests that compare against a
+ * GPU at 1e-5 hand the device's own exp2f values in here (computed with torch.exp2 on the GPU); NULL -> libm. */
+static const float *orc_exp2_override = NULL;
+static uint32_t orc_exp2_override_n = 0;
+void orc_set_level_exp2(const float *values, uint32_t n) { orc_exp2_override = values; orc_exp2_override_n = n; }
+
 /* per-level constants, gridencoder.cu:137-139 (float exp2f, fused `*H - 1`). */
 static void orc_level_consts(uint32_t level, float S, uint32_t H, float *scale, uint32_t *resolution) {
-    const float e = exp2f((float)level * S);
+    const float e = (orc_exp2_override && level < orc_exp2_override_n) ? orc_exp2_override[level] : exp2f((float)level * S);
     *scale = fmaf(e, (float)H, -1.0f);
     *resolution = (uint32_t)ceilf(*scale) + 1;
 }
@@ -73,6 +80,13 @@ static int orc_oob(const float *x, uint32_t D) {
     return 0;
 }
 
+/* The reference declares `float pos_deriv[D] = {1.0f}` (gridencoder.cu:143): only element 0 is 1, the
+ * rest are 0, so with LINEAR interpolation its dy_dx (and therefore grad_inputs) is zero for d > 0.
+ * quirk == 1 restates that faithfully (used when checking against the reference extension);
+ * quirk == 0 (default) is the mathematically correct derivative, which is what the B200 kernels ship. */
+static int orc_pos_deriv_quirk = 0;
+void orc_set_pos_deriv_quirk(int on) { orc_pos_deriv_quirk = on; }
+
 /* gridencoder.cu:146-156: position inside the level; returns base cell + (smooth)fraction. */
 static void orc_locate(const float *x, uint32_t D, float scale, int align_corners, uint32_t interp,
                        float *pos, float *pos_deriv, uint32_t *pos_grid) {
@@ -81,7 +95,7 @@ static void orc_locate(const float *x, uint32_t D, float scale, int align_corner
         const float fl = floorf(p);
         pos_grid[d] = (uint32_t)fl;
         p -= (float)pos_grid[d];
-        pos_deriv[d] = 1.0f;
+        pos_deriv[d] = (orc_pos_deriv_quirk && d > 0) ? 0.0f : 1.0f;
         if (interp == 1) { /* smoothstep, gridencoder.cu:39-47 */
             pos_deriv[d] = 6 * p * (1.0f - p);
             p = p * p * (3.0f - 2.0f * p);

@@ -1,0 +1,120 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/ngp_b200.h declares, the ctypes table agrees with the header, and the Python packages
+expose the reference's plugin API (names, signatures, defaults).  No compute calls (no GPU here)."""
+import inspect
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "ngp_b200.h")
+
+
+def _header_decls():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    decls = {}
+    for m in re.finditer(r"NGP_API\s+([\w\s\*]+?)\b(ngp_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.S):
+        args = m.group(3).strip()
+        n = 0 if args in ("", "void") else len([a for a in args.split(",") if a.strip()])
+        decls[m.group(2)] = n
+    return decls
+
+
+def test_library_exports_every_declared_symbol():
+    import ngp_abi
+    decls = _header_decls()
+    assert len(decls) >= 27
+    out = subprocess.check_output(["nm", "-D", "--defined-only", ngp_abi.LIB_PATH], text=True)
+    exported = {line.split()[-1] for line in out.splitlines() if " T " in line}
+    missing = sorted(set(decls) - exported)
+    assert not missing, f"declared in ngp_b200.h but not exported: {missing}"
+    undeclared = sorted(s for s in exported if s.startswith("ngp_") and s not in decls)
+    assert not undeclared, f"exported but not declared: {undeclared}"
+
+
+def test_ctypes_table_matches_header():
+    import ngp_abi
+    decls = _header_decls()
+    assert set(ngp_abi.SIGNATURES) == set(decls)
+    for name, n in decls.items():
+        assert len(ngp_abi.SIGNATURES[name][1]) == n, name
+
+
+def test_library_is_sm100a_only_and_has_no_cpu_fallback():
+    import ngp_abi
+    out = subprocess.run(["cuobjdump", "-lelf", ngp_abi.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+    assert ngp_abi.lib.ngp_abi_version() == 1
+    assert ngp_abi.get_option("hashgrid_fwd_variant") == -1
+    with pytest.raises(ngp_abi.NgpError, match="unknown option"):
+        ngp_abi.set_option("no_such_option", 1)
+    # the product path never imports the oracle
+    pkg = os.path.join(ROOT, "torch-ngp_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "cpu_ref" not in text and "ngp_oracle" not in text and "from oracle" not in text, f
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+    import gridencoder
+    import raymarching
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        gridencoder._backend.grid_encode_forward(torch.rand(4, 3), torch.rand(64, 2), torch.tensor([0, 64], dtype=torch.int32),
+                                                 torch.empty(1, 4, 2), 4, 3, 2, 1, 1.0, 4, None, 0, False, 0)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        raymarching._backend.morton3D(torch.zeros(4, 3, dtype=torch.int32), 4, torch.zeros(4, dtype=torch.int32))
+
+
+def test_plugin_api_signatures_match_reference():
+    """Names and defaults of /root/reference/{gridencoder/grid.py:755,raymarching/raymarching.py,ffmlp/ffmlp.py:100}."""
+    import gridencoder
+    import raymarching
+    sig = inspect.signature(gridencoder.GridEncoder.__init__)
+    expect = dict(input_dim=3, num_levels=16, level_dim=2, per_level_scale=2, base_resolution=16, log2_hashmap_size=19,
+                  desired_resolution=None, gridtype="hash", align_corners=False, interpolation="linear")
+    assert {k: v.default for k, v in sig.parameters.items() if k != "self"} == expect
+    assert list(inspect.signature(gridencoder.GridEncoder.forward).parameters) == ["self", "inputs", "bound"]
+    assert list(inspect.signature(gridencoder.GridEncoder.grad_total_variation).parameters) == ["self", "weight", "inputs", "bound", "B"]
+    fwd = inspect.signature(gridencoder.grid._grid_encode.forward)
+    assert list(fwd.parameters)[1:] == ["inputs", "embeddings", "offsets", "per_level_scale", "base_resolution", "calc_grad_inputs",
+                                        "gridtype", "align_corners", "interpolation"]
+    rm = raymarching.raymarching
+    assert list(inspect.signature(rm._march_rays_train.forward).parameters)[1:] == [
+        "rays_o", "rays_d", "bound", "density_bitfield", "C", "H", "nears", "fars", "step_counter", "mean_count", "perturb", "align",
+        "force_all_rays", "dt_gamma", "max_steps"]
+    d = {k: v.default for k, v in inspect.signature(rm._march_rays_train.forward).parameters.items()}
+    assert (d["mean_count"], d["perturb"], d["align"], d["force_all_rays"], d["dt_gamma"], d["max_steps"]) == (-1, False, -1, False, 0, 1024)
+    assert list(inspect.signature(rm._march_rays.forward).parameters)[1:] == [
+        "n_alive", "n_step", "rays_alive", "rays_t", "rays_o", "rays_d", "bound", "density_bitfield", "C", "H", "near", "far", "align",
+        "perturb", "dt_gamma", "max_steps"]
+    assert inspect.signature(rm._composite_rays_train.forward).parameters["T_thresh"].default == 1e-4
+    assert inspect.signature(rm._composite_rays.forward).parameters["T_thresh"].default == 1e-2
+    assert inspect.signature(rm._near_far_from_aabb.forward).parameters["min_near"].default == 0.2
+    for name in ("near_far_from_aabb", "sph_from_ray", "morton3D", "morton3D_invert", "packbits", "march_rays_train",
+                 "composite_rays_train", "march_rays", "composite_rays"):
+        assert callable(getattr(raymarching, name))
+    for name in ("near_far_from_aabb", "sph_from_ray", "morton3D", "morton3D_invert", "packbits", "march_rays_train",
+                 "composite_rays_train_forward", "composite_rays_train_backward", "march_rays", "composite_rays"):
+        assert callable(getattr(raymarching._backend, name))
+    for name in ("grid_encode_forward", "grid_encode_backward", "grad_total_variation"):
+        assert callable(getattr(gridencoder._backend, name))
+
+
+def test_grid_encoder_state_dict_layout():
+    """Checkpoint compatibility: parameter/buffer names, shapes, dtypes of the reference module."""
+    import torch
+    import gridencoder
+    enc = gridencoder.GridEncoder(desired_resolution=2048)
+    sd = enc.state_dict()
+    assert set(sd) == {"embeddings", "offsets"}
+    assert sd["embeddings"].shape == (6119864, 2) and sd["embeddings"].dtype == torch.float32
+    assert sd["offsets"].shape == (17,) and sd["offsets"].dtype == torch.int32
+    assert enc.output_dim == 32 and int(enc.n_params) == 12239728
+    assert sd["embeddings"].abs().max() <= 1e-4

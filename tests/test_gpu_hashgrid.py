@@ -161,9 +161,13 @@ def test_warp_aggregated_backward_coherent_points(oracle):
     assert np.allclose(ge.cpu().numpy(), ref_ge, rtol=1e-4, atol=1e-4 * np.abs(ref_ge).max())
 
 
-def test_config1_slice_vs_oracle_fp32_fp16(oracle):
+def test_config1_slice_vs_oracle_fp32_fp16(oracle, request):
     """BASELINE config 1 geometry (L=16 F=2 T=2^19, desired_resolution 2048) on 2^14 points vs the oracle."""
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
+    # the level scale uses the device's exp2f; give the oracle the same 16 values (see ngp_oracle.c)
+    S32 = torch.tensor(np.float32(np.log2(pls)), device=DEV)
+    oracle.set_level_exp2(torch.exp2(torch.arange(16, device=DEV, dtype=torch.float32) * S32).cpu().numpy())
+    request.addfinalizer(lambda: oracle.set_level_exp2(None))
     rng = np.random.default_rng(0)
     B = 1 << 14
     x = rng.random((B, 3)).astype(np.float32)
@@ -172,18 +176,14 @@ def test_config1_slice_vs_oracle_fp32_fp16(oracle):
     xt, ot = torch.from_numpy(x).to(DEV), torch.from_numpy(offsets).to(DEV)
     out, _ = _run_fwd(xt, torch.from_numpy(emb).to(DEV), ot, pls, 16)
     got = out.cpu().numpy()
-    # device exp2f vs libm exp2f may differ by an ulp in the level scale: allow a handful of cell-boundary flips
-    bad = np.abs(got - ref) > 1e-5 * np.abs(ref).max() + 1e-5 * np.abs(ref)
-    assert bad.mean() < 1e-4, bad.mean()
-    assert np.abs(got - ref).max() < 5e-3
+    assert np.allclose(got, ref, rtol=1e-5, atol=1e-5 * np.abs(ref).max())
     out16, _ = _run_fwd(xt, torch.from_numpy(emb).to(DEV).half(), ot, pls, 16)
     ref16, _ = oracle.grid_encode_forward(x, emb.astype(np.float16).astype(np.float32), offsets, pls, 16)
     assert np.allclose(out16.float().cpu().numpy(), ref16, rtol=1e-3, atol=1e-3 * np.abs(ref16).max())
     g = rng.standard_normal(ref.shape).astype(np.float32)
     ref_ge, _ = oracle.grid_encode_backward(g, x, emb, offsets, pls, 16)
     ge, _ = _run_bwd(torch.from_numpy(g).to(DEV), xt, torch.from_numpy(emb).to(DEV), ot, pls, 16)
-    bad = np.abs(ge.cpu().numpy() - ref_ge) > 1e-4 * np.abs(ref_ge).max()
-    assert bad.mean() < 1e-4
+    assert np.allclose(ge.cpu().numpy(), ref_ge, rtol=1e-4, atol=1e-5 * np.abs(ref_ge).max())
 
 
 def test_full_size_properties_config1():

@@ -26,6 +26,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_bwd_variant", -1},  // -1 auto, 0 generic atomics, 1 paired + warp-aggregated
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
+        {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_block", 128},
     };
     return o;

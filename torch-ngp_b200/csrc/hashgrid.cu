@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
                                                           const int *__restrict__ offsets, T *__restrict__ outputs,
                                                           uint32_t B, uint32_t L, float S, uint32_t H,
                                                           T *__restrict__ dy_dx, uint32_t gridtype, bool align_corners,
-                                                          uint32_t interp, int layout) {
+                                                          uint32_t interp, int layout, bool pos_deriv_quirk) {
     using A = typename acc_of<T>::type;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -129,7 +129,10 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
         pos[d] = x[d] * lv.scale + (align_corners ? 0.0f : 0.5f);
         pg[d] = (uint32_t)floorf(pos[d]);
         pos[d] -= (float)pg[d];
-        pos_deriv[d] = 1.0f;
+        // The reference initialises `float pos_deriv[D] = {1.0f}` (gridencoder.cu:143): only element 0 is 1, so its
+        // linear-interpolation dy_dx is zero for d > 0.  Default here is the correct derivative (all ones);
+        // option hashgrid_ref_pos_deriv_quirk=1 reproduces the reference bit for bit.
+        pos_deriv[d] = (pos_deriv_quirk && d > 0) ? 0.0f : 1.0f;
         if (interp == 1) {
             pos_deriv[d] = smoothstep_df(pos[d]);
             pos[d] = smoothstep_f(pos[d]);

@@ -11,11 +11,12 @@ template <typename T, uint32_t D>
 int launch_fwd_generic(const float *inputs, const T *emb, const int *offsets, T *out, uint32_t B, uint32_t C, uint32_t L,
                        float S, uint32_t H, T *dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     const dim3 grid(div_round_up(B, 256u), L, 1);
+    const bool quirk = get_option("hashgrid_ref_pos_deriv_quirk", 0) != 0;
     switch (C) {
-        case 1: k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout); break;
-        case 2: k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout); break;
-        case 4: k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout); break;
-        case 8: k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout); break;
+        case 1: k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
+        case 2: k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
+        case 4: k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
+        case 8: k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
         default: set_error("GridEncoding: C must be 1, 2, 4, or 8."); return NGP_EINVAL;
     }
     NGP_CHECK_LAUNCH();
@@ -172,6 +173,7 @@ int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const i
                             void *outputs, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
                             uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream) {
     using namespace ngp;
+    if (B == 0) return NGP_OK;
     NGP_CHECK_ARG(inputs && embeddings && offsets && outputs, "grid_encode_forward: null pointer argument");
     NGP_CHECK_ARG(layout == NGP_LAYOUT_LBC || layout == NGP_LAYOUT_BLC, "grid_encode_forward: bad layout %d", layout);
     NGP_CHECK_ARG(L >= 1 && L <= 65535, "grid_encode_forward: L=%u out of range", L);
@@ -199,6 +201,7 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
                              uint32_t interp, int dtype, int layout, void *stream) {
     using namespace ngp;
     (void)embeddings;
+    if (B == 0) return NGP_OK;
     NGP_CHECK_ARG(grad && inputs && offsets && grad_embeddings, "grid_encode_backward: null pointer argument");
     NGP_CHECK_ARG((dy_dx == nullptr) == (grad_inputs == nullptr), "grid_encode_backward: dy_dx and grad_inputs must be given together");
     NGP_CHECK_ARG(layout == NGP_LAYOUT_LBC || layout == NGP_LAYOUT_BLC, "grid_encode_backward: bad layout %d", layout);
@@ -238,6 +241,7 @@ int ngp_grad_total_variation(const void *inputs, const void *embeddings, void *g
                              uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, uint32_t gridtype,
                              int align_corners, int dtype, void *stream) {
     using namespace ngp;
+    if (B == 0) return NGP_OK;
     NGP_CHECK_ARG(inputs && embeddings && grad && offsets, "grad_total_variation: null pointer argument");
     if (B == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;

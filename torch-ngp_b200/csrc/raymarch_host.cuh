@@ -13,8 +13,8 @@ extern "C" {
 int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, uint32_t N, float min_near,
                            float *nears, float *fars, void *stream) {
     using namespace ngp;
-    NGP_CHECK_ARG(rays_o && rays_d && aabb && nears && fars, "near_far_from_aabb: null pointer argument");
     if (N == 0) return NGP_OK;
+    NGP_CHECK_ARG(rays_o && rays_d && aabb && nears && fars, "near_far_from_aabb: null pointer argument");
     k_near_far<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N, min_near, nears, fars);
     NGP_CHECK_LAUNCH();
     return NGP_OK;
@@ -22,8 +22,8 @@ int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float
 
 int ngp_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uint32_t N, float *coords, void *stream) {
     using namespace ngp;
-    NGP_CHECK_ARG(rays_o && rays_d && coords, "sph_from_ray: null pointer argument");
     if (N == 0) return NGP_OK;
+    NGP_CHECK_ARG(rays_o && rays_d && coords, "sph_from_ray: null pointer argument");
     k_sph_from_ray<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, radius, N, coords);
     NGP_CHECK_LAUNCH();
     return NGP_OK;
@@ -31,8 +31,8 @@ int ngp_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uin
 
 int ngp_morton3D(const int *coords, uint32_t N, int *indices, void *stream) {
     using namespace ngp;
-    NGP_CHECK_ARG(coords && indices, "morton3D: null pointer argument");
     if (N == 0) return NGP_OK;
+    NGP_CHECK_ARG(coords && indices, "morton3D: null pointer argument");
     k_morton3D<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(coords, N, indices);
     NGP_CHECK_LAUNCH();
     return NGP_OK;
@@ -40,8 +40,8 @@ int ngp_morton3D(const int *coords, uint32_t N, int *indices, void *stream) {
 
 int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *stream) {
     using namespace ngp;
-    NGP_CHECK_ARG(indices && coords, "morton3D_invert: null pointer argument");
     if (N == 0) return NGP_OK;
+    NGP_CHECK_ARG(indices && coords, "morton3D_invert: null pointer argument");
     k_morton3D_invert<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(indices, N, coords);
     NGP_CHECK_LAUNCH();
     return NGP_OK;
@@ -49,8 +49,8 @@ int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *strea
 
 int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream) {
     using namespace ngp;
-    NGP_CHECK_ARG(grid && bitfield, "packbits: null pointer argument");
     if (N == 0) return NGP_OK;
+    NGP_CHECK_ARG(grid && bitfield, "packbits: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
     uint32_t done = 0;
     if (aligned(grid, 16) && aligned(bitfield, 4) && N >= 4) {
@@ -76,11 +76,11 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
                          const float *fars, float *xyzs, float *dirs, float *deltas, int *rays, int *counter,
                          const float *noises, void *workspace, size_t workspace_bytes, void *stream) {
     using namespace ngp;
+    if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays_o && rays_d && grid && nears && fars && xyzs && dirs && deltas && rays && counter && noises,
                   "march_rays_train: null pointer argument");
     NGP_CHECK_ARG(C >= 1 && C <= 16 && H >= 1 && H <= 1024, "march_rays_train: C=%u / H=%u out of range", C, H);
     NGP_CHECK_ARG(aligned(deltas, 8), "march_rays_train: deltas must be 8-byte aligned");
-    if (N == 0) return NGP_OK;
     const uint32_t nb = div_round_up(N, (uint32_t)kMarchBlock);
     NGP_CHECK_ARG(workspace && workspace_bytes >= scan_ws_bytes(nb), "march_rays_train: workspace too small (%zu < %zu bytes)",
                   workspace_bytes, scan_ws_bytes(nb));
@@ -100,9 +100,9 @@ int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, con
                                      uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth,
                                      float *image, void *stream) {
     using namespace ngp;
+    if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays && weights_sum && depth && image, "composite_rays_train_forward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas), "composite_rays_train_forward: null sample buffers with M=%u", M);
-    if (N == 0) return NGP_OK;
     k_composite_train_fwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(sigmas, rgbs, deltas, rays, M, N, T_thresh,
                                                                                  weights_sum, depth, image);
     NGP_CHECK_LAUNCH();
@@ -114,11 +114,11 @@ int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float
                                       const float *weights_sum, const float *depth, const float *image, uint32_t M,
                                       uint32_t N, float T_thresh, float *grad_sigmas, float *grad_rgbs, void *stream) {
     using namespace ngp;
+    if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(grad_weights_sum && grad_depth && grad_image && rays && weights_sum && depth && image,
                   "composite_rays_train_backward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas && grad_sigmas && grad_rgbs),
                   "composite_rays_train_backward: null sample buffers with M=%u", M);
-    if (N == 0) return NGP_OK;
     k_composite_train_bwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(
         grad_weights_sum, grad_depth, grad_image, sigmas, rgbs, deltas, rays, weights_sum, depth, image, M, N, T_thresh,
         grad_sigmas, grad_rgbs);
