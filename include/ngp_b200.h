@@ -156,6 +156,15 @@ NGP_API int ngp_free_splitk(void);
 NGP_API int ngp_sh_encode_forward(const float *inputs, void *outputs, uint32_t B, uint32_t degree, uint32_t out_stride,
                           int dtype, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * diagnostics
+ * ------------------------------------------------------------------------------------------- */
+/* Runs nk tcgen05.mma (kind::f16, M=128) instructions on caller-built shared-memory byte images and
+ * dumps the fp32 accumulator D[128, N] (tests/test_gpu_umma.py pins the operand-image conventions). */
+NGP_API int ngp_umma_selftest(const void *a_img, uint32_t a_bytes, const void *b_img, uint32_t b_bytes, float *D, uint32_t N,
+                      uint32_t nk, uint32_t idesc, uint32_t a_lbo, uint32_t a_sbo, uint32_t a_step, uint32_t b_lbo,
+                      uint32_t b_sbo, uint32_t b_step, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,7 @@ SIGNATURES = {
     "ngp_allocate_splitk": (_int, [_sz]),
     "ngp_free_splitk": (_int, []),
     "ngp_sh_encode_forward": (_int, [_vp, _vp, _u32, _u32, _u32, _int, _vp]),
+    "ngp_umma_selftest": (_int, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp]),
 }
 
 
