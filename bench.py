@@ -1,0 +1,382 @@
+"""bench.py -- the driver's measurement contract for the Instant-NGP hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One JSON line on stdout (rank 0).  Workloads (BASELINE.json `configs`):
+    hashgrid    configs[0]  GridEncoder fwd+bwd, 2^18 random points, L=16 F=2 log2_hashmap=19, fp32
+    nerf_train  configs[1]/[2]  NeRF training step (hash grid + cuda_ray + fp16), 4096 rays per GPU per step
+    render      configs[3]  1920x1080 inference frame, row bands sharded over the GPUs
+    sdf         configs[4]  hash-grid SDF + FFMLP, 2^20 points per GPU per step
+A "step" is one pass of the hot path over one batch of synthetic input.  `value` is timed with inputs
+resident in HBM; `e2e` is the same metric through the public plugin API with pinned HOST inputs, the
+H2D copy and a D2H read of the result inside the timed region.  `--impl reference` times the CPU
+restatement under oracle/ (the reference has no CPU implementation of this path) on
+the host cores, bounded sample, rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "torch-ngp_b200"), os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+
+def load_peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written) else the profiling recipe's fallback."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "tflops": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "tflops_burst": float(p["bf16_tflops"]), "source": "measured"}
+    except Exception:
+        return {"hbm_gbs": 6650.0, "tflops": 1400.0, "tflops_burst": 1590.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0, period_ms=100):
+        self.index, self.period_ms, self.proc, self.lines = index, period_ms, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", str(self.period_ms)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(n_gpus):
+    """One process per GPU under torchrun; single process otherwise."""
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo", rank=rank, world_size=world)
+    return rank, world, local
+
+
+def barrier_sync(world):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+# ==================================================================================================
+# workload: GridEncoder fwd+bwd (BASELINE.json configs[0])
+# ==================================================================================================
+class HashGridWorkload:
+    """2^18 points U[-1,1]^3 per GPU, L=16 F=2 log2_hashmap=19 desired_resolution=2048, fp32 table.
+    Device step = forward + grad-table clear + backward through gridencoder._backend (C ABI).
+    Algorithmic bytes: fwd 1,164 B/pt, bwd 1,164 B/pt + T*C*4 B table clear."""
+    name = "hashgrid"
+    metric = "hash-encode Mpts/s fwd+bwd"
+    unit = "Mpts/s"
+    dtype = "f32"
+    scaling = "weak"
+
+    def __init__(self, args):
+        self.B = args.points or (1 << 18)
+        self.L, self.C, self.D, self.H = 16, 2, 3, 16
+
+    def config(self, world):
+        return {"workload": "GridEncoder fwd+bwd, 2^18 random points in [-1,1]^3 per GPU, L=16 F=2 log2_hashmap=19 fp32 (configs[0])",
+                "points_per_gpu": self.B, "table_entries": int(self.T), "l2": "flushed between steps (256 MiB memset outside the per-step events)",
+                "parallelism": f"dp{world} (independent points, no collective)"}
+
+    def setup(self, dev, rank, world):
+        import torch
+        import gridencoder
+        self.torch, self.dev = torch, dev
+        torch.manual_seed(1000 + rank)
+        self.enc = gridencoder.GridEncoder(desired_resolution=2048).to(dev)
+        self.T = int(self.enc.offsets[-1].item())
+        self.S = float(np.log2(self.enc.per_level_scale))
+        self.x01 = torch.rand(self.B, 3, device=dev)
+        self.grad = torch.randn(self.B, self.L * self.C, device=dev)
+        self.out = torch.empty(self.B, self.L * self.C, device=dev)
+        self.g_emb = torch.zeros_like(self.enc.embeddings)
+        self.be = gridencoder._backend
+        self.oh = self.be.host_offsets(self.enc.offsets)
+        # e2e: pinned host inputs
+        self.x_host = (self.x01 * 2 - 1).cpu().pin_memory()
+        self.g_host = self.grad.cpu().pin_memory()
+        self.x_dev = torch.empty_like(self.x01)
+        self.units_per_step = self.B
+        self.h2d_bytes = self.x_host.numel() * 4 + self.g_host.numel() * 4
+        self.d2h_bytes = 4
+
+    def step_device(self):
+        import ngp_abi as abi
+        e, emb = self.enc, self.enc.embeddings.data
+        self.be.grid_encode_forward(self.x01, emb, e.offsets, self.out, self.B, 3, 2, self.L, self.S, self.H, None, 0, False, 0,
+                                    layout=abi.LAYOUT_BLC, offsets_host=self.oh)
+        self.g_emb.zero_()
+        self.be.grid_encode_backward(self.grad, self.x01, emb, e.offsets, self.g_emb, self.B, 3, 2, self.L, self.S, self.H, None, None,
+                                     0, False, 0, layout=abi.LAYOUT_BLC, offsets_host=self.oh)
+
+    def step_e2e(self):
+        """Public API: GridEncoder.forward + autograd backward; inputs and upstream gradient come from pinned host memory."""
+        torch = self.torch
+        self.x_dev.copy_(self.x_host, non_blocking=True)
+        g = self.g_host.to(self.dev, non_blocking=True)
+        self.enc.embeddings.grad = None
+        y = self.enc(self.x_dev, bound=1)
+        loss = (y * g).sum()
+        loss.backward()
+        return float(loss.item())  # D2H
+
+    def launches_per_step(self):
+        return None  # counted live
+
+    def roofline(self, prof, peaks, steps):
+        """Dominant kernel = the L2-level scatter of the backward (k_grid_bwd_d3c2): its share of the algorithmic bytes."""
+        Lh = self.L - self.n_smem_levels(prof)
+        per_level_bwd = self.B * (self.C * 4 + 8 * self.C * 4) + 0  # grad read + 8 corner RMW targets (counted once, as SURVEY)
+        name = "k_grid_bwd_d3c2"
+        if name not in prof:
+            return None
+        cnt, ms = prof[name]
+        alg = Lh * per_level_bwd + self.B * 12
+        achieved = alg / (ms / cnt * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                "traffic": None, "peak_source": peaks["source"], "algorithmic_bytes_per_launch": alg, "us_per_launch": ms / cnt * 1e3}
+
+    def n_smem_levels(self, prof):
+        n = 0
+        for l in range(self.L):
+            if (int(self.oh[l + 1]) - int(self.oh[l])) * 8 <= 200 * 1024:
+                n += 1
+            else:
+                break
+        return n
+
+    def step_algorithmic_bytes(self):
+        s = 4
+        return self.B * (4 * 3 + 8 * self.L * self.C * s + self.L * self.C * s) * 2 + self.T * self.C * s
+
+    # ---- CPU baseline: the oracle port (C + OpenMP), all host cores, bounded sample -------------
+    def cpu_baseline(self, budget_s=15.0):
+        from oracle import cpu_ref
+        cpu_ref.build()
+        offs, pls = cpu_ref.make_offsets(desired_resolution=2048)
+        rng = np.random.default_rng(0)
+        emb = ((rng.random((offs[-1], 2)) - 0.5) * 2e-4).astype(np.float32)
+        Bs = 1 << 16
+        x = rng.random((Bs, 3)).astype(np.float32)
+        g = rng.standard_normal((16, Bs, 2)).astype(np.float32)
+        t_total, n = 0.0, 0
+        cpu_ref.grid_encode_forward(x, emb, offs, pls, 16)  # warm-up
+        while t_total < budget_s and n < 64:
+            t0 = time.perf_counter()
+            cpu_ref.grid_encode_forward(x, emb, offs, pls, 16)
+            cpu_ref.grid_encode_backward(g, x, emb, offs, pls, 16)
+            t_total += time.perf_counter() - t0
+            n += 1
+        return {"value": Bs * n / t_total / 1e6, "unit": self.unit, "cores": os.cpu_count(), "kind": "port",
+                "sample": f"{n} x fwd+bwd of 2^16 points (same table), oracle/ngp_oracle.c with OpenMP on all host cores"}
+
+
+WORKLOADS = {"hashgrid": HashGridWorkload}
+DEFAULT_WORKLOAD = "hashgrid"
+
+
+# ==================================================================================================
+# driver
+# ==================================================================================================
+def timed_region(wl, steps, world, flush):
+    """EXACTLY `steps` steps, barrier + synchronize on both sides, per-step CUDA events on the launching
+    (current) stream; the L2 flush sits between the per-step event pairs.  -> mean ms per step (this rank)."""
+    import torch
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    barrier_sync(world)
+    for a, b in ev:
+        if flush is not None:
+            flush.zero_()
+        a.record()
+        wl.step_device()
+        b.record()
+    barrier_sync(world)
+    return sum(a.elapsed_time(b) for a, b in ev) / steps
+
+
+def e2e_region(wl, steps, world):
+    """Same metric through the public API with pinned host inputs; wall clock around H2D + step + D2H."""
+    barrier_sync(world)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        wl.step_e2e()
+    barrier_sync(world)
+    return (time.perf_counter() - t0) * 1e3 / steps
+
+
+def run_reference(wl, args, rank, world):
+    """`--impl reference`: the CPU restatement of the path on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    per = max(2.0, min(20.0, 60.0 / max(1, args.steps + args.warmup)))
+    for _ in range(min(args.warmup, 1)):
+        wl.cpu_baseline(budget_s=1.0)
+    vals = [wl.cpu_baseline(budget_s=per) for _ in range(max(1, min(args.steps, 4)))]
+    v = float(np.median([x["value"] for x in vals]))
+    cb = dict(vals[0]); cb["value"] = v
+    wl.T = getattr(wl, "T", 0)
+    line = {"impl": "reference", "metric": wl.metric, "value": v, "unit": wl.unit, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
+            "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world) if hasattr(wl, "enc") or True else {},
+            "cpu_baseline": cb, "e2e": {"value": v, "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default=os.environ.get("NGP_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--points", type=int, default=0, help="override the per-GPU batch (development only)")
+    ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    wl = WORKLOADS[args.workload](args)
+    if args.impl == "reference":
+        rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+        if hasattr(wl, "T") is False:
+            wl.T = 6119864
+        run_reference(wl, args, rank, world)
+        return
+
+    import torch
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (the product path has no CPU fallback)"
+    rank, world, local = dist_setup(args.gpus)
+    dev = torch.device("cuda", local)
+    import ngp_abi as abi
+    peaks = load_peaks()
+    wl.setup(dev, rank, world)
+    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    for _ in range(args.warmup):
+        wl.step_device()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(index=local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    n0 = abi.launch_count()
+    ms_local = timed_region(wl, args.steps, world, flush)
+    launches = (abi.launch_count() - n0) / args.steps
+    clocks = sampler.stop() if sampler else None
+    ms = max_over_ranks(ms_local, world)
+    units = sum_over_ranks(float(wl.units_per_step), world)
+
+    # per-kernel durations, live, same region re-run with the library's per-launch CUDA events enabled
+    abi.set_option("profile_events", 1)
+    timed_region(wl, args.steps, world, flush)
+    prof = abi.profile_collect()
+    abi.set_option("profile_events", 0)
+    roof = wl.roofline(prof, peaks, args.steps)
+
+    # end to end through the plugin API, host buffers
+    for _ in range(2):
+        wl.step_e2e()
+    ms_e2e = max_over_ranks(e2e_region(wl, args.steps, world), world)
+
+    if rank == 0:
+        scale = 1e-6 if wl.unit.startswith("M") else 1.0
+        line = {"metric": wl.metric, "value": units / (ms * 1e-3) * scale, "unit": wl.unit, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
+                "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world),
+                "e2e": {"value": units / (ms_e2e * 1e-3) * scale, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
+                        "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": ms_e2e},
+                "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+                "kernels": {k: {"launches_per_step": c / args.steps, "us_per_launch": t / c * 1e3} for k, (c, t) in sorted(prof.items())}}
+        if hasattr(wl, "step_algorithmic_bytes"):
+            a = wl.step_algorithmic_bytes()
+            line["roofline_step"] = {"bound": "hbm", "achieved": a / (ms_local * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                     "frac": a / (ms_local * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": a}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = wl.cpu_baseline()
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

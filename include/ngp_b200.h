@@ -55,6 +55,11 @@ NGP_API int ngp_abi_version(void);
 /* Tuning knobs used by bench/tests (e.g. "hashgrid_fwd_variant"); unknown keys -> NGP_EINVAL. */
 NGP_API int ngp_set_option(const char *key, int value);
 NGP_API int ngp_get_option(const char *key, int *value);
+/* Launch accounting: total kernel launches made by the library in this process, and -- while option
+ * "profile_events" is 1 (not during CUDA-graph capture) -- per-kernel CUDA-event durations, returned as
+ * text lines "<kernel> <count> <total_ms>\n" (the call synchronises on the recorded events and clears them). */
+NGP_API long long ngp_launch_count(void);
+NGP_API int ngp_profile_collect(char *buf, size_t buf_bytes);
 
 /* ---------------------------------------------------------------------------------------------
  * gridencoder  (replaces gridencoder.h:12-15)
@@ -124,22 +129,29 @@ NGP_API int ngp_compact_alive(const int *in, uint32_t n, const int *n_dev, int *
                       size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
- * ffmlp  (replaces ffmlp.h:8-14).  fp16 storage, fp32 accumulation on tcgen05 tensor cores.
- * Row-major [B, dim] activations (== the reference's "col-major [dim, B]"), weights flat, each
- * layer row-major [out, in] (ffmlp.cu:631-634).  B % 128 == 0 (FFMLP.forward pads, ffmlp.py:157-159).
+ * ffmlp  (replaces ffmlp.h:8-14).  fp16 activations, fp32 accumulation on tcgen05 tensor cores (TMEM).
+ * Row-major [B, dim] activations (== the reference's "col-major [dim, B]"), weights flat, each layer
+ * row-major [out, in] (ffmlp.cu:631-634), fp16 or fp32 (`weights_dtype`; fp32 is rounded to fp16 while
+ * staged into shared memory).  Any B >= 0 (the ragged tail tile is masked; FFMLP.forward's padding copy,
+ * ffmlp.py:157-159, is not needed).  hidden_dim in {16,32,64,128}, input_dim % 16 == 0 (<= 128),
+ * output_dim % 16 == 0 (<= 128), num_layers >= 2 (num_layers + 1 matmuls), activation 0 = ReLU,
+ * output_activation 6 = None (all that FFMLP ever passes, ffmlp.py:107-108); anything else -> NGP_EUNSUPPORTED.
+ * forward_buffer / inference_buffer / backward_buffer are accepted for signature compatibility and may be
+ * NULL: they are never written (activations live in shared memory; the backward recomputes the forward).
  * ------------------------------------------------------------------------------------------- */
-NGP_API int ngp_ffmlp_forward(const void *inputs, const void *weights, uint32_t B, uint32_t input_dim, uint32_t output_dim,
-                      uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
-                      void *forward_buffer, void *outputs, void *stream);
-NGP_API int ngp_ffmlp_inference(const void *inputs, const void *weights, uint32_t B, uint32_t input_dim, uint32_t output_dim,
-                        uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
-                        void *inference_buffer, void *outputs, void *stream);
-/* grad_weights is fp16 like the reference when grad_weights_dtype == NGP_DTYPE_F16, or an fp32 buffer
- * (NGP_DTYPE_F32, no K=2^20 reduction in half precision).  Both are OVERWRITTEN, not accumulated. */
-NGP_API int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, const void *forward_buffer,
-                       uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers,
-                       uint32_t activation, uint32_t output_activation, int calc_grad_inputs, void *backward_buffer,
-                       void *grad_inputs, void *grad_weights, int grad_weights_dtype, void *workspace,
+NGP_API int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim,
+                      uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                      uint32_t output_activation, void *forward_buffer, void *outputs, void *stream);
+NGP_API int ngp_ffmlp_inference(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim,
+                        uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                        uint32_t output_activation, void *inference_buffer, void *outputs, void *stream);
+/* grad_weights: fp16 like the reference (NGP_DTYPE_F16) or fp32 (NGP_DTYPE_F32); OVERWRITTEN, not accumulated.
+ * grad_inputs [B, input_dim] fp16, written iff calc_grad_inputs.  workspace: ngp_ffmlp_backward_workspace_bytes()
+ * bytes, zero-initialised once by the caller; the kernel leaves it zeroed for the next call. */
+NGP_API int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, int weights_dtype,
+                       const void *forward_buffer, uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
+                       uint32_t num_layers, uint32_t activation, uint32_t output_activation, int calc_grad_inputs,
+                       void *backward_buffer, void *grad_inputs, void *grad_weights, int grad_weights_dtype, void *workspace,
                        size_t workspace_bytes, void *stream);
 NGP_API size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
                                           uint32_t num_layers);

@@ -2,9 +2,11 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "common.cuh"
 
@@ -28,6 +30,8 @@ static std::map<std::string, int> &options() {
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_block", 128},
+        {"ffmlp_available", 0},
+        {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in
     };
     return o;
 }
@@ -36,6 +40,36 @@ int get_option(const char *key, int dflt) {
     std::lock_guard<std::mutex> l(g_opt_mu);
     auto it = options().find(key);
     return it == options().end() ? dflt : it->second;
+}
+
+// ---- launch accounting ---------------------------------------------------------------------------
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_prof_on{0};
+struct prof_rec { const char *name; cudaEvent_t a, b; };
+static std::mutex g_prof_mu;
+static std::vector<prof_rec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_free;
+
+static cudaEvent_t prof_event() {
+    if (!g_prof_free.empty()) { cudaEvent_t e = g_prof_free.back(); g_prof_free.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+prof_scope::prof_scope(const char *name, cudaStream_t st_) : slot(-1), st(st_) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> l(g_prof_mu);
+    prof_rec r{name, prof_event(), prof_event()};
+    cudaEventRecord(r.a, st);
+    slot = (int)g_prof_recs.size();
+    g_prof_recs.push_back(r);
+}
+prof_scope::~prof_scope() {
+    if (slot < 0) return;
+    std::lock_guard<std::mutex> l(g_prof_mu);
+    cudaEventRecord(g_prof_recs[slot].b, st);
 }
 
 int sm_count() {
@@ -66,7 +100,39 @@ int ngp_set_option(const char *key, int value) {
         return NGP_EINVAL;
     }
     it->second = value;
+    if (strcmp(key, "profile_events") == 0) ngp::g_prof_on.store(value != 0);
     return NGP_OK;
+}
+
+long long ngp_launch_count(void) { return ngp::g_launches.load(); }
+
+// Synchronises the recorded events and writes one line per kernel name: "<name> <count> <total_ms>\n".
+// Returns the number of bytes written (excluding the NUL), or a negative error code; clears the records.
+int ngp_profile_collect(char *buf, size_t buf_bytes) {
+    using namespace ngp;
+    if (!buf || buf_bytes == 0) return NGP_EINVAL;
+    std::lock_guard<std::mutex> l(g_prof_mu);
+    std::map<std::string, std::pair<long long, double>> agg;
+    for (auto &r : g_prof_recs) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+            auto &e = agg[r.name];
+            e.first += 1;
+            e.second += ms;
+        }
+        g_prof_free.push_back(r.a);
+        g_prof_free.push_back(r.b);
+    }
+    g_prof_recs.clear();
+    cudaGetLastError();
+    size_t off = 0;
+    buf[0] = 0;
+    for (auto &kv : agg) {
+        int n = snprintf(buf + off, buf_bytes - off, "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        if (n < 0 || (size_t)n >= buf_bytes - off) break;
+        off += (size_t)n;
+    }
+    return (int)off;
 }
 
 int ngp_get_option(const char *key, int *value) {

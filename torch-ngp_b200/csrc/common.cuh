@@ -13,6 +13,20 @@ void set_error(const char *fmt, ...);
 int get_option(const char *key, int dflt);
 int sm_count();  // SMs of the current device (148 on B200), cached
 
+// Per-launch accounting (abi.cu).  Always counts launches (ngp_launch_count); when the option
+// "profile_events" is 1 it also brackets the launch with CUDA events on `st`, read back through
+// ngp_profile_collect() -- bench.py's live per-kernel durations.  Not capture-safe: keep it off
+// while a CUDA graph is being captured.
+struct prof_scope {
+    int slot;
+    cudaStream_t st;
+    prof_scope(const char *name, cudaStream_t st);
+    ~prof_scope();
+};
+#define NGP_PROF_CAT2(a, b) a##b
+#define NGP_PROF_CAT(a, b) NGP_PROF_CAT2(a, b)
+#define NGP_PROF(name, st) ngp::prof_scope NGP_PROF_CAT(_ngp_ps_, __LINE__)(name, st)
+
 template <typename T>
 __host__ __device__ inline T div_round_up(T a, T b) { return (a + b - 1) / b; }
 

@@ -13,10 +13,10 @@ int launch_fwd_generic(const float *inputs, const T *emb, const int *offsets, T 
     const dim3 grid(div_round_up(B, 256u), L, 1);
     const bool quirk = get_option("hashgrid_ref_pos_deriv_quirk", 0) != 0;
     switch (C) {
-        case 1: k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
-        case 2: k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
-        case 4: k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
-        case 8: k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); break;
+        case 1: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
+        case 2: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
+        case 4: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
+        case 8: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
         default: set_error("GridEncoding: C must be 1, 2, 4, or 8."); return NGP_EINVAL;
     }
     NGP_CHECK_LAUNCH();
@@ -32,8 +32,8 @@ int launch_bwd_generic(const T *grad, const float *inputs, const int *offsets, T
     const uint32_t gi = div_round_up(B * D, 256u);
 #define NGP_BWD_CASE(CC)                                                                                                  \
     case CC:                                                                                                              \
-        k_grid_bwd_generic<T, D, CC><<<grid, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout); \
-        if (dy_dx) k_input_bwd<T, D, CC><<<gi, 256, 0, st>>>(grad, dy_dx, g_in, B, L, layout);                            \
+        { NGP_PROF("k_grid_bwd_generic", st); k_grid_bwd_generic<T, D, CC><<<grid, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout); } \
+        if (dy_dx) { NGP_PROF("k_input_bwd", st); k_input_bwd<T, D, CC><<<gi, 256, 0, st>>>(grad, dy_dx, g_in, B, L, layout); }                            \
         break;
     switch (C) {
         NGP_BWD_CASE(1) NGP_BWD_CASE(2) NGP_BWD_CASE(4) NGP_BWD_CASE(8)
@@ -49,10 +49,10 @@ int launch_tv(const T *inputs, const T *emb, T *grad, const int *offsets, float 
               float S, uint32_t H, uint32_t gridtype, bool ac, cudaStream_t st) {
     const dim3 grid(div_round_up(B, 256u), L, 1);
     switch (C) {
-        case 1: k_grad_tv<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); break;
-        case 2: k_grad_tv<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); break;
-        case 4: k_grad_tv<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); break;
-        case 8: k_grad_tv<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); break;
+        case 1: { NGP_PROF("k_grad_tv", st); k_grad_tv<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); } break;
+        case 2: { NGP_PROF("k_grad_tv", st); k_grad_tv<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); } break;
+        case 4: { NGP_PROF("k_grad_tv", st); k_grad_tv<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); } break;
+        case 8: { NGP_PROF("k_grad_tv", st); k_grad_tv<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, grad, offsets, weight, B, L, S, H, gridtype, ac); } break;
         default: set_error("GridEncoding: C must be 1, 2, 4, or 8."); return NGP_EINVAL;
     }
     NGP_CHECK_LAUNCH();
@@ -107,12 +107,12 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
         nb = nb < 1 ? 1 : nb;
         const uint32_t need = div_round_up(B, 1024u);
         nb = nb > need ? need : nb;
-        k_grid_fwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout);
+        { NGP_PROF("k_grid_fwd_d3c2_smem", st); k_grid_fwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout); }
         NGP_CHECK_LAUNCH();
     }
     if (ns < L) {
-        k_grid_fwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac,
-                                                                                 interp, layout, ns);
+        { NGP_PROF("k_grid_fwd_d3c2", st); k_grid_fwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac,
+                                                                                 interp, layout, ns); }
         NGP_CHECK_LAUNCH();
     }
     return NGP_OK;
@@ -134,13 +134,13 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         nb = nb < 1 ? 1 : nb;
         const uint32_t need = div_round_up(B, 1024u);
         nb = nb > need ? need : nb;
-        k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout);
+        { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout); }
         NGP_CHECK_LAUNCH();
     }
     if (ns < L) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
-        k_grid_bwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac,
-                                                                                 interp, layout, ns, warp_agg);
+        { NGP_PROF("k_grid_bwd_d3c2", st); k_grid_bwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac,
+                                                                                 interp, layout, ns, warp_agg); }
         NGP_CHECK_LAUNCH();
     }
     return NGP_OK;
@@ -217,7 +217,7 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
             if (fast) {
                 rc = bwd_d3c2<float>((const float *)grad, inputs, offsets, offsets_host, (float *)grad_embeddings, B, L, S, H, gridtype, ac, interp, layout, st);
                 if (rc != NGP_OK || !dy_dx) return rc;
-                k_input_bwd<float, 3, 2><<<div_round_up(B * 3, 256u), 256, 0, st>>>((const float *)grad, (const float *)dy_dx, (float *)grad_inputs, B, L, layout);
+                { NGP_PROF("k_input_bwd", st); k_input_bwd<float, 3, 2><<<div_round_up(B * 3, 256u), 256, 0, st>>>((const float *)grad, (const float *)dy_dx, (float *)grad_inputs, B, L, layout); }
                 NGP_CHECK_LAUNCH();
                 return NGP_OK;
             }
@@ -226,7 +226,7 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
             if (fast) {
                 rc = bwd_d3c2<__half>((const __half *)grad, inputs, offsets, offsets_host, (__half *)grad_embeddings, B, L, S, H, gridtype, ac, interp, layout, st);
                 if (rc != NGP_OK || !dy_dx) return rc;
-                k_input_bwd<__half, 3, 2><<<div_round_up(B * 3, 256u), 256, 0, st>>>((const __half *)grad, (const __half *)dy_dx, (__half *)grad_inputs, B, L, layout);
+                { NGP_PROF("k_input_bwd", st); k_input_bwd<__half, 3, 2><<<div_round_up(B * 3, 256u), 256, 0, st>>>((const __half *)grad, (const __half *)dy_dx, (__half *)grad_inputs, B, L, layout); }
                 NGP_CHECK_LAUNCH();
                 return NGP_OK;
             }

@@ -15,7 +15,7 @@ int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float
     using namespace ngp;
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays_o && rays_d && aabb && nears && fars, "near_far_from_aabb: null pointer argument");
-    k_near_far<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N, min_near, nears, fars);
+    { NGP_PROF("k_near_far", (cudaStream_t)stream); k_near_far<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N, min_near, nears, fars); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -24,7 +24,7 @@ int ngp_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uin
     using namespace ngp;
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays_o && rays_d && coords, "sph_from_ray: null pointer argument");
-    k_sph_from_ray<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, radius, N, coords);
+    { NGP_PROF("k_sph_from_ray", (cudaStream_t)stream); k_sph_from_ray<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, radius, N, coords); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -33,7 +33,7 @@ int ngp_morton3D(const int *coords, uint32_t N, int *indices, void *stream) {
     using namespace ngp;
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(coords && indices, "morton3D: null pointer argument");
-    k_morton3D<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(coords, N, indices);
+    { NGP_PROF("k_morton3D", (cudaStream_t)stream); k_morton3D<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(coords, N, indices); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -42,7 +42,7 @@ int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *strea
     using namespace ngp;
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(indices && coords, "morton3D_invert: null pointer argument");
-    k_morton3D_invert<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(indices, N, coords);
+    { NGP_PROF("k_morton3D_invert", (cudaStream_t)stream); k_morton3D_invert<<<div_round_up(N, 256u), 256, 0, (cudaStream_t)stream>>>(indices, N, coords); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -55,13 +55,13 @@ int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *b
     uint32_t done = 0;
     if (aligned(grid, 16) && aligned(bitfield, 4) && N >= 4) {
         const uint32_t N4 = N / 4;
-        k_packbits32<<<div_round_up(N4, 256u), 256, 0, st>>>(reinterpret_cast<const float4 *>(grid), N4, density_thresh,
-                                                             reinterpret_cast<uint32_t *>(bitfield));
+        { NGP_PROF("k_packbits32", st); k_packbits32<<<div_round_up(N4, 256u), 256, 0, st>>>(reinterpret_cast<const float4 *>(grid), N4, density_thresh,
+                                                             reinterpret_cast<uint32_t *>(bitfield)); }
         NGP_CHECK_LAUNCH();
         done = N4 * 4;
     }
     if (done < N) {
-        k_packbits_tail<<<div_round_up(N - done, 256u), 256, 0, st>>>(grid, done, N, density_thresh, bitfield);
+        { NGP_PROF("k_packbits_tail", st); k_packbits_tail<<<div_round_up(N - done, 256u), 256, 0, st>>>(grid, done, N, density_thresh, bitfield); }
         NGP_CHECK_LAUNCH();
     }
     return NGP_OK;
@@ -87,11 +87,11 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
     cudaStream_t st = (cudaStream_t)stream;
     march_ws_t *ws = reinterpret_cast<march_ws_t *>(workspace);
     NGP_CHECK_CUDA(cudaMemsetAsync(ws, 0, 2 * sizeof(uint32_t), st));
-    k_march_train_count<<<nb, kMarchBlock, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, noises,
-                                                   rays, counter, ws);
+    { NGP_PROF("k_march_train_count", st); k_march_train_count<<<nb, kMarchBlock, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, noises,
+                                                   rays, counter, ws); }
     NGP_CHECK_LAUNCH();
-    k_march_train_write<<<nb, kMarchBlock, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, noises,
-                                                   xyzs, dirs, deltas, rays, ws);
+    { NGP_PROF("k_march_train_write", st); k_march_train_write<<<nb, kMarchBlock, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, noises,
+                                                   xyzs, dirs, deltas, rays, ws); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -103,8 +103,8 @@ int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, con
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays && weights_sum && depth && image, "composite_rays_train_forward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas), "composite_rays_train_forward: null sample buffers with M=%u", M);
-    k_composite_train_fwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(sigmas, rgbs, deltas, rays, M, N, T_thresh,
-                                                                                 weights_sum, depth, image);
+    { NGP_PROF("k_composite_train_fwd", (cudaStream_t)stream); k_composite_train_fwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(sigmas, rgbs, deltas, rays, M, N, T_thresh,
+                                                                                 weights_sum, depth, image); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -119,9 +119,9 @@ int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float
                   "composite_rays_train_backward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas && grad_sigmas && grad_rgbs),
                   "composite_rays_train_backward: null sample buffers with M=%u", M);
-    k_composite_train_bwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(
+    { NGP_PROF("k_composite_train_bwd", (cudaStream_t)stream); k_composite_train_bwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(
         grad_weights_sum, grad_depth, grad_image, sigmas, rgbs, deltas, rays, weights_sum, depth, image, M, N, T_thresh,
-        grad_sigmas, grad_rgbs);
+        grad_sigmas, grad_rgbs); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -137,9 +137,9 @@ int ngp_march_rays(uint32_t n_alive, const int *n_alive_dev, uint32_t n_step, co
     NGP_CHECK_ARG(rays_alive && rays_t && rays_o && rays_d && grid && fars && xyzs && dirs && deltas && noises,
                   "march_rays: null pointer argument");
     NGP_CHECK_ARG(aligned(deltas, 8), "march_rays: deltas must be 8-byte aligned");
-    k_march_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, rays_alive, rays_t, rays_o,
+    { NGP_PROF("k_march_rays", (cudaStream_t)stream); k_march_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, rays_alive, rays_t, rays_o,
                                                                                rays_d, bound, dt_gamma, max_steps, C, H, grid, fars,
-                                                                               xyzs, dirs, deltas, noises);
+                                                                               xyzs, dirs, deltas, noises); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -152,9 +152,9 @@ int ngp_composite_rays(uint32_t n_alive, const int *n_alive_dev, uint32_t n_step
     NGP_CHECK_ARG(rays_alive && rays_t && sigmas && rgbs && deltas && weights_sum && depth && image,
                   "composite_rays: null pointer argument");
     NGP_CHECK_ARG(aligned(deltas, 8), "composite_rays: deltas must be 8-byte aligned");
-    k_composite_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, T_thresh, rays_alive,
+    { NGP_PROF("k_composite_rays", (cudaStream_t)stream); k_composite_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, T_thresh, rays_alive,
                                                                                    rays_t, sigmas, rgbs, deltas, weights_sum, depth,
-                                                                                   image);
+                                                                                   image); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -172,11 +172,11 @@ int ngp_compact_alive(const int *in, uint32_t n, const int *n_dev, int *out, int
     cudaStream_t st = (cudaStream_t)stream;
     march_ws_t *ws = reinterpret_cast<march_ws_t *>(workspace);
     NGP_CHECK_CUDA(cudaMemsetAsync(ws, 0, 2 * sizeof(uint32_t), st));
-    k_compact_count<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, n_out, ws);
+    { NGP_PROF("k_compact_count", st); k_compact_count<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, n_out, ws); }
     NGP_CHECK_LAUNCH();
-    k_compact_write<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, out, ws);
+    { NGP_PROF("k_compact_write", st); k_compact_write<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, out, ws); }
     NGP_CHECK_LAUNCH();
-    k_compact_publish<<<1, 1, 0, st>>>(ws, n_out);
+    { NGP_PROF("k_compact_publish", st); k_compact_publish<<<1, 1, 0, st>>>(ws, n_out); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

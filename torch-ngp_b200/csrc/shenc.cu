@@ -51,8 +51,8 @@ extern "C" int ngp_sh_encode_forward(const float *inputs, void *outputs, uint32_
     if (B == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;
     switch (dtype) {
-        case NGP_DTYPE_F32: k_sh_encode<float><<<div_round_up(B, 256u), 256, 0, st>>>(inputs, (float *)outputs, B, degree, out_stride); break;
-        case NGP_DTYPE_F16: k_sh_encode<__half><<<div_round_up(B, 256u), 256, 0, st>>>(inputs, (__half *)outputs, B, degree, out_stride); break;
+        case NGP_DTYPE_F32: { NGP_PROF("k_sh_encode", st); k_sh_encode<float><<<div_round_up(B, 256u), 256, 0, st>>>(inputs, (float *)outputs, B, degree, out_stride); } break;
+        case NGP_DTYPE_F16: { NGP_PROF("k_sh_encode", st); k_sh_encode<__half><<<div_round_up(B, 256u), 256, 0, st>>>(inputs, (__half *)outputs, B, degree, out_stride); } break;
         default: set_error("sh_encode_forward: outputs must be float or half (dtype code %d)", dtype); return NGP_EINVAL;
     }
     NGP_CHECK_LAUNCH();

@@ -62,8 +62,8 @@ extern "C" int ngp_umma_selftest(const void *a_img, uint32_t a_bytes, const void
     const size_t smem = ((a_bytes + 1023u) & ~1023u) + ((b_bytes + 1023u) & ~1023u);
     NGP_CHECK_ARG(smem <= 200 * 1024, "umma_selftest: images too large");
     NGP_CHECK_CUDA(cudaFuncSetAttribute(k_umma_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    k_umma_raw<<<1, 128, smem, (cudaStream_t)stream>>>((const uint8_t *)a_img, a_bytes, (const uint8_t *)b_img, b_bytes, D, N, nk, idesc,
-                                                       a_lbo, a_sbo, a_step, b_lbo, b_sbo, b_step);
+    { NGP_PROF("k_umma_raw", (cudaStream_t)stream); k_umma_raw<<<1, 128, smem, (cudaStream_t)stream>>>((const uint8_t *)a_img, a_bytes, (const uint8_t *)b_img, b_bytes, D, N, nk, idesc,
+                                                       a_lbo, a_sbo, a_step, b_lbo, b_sbo, b_step); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

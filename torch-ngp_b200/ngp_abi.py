@@ -25,6 +25,8 @@ SIGNATURES = {
     "ngp_abi_version": (_int, []),
     "ngp_set_option": (_int, [ctypes.c_char_p, _int]),
     "ngp_get_option": (_int, [ctypes.c_char_p, ctypes.POINTER(_int)]),
+    "ngp_launch_count": (ctypes.c_longlong, []),
+    "ngp_profile_collect": (_int, [ctypes.c_char_p, _sz]),
     "ngp_grid_encode_forward": (_int, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _u32, _int, _u32, _int, _int, _vp]),
     "ngp_grid_encode_backward": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _vp, _u32, _int, _u32, _int, _int, _vp]),
     "ngp_grad_total_variation": (_int, [_vp, _vp, _vp, _vp, _f32, _u32, _u32, _u32, _u32, _f32, _u32, _u32, _int, _int, _vp]),
@@ -41,9 +43,9 @@ SIGNATURES = {
     "ngp_composite_rays": (_int, [_u32, _vp, _u32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ngp_compact_alive_workspace_bytes": (_sz, [_u32]),
     "ngp_compact_alive": (_int, [_vp, _u32, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "ngp_ffmlp_forward": (_int, [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
-    "ngp_ffmlp_inference": (_int, [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
-    "ngp_ffmlp_backward": (_int, [_vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp, _vp, _vp, _int, _vp, _sz, _vp]),
+    "ngp_ffmlp_forward": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "ngp_ffmlp_inference": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "ngp_ffmlp_backward": (_int, [_vp, _vp, _vp, _int, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp, _vp, _vp, _int, _vp, _sz, _vp]),
     "ngp_ffmlp_backward_workspace_bytes": (_sz, [_u32, _u32, _u32, _u32]),
     "ngp_allocate_splitk": (_int, [_sz]),
     "ngp_free_splitk": (_int, []),
@@ -85,6 +87,23 @@ def get_option(key):
     v = _int(0)
     check(lib.ngp_get_option(key.encode(), ctypes.byref(v)))
     return v.value
+
+
+def launch_count():
+    return int(lib.ngp_launch_count())
+
+
+def profile_collect():
+    """-> {kernel name: (launch count, total ms)} since the last call (needs option profile_events=1)."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    n = lib.ngp_profile_collect(buf, len(buf))
+    if n < 0:
+        check(n)
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.rsplit(" ", 2)
+        out[name] = (int(cnt), float(ms))
+    return out
 
 
 def stream():
