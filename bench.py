@@ -201,14 +201,19 @@ class HashGridWorkload:
         return None  # counted live
 
     def roofline(self, prof, peaks, steps):
-        """Dominant kernel = the L2-level scatter of the backward (k_grid_bwd_d3c2): its share of the algorithmic bytes."""
-        Lh = self.L - self.n_smem_levels(prof)
-        per_level_bwd = self.B * (self.C * 4 + 8 * self.C * 4) + 0  # grad read + 8 corner RMW targets (counted once, as SURVEY)
-        name = "k_grid_bwd_d3c2"
-        if name not in prof:
+        """Dominant kernel of the step (largest total device time among the grid kernels) against the HBM peak.
+        Algorithmic bytes per launch (element size s=4): forward B*(12 + 8*L*C*s + L*C*s),
+        backward B*(L*C*s + 12 + 8*L*C*s), times the share of the L levels that launch covers."""
+        grid = {k: v for k, v in prof.items() if k.startswith("k_grid_")}
+        if not grid:
             return None
-        cnt, ms = prof[name]
-        alg = Lh * per_level_bwd + self.B * 12
+        name = max(grid, key=lambda k: grid[k][1])
+        cnt, ms = grid[name]
+        share = 1.0
+        if not name.endswith("_lg4"):  # the split variants: shared-memory levels vs L2 levels
+            ns = self.n_smem_levels(prof)
+            share = (ns if name.endswith("_smem") else self.L - ns) / self.L
+        alg = self.B * (12 + 9 * self.L * self.C * 4) * share
         achieved = alg / (ms / cnt * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": None, "peak_source": peaks["source"], "algorithmic_bytes_per_launch": alg, "us_per_launch": ms / cnt * 1e3}

@@ -108,7 +108,8 @@ def test_torch_gradcheck_fp64_reference_config():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
 @pytest.mark.parametrize("layout", [0, 1])
-def test_fast_path_equals_generic(oracle, dtype, layout):
+@pytest.mark.parametrize("variant", [1, 2])
+def test_fast_path_equals_generic(oracle, dtype, layout, variant):
     """D=3,C=2 fast kernels (paired accesses, shared-memory coarse levels) vs the generic kernels."""
     abi = _abi()
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
@@ -124,8 +125,9 @@ def test_fast_path_equals_generic(oracle, dtype, layout):
         e = emb[: int(offs2[-1])].contiguous()
         abi.set_option("hashgrid_fwd_variant", 0)
         ref, _ = _run_fwd(x, e, ot, pls, 16, False, 0, ac, interp, layout)
-        abi.set_option("hashgrid_fwd_variant", -1)
+        abi.set_option("hashgrid_fwd_variant", variant)
         out, _ = _run_fwd(x, e, ot, pls, 16, False, 0, ac, interp, layout)
+        abi.set_option("hashgrid_fwd_variant", -1)
         if dtype == torch.float32:
             assert torch.equal(out, ref)  # same operation order -> bit-identical
         else:
@@ -133,7 +135,7 @@ def test_fast_path_equals_generic(oracle, dtype, layout):
         g = torch.randn_like(ref)
         abi.set_option("hashgrid_bwd_variant", 0)
         ge_ref, _ = _run_bwd(g, x, e, ot, pls, 16, None, 0, ac, interp, layout)
-        abi.set_option("hashgrid_bwd_variant", -1)
+        abi.set_option("hashgrid_bwd_variant", variant)
         for agg in (0, 1):
             abi.set_option("hashgrid_bwd_warp_agg", agg)
             ge, _ = _run_bwd(g, x, e, ot, pls, 16, None, 0, ac, interp, layout)
@@ -144,6 +146,7 @@ def test_fast_path_equals_generic(oracle, dtype, layout):
                 hashed = slice(int(offs2[6]), None)
                 assert torch.allclose(ge[hashed].float(), ge_ref[hashed].float(), rtol=2e-2, atol=2e-2)
         abi.set_option("hashgrid_bwd_warp_agg", 1)
+        abi.set_option("hashgrid_bwd_variant", -1)
 
 
 def test_warp_aggregated_backward_coherent_points(oracle):

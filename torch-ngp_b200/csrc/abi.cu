@@ -24,8 +24,8 @@ void set_error(const char *fmt, ...) {
 static std::mutex g_opt_mu;
 static std::map<std::string, int> &options() {
     static std::map<std::string, int> o = {
-        {"hashgrid_fwd_variant", -1},  // -1 auto, 0 generic, 1 paired-gather fast path
-        {"hashgrid_bwd_variant", -1},  // -1 auto, 0 generic atomics, 1 paired + warp-aggregated
+        {"hashgrid_fwd_variant", -1},  // -1 auto, 0 generic, 1 paired-gather (point,level) threads, 2 sector-gather (point, 4 levels) threads
+        {"hashgrid_bwd_variant", -1},  // -1 auto, 0 generic atomics, 1 paired + warp-aggregated (+ smem levels), 2 (point, 4 levels) threads
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)

@@ -346,5 +346,196 @@ __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict
     }
 }
 
+// ==========================================================================================
+// v2 fast path: one thread = one point x LG consecutive levels.
+//
+// Measured on B200 (profiles/): both directions are bound by L2 *sector transactions* (LTS
+// throughput 73-84 %, DRAM ~10 %), not by bytes -- the 46.7 MiB table lives in L2 and every
+// corner row of a hashed level is a random 32 B sector.  So the kernels minimise transactions:
+//   * the two x-neighbours of a corner row sit in the same 32 B sector 3 times out of 4
+//     (the index differs only in its low bits): one 256-bit load (LDG.E.ENL2.256) fetches the
+//     aligned 4-entry group and the two entries are selected in registers;
+//   * a thread owns LG = 4 levels of its point: the point-major [B, L*C] output / upstream
+//     gradient row segment is one full 32 B sector per thread instead of four partial ones,
+//     the input point is read once, and 16 independent gathers are in flight per thread.
+// ==========================================================================================
+__device__ __forceinline__ bool locate3x(float x0, float x1, float x2, float scale, bool align_corners, uint32_t interp, loc3_t &o) {
+    const float off = align_corners ? 0.0f : 0.5f;
+    float q0 = x0 * scale + off, q1 = x1 * scale + off, q2 = x2 * scale + off;
+    o.p0 = (uint32_t)floorf(q0); o.p1 = (uint32_t)floorf(q1); o.p2 = (uint32_t)floorf(q2);
+    q0 -= (float)o.p0; q1 -= (float)o.p1; q2 -= (float)o.p2;
+    if (interp == 1) { q0 = smoothstep_f(q0); q1 = smoothstep_f(q1); q2 = smoothstep_f(q2); }
+    o.f0 = q0; o.f1 = q1; o.f2 = q2;
+    return true;
+}
+
+__device__ __forceinline__ float2 pick4(const float v[8], uint32_t e) {
+    const bool lo = e & 1u, hi = e & 2u;
+    const float ax = lo ? v[2] : v[0], ay = lo ? v[3] : v[1];
+    const float bx = lo ? v[6] : v[4], by = lo ? v[7] : v[5];
+    return make_float2(hi ? bx : ax, hi ? by : ay);
+}
+
+template <typename T> struct group_io;
+template <> struct group_io<float> {
+    // aligned group of 4 entries (32 B) starting at entry e4 (multiple of 4)
+    static __device__ __forceinline__ void load4(const float *base, uint32_t e4, float v[8]) {
+        asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                     : "l"(base + 2 * (size_t)e4));
+    }
+};
+template <> struct group_io<__half> {
+    static __device__ __forceinline__ void load4(const __half *base, uint32_t e4, float v[8]) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4 *>(base + 2 * (size_t)e4));
+        const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+        const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+    }
+};
+
+template <typename T>
+__device__ __forceinline__ float2 gather8_v2(const T *__restrict__ tab, const rows3_t &r) {
+    float2 v0[4], v1[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if ((r.i0[k] >> 2) == (r.i1[k] >> 2)) {  // same 4-entry group: one sector-wide access
+            float v[8];
+            group_io<T>::load4(tab, r.i0[k] & ~3u, v);
+            v0[k] = pick4(v, r.i0[k] & 3u);
+            v1[k] = pick4(v, r.i1[k] & 3u);
+        } else {
+            v0[k] = entry_io<T>::load1_nc(tab, r.i0[k]);
+            v1[k] = entry_io<T>::load1_nc(tab, r.i1[k]);
+        }
+    }
+    float a = 0, b = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // same accumulation order as gather8 / the generic kernel
+        a += r.w0[k] * v0[k].x; b += r.w0[k] * v0[k].y;
+        a += r.w1[k] * v1[k].x; b += r.w1[k] * v1[k].y;
+    }
+    return make_float2(a, b);
+}
+
+__device__ __forceinline__ void store_row4(float *p, const float2 r[4]) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r[0].x), "f"(r[0].y), "f"(r[1].x), "f"(r[1].y),
+                 "f"(r[2].x), "f"(r[2].y), "f"(r[3].x), "f"(r[3].y)
+                 : "memory");
+}
+__device__ __forceinline__ void store_row4(__half *p, const float2 r[4]) {
+    uint4 u;
+    u.x = pack_h2(r[0].x, r[0].y); u.y = pack_h2(r[1].x, r[1].y); u.z = pack_h2(r[2].x, r[2].y); u.w = pack_h2(r[3].x, r[3].y);
+    *reinterpret_cast<uint4 *>(p) = u;
+}
+__device__ __forceinline__ void load_row4(const float *p, float2 r[4]) {
+    float v[8];
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) r[k] = make_float2(v[2 * k], v[2 * k + 1]);
+}
+__device__ __forceinline__ void load_row4(const __half *p, float2 r[4]) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4 *>(p));
+    r[0] = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)); r[1] = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+    r[2] = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)); r[3] = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+}
+
+// forward: grid = (ceil(B/256), L/4); L % 4 == 0, table base 32 B aligned (host-checked)
+template <typename T>
+__global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restrict__ inputs, const T *__restrict__ grid,
+                                                           const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B,
+                                                           uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
+                                                           uint32_t interp, int layout) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint32_t l0 = blockIdx.y * 4;
+    const float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
+    const bool oob = (x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
+    float2 res[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        res[k] = make_float2(0.f, 0.f);
+        if (oob) continue;
+        const level_t lv = level_consts(offsets, l0 + k, S, H);
+        const geo3_t g = make_geo3(lv, gridtype, align_corners);
+        loc3_t o;
+        locate3x(x0, x1, x2, lv.scale, align_corners, interp, o);
+        rows3_t r;
+        make_rows3(g, o, r);
+        res[k] = gather8_v2<T>(grid + (size_t)lv.offset * 2, r);
+    }
+    if (layout == NGP_LAYOUT_BLC) {
+        store_row4(outputs + ((size_t)b * L + l0) * 2, res);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) entry_io<T>::store1(outputs + ((size_t)(l0 + k) * B + b) * 2, res[k].x, res[k].y);
+    }
+}
+
+// backward: same mapping; x-neighbours sharing an aligned pair go out as one 16 B (f32) / 8 B (f16) reduction
+template <typename T>
+__global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__ grad, const float *__restrict__ inputs,
+                                                           const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B,
+                                                           uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
+                                                           uint32_t interp, int layout, int warp_agg) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t l0 = blockIdx.y * 4;
+    float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+    if (b < B) { x0 = inputs[3 * (size_t)b]; x1 = inputs[3 * (size_t)b + 1]; x2 = inputs[3 * (size_t)b + 2]; }
+    const bool valid = (b < B) && !(x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
+    if (__ballot_sync(0xffffffffu, valid) == 0) return;
+    float2 gv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) gv[k] = make_float2(0.f, 0.f);
+    if (valid) {
+        if (layout == NGP_LAYOUT_BLC) {
+            load_row4(grad + ((size_t)b * L + l0) * 2, gv);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * B + b) * 2);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const level_t lv = level_consts(offsets, l0 + k, S, H);
+        const geo3_t g = make_geo3(lv, gridtype, align_corners);
+        T *tab = grad_grid + (size_t)lv.offset * 2;
+        loc3_t o;
+        rows3_t r;
+        unsigned long long key = ~0ull - threadIdx.x;
+        if (valid) {
+            locate3x(x0, x1, x2, lv.scale, align_corners, interp, o);
+            make_rows3(g, o, r);
+            key = (unsigned long long)o.p0 | ((unsigned long long)o.p1 << 21) | ((unsigned long long)o.p2 << 42);
+        }
+        int uniform = 0;
+        if (warp_agg) __match_all_sync(0xffffffffu, key, &uniform);
+        if (uniform) {  // whole warp in one cell (coherent samples on coarse levels): reduce first
+            float s[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                s[4 * q + 0] = warp_sum(r.w0[q] * gv[k].x); s[4 * q + 1] = warp_sum(r.w0[q] * gv[k].y);
+                s[4 * q + 2] = warp_sum(r.w1[q] * gv[k].x); s[4 * q + 3] = warp_sum(r.w1[q] * gv[k].y);
+            }
+            if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if ((r.i0[q] ^ r.i1[q]) == 1u) {
+                        if (r.i0[q] & 1u) entry_io<T>::red2(tab, r.i1[q], s[4 * q + 2], s[4 * q + 3], s[4 * q + 0], s[4 * q + 1]);
+                        else entry_io<T>::red2(tab, r.i0[q], s[4 * q + 0], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                    } else {
+                        entry_io<T>::red1(tab, r.i0[q], s[4 * q + 0], s[4 * q + 1]);
+                        entry_io<T>::red1(tab, r.i1[q], s[4 * q + 2], s[4 * q + 3]);
+                    }
+                }
+            }
+        } else if (valid) {
+            scatter8<T>(tab, r, gv[k].x, gv[k].y);
+        }
+    }
+}
+
 }  // namespace
 }  // namespace ngp

@@ -94,6 +94,12 @@ uint32_t plan_smem_levels(const int *offsets_host, uint32_t L, uint32_t B, size_
 template <typename T>
 int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *offsets_host, T *out, uint32_t B, uint32_t L,
              float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+    const int variant = get_option("hashgrid_fwd_variant", -1);
+    if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
+        { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout); }
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     size_t smem = 0;
     const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(T), &smem);
     if (ns > 0) {
@@ -121,6 +127,13 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
 template <typename T>
 int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *offsets_host, T *g_emb, uint32_t B, uint32_t L,
              float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+    const int variant = get_option("hashgrid_bwd_variant", -1);
+    if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
+        const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
+        { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg); }
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     size_t smem = 0;
     const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(float), &smem);  // fp32 accumulators
     if (ns > 0) {
