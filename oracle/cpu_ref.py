@@ -285,11 +285,15 @@ def ffmlp_forward(inputs, weights, input_dim, output_dim_padded, hidden_dim, num
     return x, acts
 
 
-def ffmlp_backward(grad, inputs, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype=np.float64):
-    """-> (grad_inputs [B,in], grad_weights flat), matching ffmlp.cu:749-895's results."""
+def ffmlp_backward(grad, inputs, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype=np.float64,
+                   round_activations_fp16=False):
+    """-> (grad_inputs [B,in], grad_weights flat), matching ffmlp.cu:749-895's results.
+    round_activations_fp16: the saved activations (and so the ReLU masks, ffmlp.cu:105-108) are the fp16-rounded ones,
+    as both the reference and the tcgen05 kernels store them -- a pre-activation within rounding distance of zero
+    otherwise flips a mask and changes that unit's whole gradient contribution."""
     x = np.asarray(inputs, dtype=dtype)
     ws = ffmlp_split_weights(np.asarray(weights, dtype=dtype), input_dim, output_dim_padded, hidden_dim, num_layers)
-    _, acts = ffmlp_forward(x, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype)
+    _, acts = ffmlp_forward(x, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype, round_activations_fp16)
     g = np.asarray(grad, dtype=dtype)
     gws = [None] * len(ws)
     for i in range(num_layers, -1, -1):

@@ -30,7 +30,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_block", 128},
-        {"ffmlp_available", 0},
+        {"ffmlp_available", 1},
         {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in
     };
     return o;

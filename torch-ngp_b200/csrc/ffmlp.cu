@@ -1,12 +1,590 @@
-// ffmlp.cu -- placeholder until the tcgen05 fused MLP lands; fails loudly.
+// ffmlp.cu -- fully-fused small MLP on tcgen05 tensor cores (sm_100a).
+//
+// Contract: /root/reference/ffmlp/src/ffmlp.cu (kernel_mlp_fused :331-407, kernel_mlp_fused_backward :410-518,
+// host ffmlp_forward :635-671, ffmlp_inference :673-709, ffmlp_backward :749-895) behind the C ABI of
+// include/ngp_b200.h:  h = ReLU(W_0 x), h = ReLU(W_k h) x (num_layers-1), y = W_last h, no biases, fp16 storage.
+//
+// Design (not a translation of the reference's wmma register-fragment kernel):
+//   * one CTA = 128 threads = one 128-row batch tile at a time, persistent over tiles; thread t owns row t
+//     (= TMEM lane t) in every epilogue;
+//   * every weight matrix is staged ONCE per CTA into shared memory as 128B-swizzled UMMA tiles
+//     (fp32 parameters are rounded to fp16 on the way in: no per-call cast kernel);
+//   * each layer is a few tcgen05.mma (M=128, N=width, K=16) issued by one thread, accumulating in fp32 in
+//     TMEM; the epilogue (tcgen05.ld -> ReLU -> fp16) writes the next layer's A operand straight back into a
+//     swizzled shared-memory tile -- activations never touch HBM (the reference streams
+//     [num_layers, B, hidden] out in training mode and reads it back in the backward);
+//   * the backward recomputes the forward per tile, keeps every activation / gradient tile in shared
+//     memory, runs dL/dx through MN-major views of the SAME weight images, and accumulates all weight
+//     gradients dW_m += G_m^T H_{m-1} in TMEM across the CTA's tiles (fp32, K = whole batch share), flushed
+//     once per CTA with vector reductions; the last CTA converts the fp32 sum to the requested dtype.
+//   * input / upstream-gradient tiles are prefetched one tile ahead with cp.async (zero-filled ragged tail).
 #include "common.cuh"
-extern "C" {
-int ngp_ffmlp_forward(const void *, const void *, int, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, void *, void *, void *) {
-    ngp::set_error("ffmlp_forward: not implemented yet"); return NGP_EUNSUPPORTED; }
-int ngp_ffmlp_inference(const void *, const void *, int, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, void *, void *, void *) {
-    ngp::set_error("ffmlp_inference: not implemented yet"); return NGP_EUNSUPPORTED; }
-int ngp_ffmlp_backward(const void *, const void *, const void *, int, const void *, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, int,
-                       void *, void *, void *, int, void *, size_t, void *) {
-    ngp::set_error("ffmlp_backward: not implemented yet"); return NGP_EUNSUPPORTED; }
-size_t ngp_ffmlp_backward_workspace_bytes(uint32_t, uint32_t, uint32_t, uint32_t) { return 0; }
+#include "umma.cuh"
+
+namespace ngp {
+namespace {
+
+using namespace umma;
+
+constexpr uint32_t kTileRows = 128;
+constexpr uint32_t kActTileBytes = kTileRows * kTileRowBytes;  // 16 KB: 128 rows x 64 halves
+constexpr uint32_t kMaxLayers = 8;                             // num_layers <= 8 (num_layers + 1 matrices)
+
+__host__ __device__ inline uint32_t ktiles(uint32_t k) { return (k + 63u) / 64u; }
+
+struct mlp_t {
+    uint32_t B, in, out, hid, nl;
+    // weight matrix m (0..nl): rows[m] x K[m], flat offset woff[m] (elements), smem offset soff[m] (bytes)
+    uint32_t rows[kMaxLayers + 1], K[kMaxLayers + 1], woff[kMaxLayers + 1], soff[kMaxLayers + 1];
+    uint32_t wbytes, nweights;
+};
+
+inline void make_mlp(mlp_t &m, uint32_t B, uint32_t in, uint32_t out, uint32_t hid, uint32_t nl) {
+    m.B = B; m.in = in; m.out = out; m.hid = hid; m.nl = nl;
+    uint32_t w = 0, s = 0;
+    for (uint32_t i = 0; i <= nl; ++i) {
+        m.rows[i] = (i == nl) ? out : hid;
+        m.K[i] = (i == 0) ? in : hid;
+        m.woff[i] = w;
+        m.soff[i] = s;
+        w += m.rows[i] * m.K[i];
+        s += ktiles(m.K[i]) * m.rows[i] * kTileRowBytes;
+    }
+    m.nweights = w;
+    m.wbytes = (s + 1023u) & ~1023u;
 }
+
+// ---- staging ---------------------------------------------------------------------------------------
+// all weight matrices -> swizzled K-major tiles ([rows x 64 halves] per 64 input columns)
+template <typename WT>
+__device__ __forceinline__ void stage_weights(uint8_t *sw, const WT *__restrict__ w, const mlp_t &m, uint32_t tid, uint32_t nth) {
+    for (uint32_t i = 0; i <= m.nl; ++i) {
+        const uint32_t rows = m.rows[i], K = m.K[i], cpr = K >> 3;
+        const WT *src = w + m.woff[i];
+        uint8_t *dst = sw + m.soff[i];
+        for (uint32_t q = tid; q < rows * cpr; q += nth) {
+            const uint32_t r = q / cpr, c8 = q - r * cpr;
+            uint4 v;
+            if constexpr (sizeof(WT) == 2) {
+                v = __ldg(reinterpret_cast<const uint4 *>(src + (size_t)r * K) + c8);
+            } else {
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(src + (size_t)r * K) + 2 * c8);
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(src + (size_t)r * K) + 2 * c8 + 1);
+                const __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
+                const __half2 h2 = __floats2half2_rn(b.x, b.y), h3 = __floats2half2_rn(b.z, b.w);
+                v.x = *reinterpret_cast<const uint32_t *>(&h0); v.y = *reinterpret_cast<const uint32_t *>(&h1);
+                v.z = *reinterpret_cast<const uint32_t *>(&h2); v.w = *reinterpret_cast<const uint32_t *>(&h3);
+            }
+            *reinterpret_cast<uint4 *>(dst + (c8 >> 3) * rows * kTileRowBytes + swz_off(r, c8 & 7u)) = v;
+        }
+    }
+}
+
+// rows [row0, row0+128) of a row-major fp16 [B x cols] matrix -> swizzled activation tiles, asynchronously;
+// rows >= B are zero-filled (cp.async src-size 0)
+__device__ __forceinline__ void load_rows_async(uint8_t *tiles, const __half *__restrict__ g, uint32_t row0, uint32_t B, uint32_t cols,
+                                                uint32_t tid, uint32_t nth) {
+    const uint32_t cpr = cols >> 3;
+    for (uint32_t q = tid; q < kTileRows * cpr; q += nth) {
+        const uint32_t r = q / cpr, c8 = q - r * cpr;
+        const uint32_t grow = row0 + r;
+        const bool ok = grow < B;
+        const __half *src = g + (size_t)(ok ? grow : 0u) * cols + c8 * 8;
+        const uint32_t dst = smem_u32(tiles + (c8 >> 3) * kActTileBytes + swz_off(r, c8 & 7u));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16u : 0u) : "memory");
+    }
+}
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+
+// ---- epilogues (thread = row = TMEM lane) --------------------------------------------------------------
+// acc[row, 0..n) -> ReLU -> fp16 -> swizzled tile(s)
+__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t n) {
+    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
+        float v[16];
+        tmem_ld16(taddr + c0, v);
+        uint4 lo, hi;
+        lo.x = pack2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)); lo.y = pack2(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
+        lo.z = pack2(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)); lo.w = pack2(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
+        hi.x = pack2(fmaxf(v[8], 0.f), fmaxf(v[9], 0.f)); hi.y = pack2(fmaxf(v[10], 0.f), fmaxf(v[11], 0.f));
+        hi.z = pack2(fmaxf(v[12], 0.f), fmaxf(v[13], 0.f)); hi.w = pack2(fmaxf(v[14], 0.f), fmaxf(v[15], 0.f));
+        const uint32_t c8 = c0 >> 3;
+        uint8_t *t = tiles + (c8 >> 3) * kActTileBytes;
+        *reinterpret_cast<uint4 *>(t + swz_off(row, c8 & 7u)) = lo;
+        *reinterpret_cast<uint4 *>(t + swz_off(row, (c8 + 1) & 7u)) = hi;
+    }
+}
+
+__device__ __forceinline__ uint32_t mask2(float a, float b, uint32_t h2) {
+    const __half2 h = *reinterpret_cast<const __half2 *>(&h2);
+    const float2 f = __half22float2(h);
+    return pack2(f.x > 0.f ? a : 0.f, f.y > 0.f ? b : 0.f);
+}
+// acc[row, 0..n) * (act[row, :] > 0) -> fp16 -> swizzled tile(s)   (ReLU backward from the saved activation)
+__device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t n) {
+    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
+        float v[16];
+        tmem_ld16(taddr + c0, v);
+        const uint32_t c8 = c0 >> 3;
+        const uint32_t o0 = (c8 >> 3) * kActTileBytes + swz_off(row, c8 & 7u), o1 = (c8 >> 3) * kActTileBytes + swz_off(row, (c8 + 1) & 7u);
+        const uint4 a0 = *reinterpret_cast<const uint4 *>(act_tiles + o0), a1 = *reinterpret_cast<const uint4 *>(act_tiles + o1);
+        uint4 lo, hi;
+        lo.x = mask2(v[0], v[1], a0.x); lo.y = mask2(v[2], v[3], a0.y); lo.z = mask2(v[4], v[5], a0.z); lo.w = mask2(v[6], v[7], a0.w);
+        hi.x = mask2(v[8], v[9], a1.x); hi.y = mask2(v[10], v[11], a1.y); hi.z = mask2(v[12], v[13], a1.z); hi.w = mask2(v[14], v[15], a1.w);
+        *reinterpret_cast<uint4 *>(tiles + o0) = lo;
+        *reinterpret_cast<uint4 *>(tiles + o1) = hi;
+    }
+}
+// acc[row, 0..n) -> fp16 -> global row (n % 16 == 0; 32 B per 16 columns, consecutive rows are contiguous)
+__device__ __forceinline__ void epi_to_global(uint32_t taddr, __half *__restrict__ dst_row, uint32_t n, bool write) {
+    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
+        float v[16];
+        tmem_ld16(taddr + c0, v);
+        if (write) {
+            uint4 lo, hi;
+            lo.x = pack2(v[0], v[1]); lo.y = pack2(v[2], v[3]); lo.z = pack2(v[4], v[5]); lo.w = pack2(v[6], v[7]);
+            hi.x = pack2(v[8], v[9]); hi.y = pack2(v[10], v[11]); hi.z = pack2(v[12], v[13]); hi.w = pack2(v[14], v[15]);
+            reinterpret_cast<uint4 *>(dst_row + c0)[0] = lo;
+            reinterpret_cast<uint4 *>(dst_row + c0)[1] = hi;
+        }
+    }
+}
+
+// ---- MMA issue helpers (one thread) ----------------------------------------------------------------------
+// D[128 x N] = A[128 x K] (K-major activation tiles) * W^T, W = weight matrix image with N rows (K-major B)
+__device__ __forceinline__ void issue_fwd(uint32_t d_tmem, const uint8_t *a_tiles, const uint8_t *w_img, uint32_t N, uint32_t K) {
+    issue_kmajor(d_tmem, smem_u32(a_tiles), kActTileBytes, smem_u32(w_img), N * kTileRowBytes, N, K, 0);
+}
+// D[128 x N] = G[128 x K] (K-major tiles) * W, W = weight image [K rows x N cols] read as an MN-major B operand
+// (N <= 64: one slab; N = 128: two slabs, LBO = slab stride = K * 128 bytes)
+__device__ __forceinline__ void issue_bwd_dx(uint32_t d_tmem, const uint8_t *g_tiles, const uint8_t *w_img, uint32_t N, uint32_t K) {
+    const uint32_t idesc = make_idesc(128, N, false, true);
+    const uint32_t a_base = smem_u32(g_tiles), b_base = smem_u32(w_img);
+    const uint32_t b_lbo = N > 64 ? K * kTileRowBytes : 0u;
+    for (uint32_t k16 = 0; k16 < K / 16; ++k16) {
+        const uint64_t ad = make_desc(a_base + (k16 >> 2) * kActTileBytes + (k16 & 3u) * 32u, 0, kAtomBytes);
+        const uint64_t bd = make_desc(b_base + k16 * 2048u, b_lbo, kAtomBytes);
+        mma_f16(d_tmem, ad, bd, idesc, k16 > 0 ? 1u : 0u);
+    }
+}
+// D[M x N] (+)= G^T H over the tile's 128 rows: G tiles [128 x M] as MN-major A (M <= 64: the second 64-wide
+// slab aliases the first, rows >= 64 of D are duplicates and ignored), H tiles [128 x N] as MN-major B
+__device__ __forceinline__ void issue_dw(uint32_t d_tmem, const uint8_t *g_tiles, const uint8_t *h_tiles, uint32_t M, uint32_t N, uint32_t acc) {
+    const uint32_t idesc = make_idesc(128, N, true, true);
+    const uint32_t a_base = smem_u32(g_tiles), b_base = smem_u32(h_tiles);
+    const uint32_t a_lbo = M > 64 ? kActTileBytes : 0u, b_lbo = N > 64 ? kActTileBytes : 0u;
+    for (uint32_t k16 = 0; k16 < kTileRows / 16; ++k16) {
+        const uint64_t ad = make_desc(a_base + k16 * 2048u, a_lbo, kAtomBytes);
+        const uint64_t bd = make_desc(b_base + k16 * 2048u, b_lbo, kAtomBytes);
+        mma_f16(d_tmem, ad, bd, idesc, (k16 > 0 || acc) ? 1u : 0u);
+    }
+}
+
+__host__ __device__ inline uint32_t tmem_cols_pow2(uint32_t n) {
+    uint32_t c = 32;
+    while (c < n) c <<= 1;
+    return c;
+}
+
+// ==========================================================================================================
+// forward / inference
+// ==========================================================================================================
+template <typename WT>
+__global__ void __launch_bounds__(128) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
+                                                   const mlp_t m, uint32_t ntiles, uint32_t tmem_cols) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes;
+    uint8_t *sw = smem;
+    uint8_t *sx[2] = {smem + m.wbytes, smem + m.wbytes + xbytes};
+    uint8_t *sa = smem + m.wbytes + 2 * xbytes;
+    (void)abytes;
+
+    uint32_t tile = blockIdx.x;
+    if (tile < ntiles) load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
+    cp_async_commit();
+    stage_weights<WT>(sw, w, m, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_init_fence();
+    }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    const uint32_t trow = tmem + ((warp * 32u) << 16);  // this warp's 32 TMEM lanes
+    uint32_t phase = 0, buf = 0;
+
+    for (; tile < ntiles; tile += gridDim.x, buf ^= 1u) {
+        const uint32_t next = tile + gridDim.x;
+        if (next < ntiles) load_rows_async(sx[buf ^ 1u], x, next * kTileRows, m.B, m.in, tid, blockDim.x);
+        cp_async_commit();
+        cp_async_wait<1>();  // this tile's rows have landed
+        fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            fence_after_sync();
+            issue_fwd(tmem, sx[buf], sw + m.soff[0], m.hid, m.in);
+            mma_commit(&s_bar);
+        }
+        for (uint32_t l = 0; l < m.nl; ++l) {
+            mbar_wait(&s_bar, phase);
+            phase ^= 1u;
+            fence_after_sync();
+            epi_relu_to_tile(trow, sa, tid, m.hid);
+            fence_proxy_async();
+            fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                fence_after_sync();
+                issue_fwd(tmem, sa, sw + m.soff[l + 1], m.rows[l + 1], m.hid);
+                mma_commit(&s_bar);
+            }
+        }
+        mbar_wait(&s_bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        const uint32_t grow = tile * kTileRows + tid;
+        epi_to_global(trow, y + (size_t)grow * m.out, m.out, grow < m.B);
+        fence_before_sync();
+        __syncthreads();  // accumulator drained before the next tile's first MMA overwrites it
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+}
+
+// ==========================================================================================================
+// backward (recomputes the forward per tile; dW accumulated in TMEM across the CTA's tiles)
+// ==========================================================================================================
+struct bwd_cols_t {
+    uint32_t acc, dw[kMaxLayers + 1], total;
+};
+__host__ __device__ inline void make_bwd_cols(const mlp_t &m, bool calc_dx, bwd_cols_t &c) {
+    uint32_t a = m.hid;
+    if (calc_dx && m.in > a) a = m.in;
+    a = (a + 31u) & ~31u;
+    c.acc = 0;
+    uint32_t o = a;
+    for (uint32_t i = 0; i <= m.nl; ++i) {
+        c.dw[i] = o;
+        o += (m.K[i] + 31u) & ~31u;
+    }
+    c.total = o;
+}
+
+template <typename WT>
+__global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
+                                                   __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
+                                                   int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
+                                                   uint32_t nbuf) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ uint32_t s_last;
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes, obytes = ktiles(m.out) * kActTileBytes;
+    uint8_t *sw = smem;
+    uint8_t *p = smem + m.wbytes;
+    // nbuf == 2: input / upstream-gradient tiles are prefetched one tile ahead; nbuf == 1 (wide layers that
+    // would not fit otherwise): loaded at the top of each tile
+    uint8_t *sx[2] = {p, p + (nbuf - 1) * xbytes};
+    p += nbuf * xbytes;
+    uint8_t *sgo[2] = {p, p + (nbuf - 1) * obytes};
+    p += nbuf * obytes;
+    uint8_t *sg[2] = {p, p + abytes};
+    p += 2 * abytes;
+    uint8_t *sh = p;  // nl activation tile sets
+    bwd_cols_t tc;
+    make_bwd_cols(m, calc_dx != 0, tc);
+
+    uint32_t tile = blockIdx.x;
+    if (tile < ntiles && nbuf == 2) {
+        load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
+        load_rows_async(sgo[0], grad, tile * kTileRows, m.B, m.out, tid, blockDim.x);
+    }
+    cp_async_commit();
+    stage_weights<WT>(sw, w, m, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_init_fence();
+    }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    const uint32_t trow = tmem + ((warp * 32u) << 16);
+    uint32_t phase = 0, buf = 0, first = 1;
+
+    for (; tile < ntiles; tile += gridDim.x, buf ^= (nbuf - 1u)) {
+        if (nbuf == 2) {
+            const uint32_t next = tile + gridDim.x;
+            if (next < ntiles) {
+                load_rows_async(sx[buf ^ 1u], x, next * kTileRows, m.B, m.in, tid, blockDim.x);
+                load_rows_async(sgo[buf ^ 1u], grad, next * kTileRows, m.B, m.out, tid, blockDim.x);
+            }
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
+            load_rows_async(sgo[0], grad, tile * kTileRows, m.B, m.out, tid, blockDim.x);
+            cp_async_commit();
+            cp_async_wait<0>();
+        }
+        fence_proxy_async();
+        __syncthreads();
+        // ---- forward recompute: H_l = ReLU(W_l H_{l-1}) kept in shared memory ----
+        if (tid == 0) {
+            fence_after_sync();
+            issue_fwd(tmem + tc.acc, sx[buf], sw + m.soff[0], m.hid, m.in);
+            mma_commit(&s_bar);
+        }
+        for (uint32_t l = 0; l < m.nl; ++l) {
+            mbar_wait(&s_bar, phase);
+            phase ^= 1u;
+            fence_after_sync();
+            epi_relu_to_tile(trow + tc.acc, sh + l * abytes, tid, m.hid);
+            fence_proxy_async();
+            fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                fence_after_sync();
+                if (l + 1 < m.nl) {
+                    issue_fwd(tmem + tc.acc, sh + l * abytes, sw + m.soff[l + 1], m.hid, m.hid);
+                } else {  // start of the backward: dH_{nl-1} = dY W_last ; dW_last += dY^T H_{nl-1}
+                    issue_bwd_dx(tmem + tc.acc, sgo[buf], sw + m.soff[m.nl], m.hid, m.out);
+                }
+                mma_commit(&s_bar);
+                if (l + 1 == m.nl) issue_dw(tmem + tc.dw[m.nl], sgo[buf], sh + l * abytes, m.out, m.hid, first ? 0u : 1u);
+            }
+        }
+        // ---- backward through the hidden layers ----
+        for (int l = (int)m.nl - 1; l >= 0; --l) {
+            uint8_t *g = sg[l & 1];
+            mbar_wait(&s_bar, phase);
+            phase ^= 1u;
+            fence_after_sync();
+            epi_mask_to_tile(trow + tc.acc, sh + (uint32_t)l * abytes, g, tid, m.hid);  // G_l = dH_l * (H_l > 0)
+            fence_proxy_async();
+            fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                fence_after_sync();
+                if (l > 0) {
+                    issue_bwd_dx(tmem + tc.acc, g, sw + m.soff[l], m.hid, m.hid);  // dH_{l-1} = G_l W_l
+                    mma_commit(&s_bar);
+                    issue_dw(tmem + tc.dw[l], g, sh + (uint32_t)(l - 1) * abytes, m.hid, m.hid, first ? 0u : 1u);
+                } else {
+                    if (calc_dx) issue_bwd_dx(tmem + tc.acc, g, sw + m.soff[0], m.in, m.hid);  // dX = G_0 W_0
+                    issue_dw(tmem + tc.dw[0], g, sx[buf], m.hid, m.in, first ? 0u : 1u);
+                    mma_commit(&s_bar);
+                }
+            }
+        }
+        mbar_wait(&s_bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        if (calc_dx) {
+            const uint32_t grow = tile * kTileRows + tid;
+            epi_to_global(trow + tc.acc, grad_x + (size_t)grow * m.in, m.in, grow < m.B);
+        }
+        fence_before_sync();
+        __syncthreads();
+        first = 0;
+    }
+    cp_async_wait<0>();
+
+    // ---- flush this CTA's dW accumulators: TMEM lane = output row of the matrix ----
+    if (!first) {
+        for (uint32_t i = 0; i <= m.nl; ++i) {
+            const uint32_t rows = m.rows[i], K = m.K[i];
+            for (uint32_t c0 = 0; c0 < K; c0 += 16) {  // warp-uniform trip count: tcgen05.ld is .sync.aligned
+                float v[16];
+                tmem_ld16(trow + tc.dw[i] + c0, v);
+                if (tid < rows) {
+                    float *d = ws + m.woff[i] + (size_t)tid * K + c0;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4)
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3]) : "memory");
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __threadfence();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+    // ---- last CTA: fp32 sum -> grad_weights (requested dtype); leave the workspace zeroed for the next call ----
+    uint32_t *counter = reinterpret_cast<uint32_t *>(ws + ((m.nweights + 3u) & ~3u));
+    if (tid == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (uint32_t i = tid; i < m.nweights; i += blockDim.x) {
+        const float v = __ldcg(ws + i);
+        if (grad_w_f32) reinterpret_cast<float *>(grad_w)[i] = v;
+        else reinterpret_cast<__half *>(grad_w)[i] = __float2half_rn(v);
+        ws[i] = 0.f;
+    }
+    if (tid == 0) *counter = 0u;
+}
+
+}  // namespace
+}  // namespace ngp
+
+// ==========================================================================================================
+// host side
+// ==========================================================================================================
+namespace ngp {
+namespace {
+
+constexpr size_t kMaxSmem = 227 * 1024;
+
+int check_dims(const char *fn, uint32_t in, uint32_t out, uint32_t hid, uint32_t nl, uint32_t act, uint32_t out_act, int wdtype) {
+    if (!(hid == 16 || hid == 32 || hid == 64 || hid == 128)) {
+        if (hid == 256) { set_error("%s: hidden_dim 256 is not supported by the tcgen05 kernels yet (16/32/64/128 are)", fn); return NGP_EUNSUPPORTED; }
+        set_error("hidden_dim should in [16, 32, 64, 128, 256]");
+        return NGP_EINVAL;
+    }
+    NGP_CHECK_ARG(in > 0 && in % 16 == 0 && in <= 128, "%s: input_dim should be 16 * m, 0 < m <= 8, but got %u", fn, in);
+    NGP_CHECK_ARG(out > 0 && out % 16 == 0 && out <= 128, "%s: (padded) output_dim should be 16 * m, 0 < m <= 8, but got %u", fn, out);
+    NGP_CHECK_ARG(nl >= 2 && nl <= kMaxLayers, "%s: num_layers should be in [2, %u], but got %u", fn, kMaxLayers, nl);
+    NGP_CHECK_ARG(wdtype == NGP_DTYPE_F16 || wdtype == NGP_DTYPE_F32, "%s: weights must be a half or float tensor", fn);
+    if (act != 0 || out_act != 6) {
+        set_error("%s: only activation=ReLU (0) with output_activation=None (6) is implemented (got %u, %u)", fn, act, out_act);
+        return NGP_EUNSUPPORTED;
+    }
+    return NGP_OK;
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    NGP_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return NGP_OK;
+}
+
+int run_forward(const char *fn, const void *inputs, const void *weights, int wdtype, uint32_t B, uint32_t in, uint32_t out, uint32_t hid,
+                uint32_t nl, uint32_t act, uint32_t out_act, void *outputs, void *stream) {
+    if (B == 0) return NGP_OK;
+    NGP_CHECK_ARG(inputs && weights && outputs, "%s: null pointer argument", fn);
+    int rc = check_dims(fn, in, out, hid, nl, act, out_act, wdtype);
+    if (rc != NGP_OK) return rc;
+    mlp_t m;
+    make_mlp(m, B, in, out, hid, nl);
+    const size_t smem = m.wbytes + 2 * (size_t)ktiles(in) * kActTileBytes + (size_t)ktiles(hid) * kActTileBytes;
+    if (smem + 1024 > kMaxSmem) { set_error("%s: configuration needs %zu bytes of shared memory (> %zu)", fn, smem, kMaxSmem); return NGP_EUNSUPPORTED; }
+    const uint32_t cols = tmem_cols_pow2(hid > out ? hid : out);
+    const uint32_t ntiles = div_round_up(B, kTileRows);
+    uint32_t per_sm = (uint32_t)(kMaxSmem / (smem + 1024));
+    if (per_sm > 512 / cols) per_sm = 512 / cols;
+    if (per_sm > 8) per_sm = 8;
+    if (per_sm < 1) per_sm = 1;
+    uint32_t grid = (uint32_t)sm_count() * per_sm;
+    if (grid > ntiles) grid = ntiles;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (wdtype == NGP_DTYPE_F16) {
+        rc = set_smem(k_ffmlp_fwd<__half>, smem);
+        if (rc != NGP_OK) return rc;
+        { NGP_PROF("k_ffmlp_fwd", st); k_ffmlp_fwd<__half><<<grid, 128, smem, st>>>((const __half *)inputs, (const __half *)weights, (__half *)outputs, m, ntiles, cols); }
+    } else {
+        rc = set_smem(k_ffmlp_fwd<float>, smem);
+        if (rc != NGP_OK) return rc;
+        { NGP_PROF("k_ffmlp_fwd", st); k_ffmlp_fwd<float><<<grid, 128, smem, st>>>((const __half *)inputs, (const float *)weights, (__half *)outputs, m, ntiles, cols); }
+    }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
+}  // namespace
+}  // namespace ngp
+
+extern "C" {
+
+int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim, uint32_t output_dim,
+                      uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation, void *forward_buffer,
+                      void *outputs, void *stream) {
+    (void)forward_buffer;  // never written: the backward recomputes the activations
+    return ngp::run_forward("ffmlp_forward", inputs, weights, weights_dtype, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                            output_activation, outputs, stream);
+}
+
+int ngp_ffmlp_inference(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim, uint32_t output_dim,
+                        uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation, void *inference_buffer,
+                        void *outputs, void *stream) {
+    (void)inference_buffer;
+    return ngp::run_forward("ffmlp_inference", inputs, weights, weights_dtype, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                            output_activation, outputs, stream);
+}
+
+size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers) {
+    const size_t nw = (size_t)hidden_dim * (input_dim + (size_t)hidden_dim * (num_layers - 1) + output_dim);
+    return (((nw + 3) & ~(size_t)3) + 4) * sizeof(float);
+}
+
+int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, int weights_dtype, const void *forward_buffer, uint32_t B,
+                       uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                       uint32_t output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs, void *grad_weights,
+                       int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream) {
+    using namespace ngp;
+    (void)forward_buffer;
+    (void)backward_buffer;
+    const char *fn = "ffmlp_backward";
+    NGP_CHECK_ARG(grad_weights, "%s: null pointer argument", fn);
+    NGP_CHECK_ARG(grad_weights_dtype == NGP_DTYPE_F16 || grad_weights_dtype == NGP_DTYPE_F32, "%s: grad_weights must be a half or float tensor", fn);
+    int rc = check_dims(fn, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, weights_dtype);
+    if (rc != NGP_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    mlp_t m;
+    make_mlp(m, B, input_dim, output_dim, hidden_dim, num_layers);
+    if (B == 0) {  // empty batch: zero gradient
+        NGP_CHECK_CUDA(cudaMemsetAsync(grad_weights, 0, (size_t)m.nweights * (grad_weights_dtype == NGP_DTYPE_F32 ? 4 : 2), st));
+        return NGP_OK;
+    }
+    NGP_CHECK_ARG(grad && inputs && weights && workspace, "%s: null pointer argument", fn);
+    NGP_CHECK_ARG(!calc_grad_inputs || grad_inputs, "%s: calc_grad_inputs needs grad_inputs", fn);
+    NGP_CHECK_ARG(workspace_bytes >= ngp_ffmlp_backward_workspace_bytes(input_dim, output_dim, hidden_dim, num_layers),
+                  "%s: workspace too small (%zu bytes)", fn, workspace_bytes);
+    bwd_cols_t tc;
+    make_bwd_cols(m, calc_grad_inputs != 0, tc);
+    if (tc.total > 512) { set_error("%s: configuration needs %u TMEM columns (> 512)", fn, tc.total); return NGP_EUNSUPPORTED; }
+    uint32_t nbuf = 2;
+    size_t smem = m.wbytes + nbuf * (size_t)(ktiles(input_dim) + ktiles(output_dim)) * kActTileBytes +
+                  (2 + (size_t)num_layers) * ktiles(hidden_dim) * kActTileBytes;
+    if (smem + 1024 > kMaxSmem) {  // drop the prefetch ring before giving up
+        nbuf = 1;
+        smem -= (size_t)(ktiles(input_dim) + ktiles(output_dim)) * kActTileBytes;
+    }
+    if (smem + 1024 > kMaxSmem) { set_error("%s: configuration needs %zu bytes of shared memory (> %zu)", fn, smem, kMaxSmem); return NGP_EUNSUPPORTED; }
+    const uint32_t cols = tmem_cols_pow2(tc.total);
+    const uint32_t ntiles = div_round_up(B, kTileRows);
+    uint32_t per_sm = (uint32_t)(kMaxSmem / (smem + 1024));
+    if (per_sm > 512 / cols) per_sm = 512 / cols;
+    if (per_sm < 1) per_sm = 1;
+    uint32_t grid = (uint32_t)sm_count() * per_sm;
+    if (grid > ntiles) grid = ntiles;
+    const int gf32 = grad_weights_dtype == NGP_DTYPE_F32;
+    if (weights_dtype == NGP_DTYPE_F16) {
+        rc = set_smem(k_ffmlp_bwd<__half>, smem);
+        if (rc != NGP_OK) return rc;
+        { NGP_PROF("k_ffmlp_bwd", st); k_ffmlp_bwd<__half><<<grid, 128, smem, st>>>((const __half *)grad, (const __half *)inputs, (const __half *)weights, (__half *)grad_inputs,
+                                                    (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf); }
+    } else {
+        rc = set_smem(k_ffmlp_bwd<float>, smem);
+        if (rc != NGP_OK) return rc;
+        { NGP_PROF("k_ffmlp_bwd", st); k_ffmlp_bwd<float><<<grid, 128, smem, st>>>((const __half *)grad, (const __half *)inputs, (const float *)weights, (__half *)grad_inputs,
+                                                  (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf); }
+    }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
+}  // extern "C"

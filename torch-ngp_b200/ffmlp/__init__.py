@@ -1,1 +1,1 @@
-from .ffmlp import FFMLP, ffmlp_forward, convert_activation, available  # noqa: F401
+from .ffmlp import FFMLP, ffmlp_forward, convert_activation, available, _backend  # noqa: F401
