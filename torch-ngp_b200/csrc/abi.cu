@@ -31,6 +31,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_block", 128},
         {"ffmlp_available", 1},
+        {"ffmlp_fwd_pipes", 0},        // > 0: cap on the tile pipelines per CTA of the FFMLP forward (tuning)
         {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in
     };
     return o;

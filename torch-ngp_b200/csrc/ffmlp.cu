@@ -100,47 +100,54 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
     return *reinterpret_cast<const uint32_t *>(&h);
 }
 
-// ---- epilogues (thread = row = TMEM lane) --------------------------------------------------------------
-// acc[row, 0..n) -> ReLU -> fp16 -> swizzled tile(s)
-__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t n) {
-    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
-        float v[16];
-        tmem_ld16(taddr + c0, v);
-        uint4 lo, hi;
-        lo.x = pack2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)); lo.y = pack2(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
-        lo.z = pack2(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)); lo.w = pack2(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
-        hi.x = pack2(fmaxf(v[8], 0.f), fmaxf(v[9], 0.f)); hi.y = pack2(fmaxf(v[10], 0.f), fmaxf(v[11], 0.f));
-        hi.z = pack2(fmaxf(v[12], 0.f), fmaxf(v[13], 0.f)); hi.w = pack2(fmaxf(v[14], 0.f), fmaxf(v[15], 0.f));
-        const uint32_t c8 = c0 >> 3;
-        uint8_t *t = tiles + (c8 >> 3) * kActTileBytes;
-        *reinterpret_cast<uint4 *>(t + swz_off(row, c8 & 7u)) = lo;
-        *reinterpret_cast<uint4 *>(t + swz_off(row, (c8 + 1) & 7u)) = hi;
+// ---- epilogues -----------------------------------------------------------------------------------------
+// A CTA has 128 * NS threads: warp w owns TMEM lanes 32*(w%4).. (hardware rule) = batch rows, and column group
+// w/4 of width CW = width/NS, so one accumulator row is drained by NS threads in parallel (the epilogue chain
+// -- tcgen05.ld, ReLU, fp16 pack, swizzled st.shared -- is latency bound, not throughput bound).
+__device__ __forceinline__ uint32_t relu2(float a, float b) {
+    const __half2 h = __hmax2(__floats2half2_rn(a, b), __float2half2_rn(0.f));
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+// acc[row, col0 .. col0+CW) -> ReLU -> fp16 -> swizzled tile(s)
+template <int CW>
+__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0) {
+    float v[CW];
+    tmem_ldN<CW>(taddr + col0, v);
+    uint8_t *t = tiles + (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
+    const uint32_t c8 = (col0 & 63u) >> 3;
+#pragma unroll
+    for (int j = 0; j < CW; j += 8) {
+        uint4 u;
+        u.x = relu2(v[j], v[j + 1]); u.y = relu2(v[j + 2], v[j + 3]); u.z = relu2(v[j + 4], v[j + 5]); u.w = relu2(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4 *>(t + (((c8 + (j >> 3)) ^ (row & 7u)) << 4)) = u;
     }
 }
 
 __device__ __forceinline__ uint32_t mask2(float a, float b, uint32_t h2) {
-    const __half2 h = *reinterpret_cast<const __half2 *>(&h2);
-    const float2 f = __half22float2(h);
-    return pack2(f.x > 0.f ? a : 0.f, f.y > 0.f ? b : 0.f);
+    // dL/dh * (h > 0): h is a ReLU output (>= 0, never -0), so "> 0" == "bit pattern != 0"
+    const uint32_t g = pack2(a, b);
+    return g & ((h2 & 0xFFFFu ? 0xFFFFu : 0u) | (h2 & 0xFFFF0000u ? 0xFFFF0000u : 0u));
 }
-// acc[row, 0..n) * (act[row, :] > 0) -> fp16 -> swizzled tile(s)   (ReLU backward from the saved activation)
-__device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t n) {
-    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
-        float v[16];
-        tmem_ld16(taddr + c0, v);
-        const uint32_t c8 = c0 >> 3;
-        const uint32_t o0 = (c8 >> 3) * kActTileBytes + swz_off(row, c8 & 7u), o1 = (c8 >> 3) * kActTileBytes + swz_off(row, (c8 + 1) & 7u);
-        const uint4 a0 = *reinterpret_cast<const uint4 *>(act_tiles + o0), a1 = *reinterpret_cast<const uint4 *>(act_tiles + o1);
-        uint4 lo, hi;
-        lo.x = mask2(v[0], v[1], a0.x); lo.y = mask2(v[2], v[3], a0.y); lo.z = mask2(v[4], v[5], a0.z); lo.w = mask2(v[6], v[7], a0.w);
-        hi.x = mask2(v[8], v[9], a1.x); hi.y = mask2(v[10], v[11], a1.y); hi.z = mask2(v[12], v[13], a1.z); hi.w = mask2(v[14], v[15], a1.w);
-        *reinterpret_cast<uint4 *>(tiles + o0) = lo;
-        *reinterpret_cast<uint4 *>(tiles + o1) = hi;
+// acc[row, col0 .. col0+CW) * (act[row, :] > 0) -> fp16 -> swizzled tile(s)   (ReLU backward from the saved activation)
+template <int CW>
+__device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t col0) {
+    float v[CW];
+    tmem_ldN<CW>(taddr + col0, v);
+    const uint32_t base = (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
+    const uint32_t c8 = (col0 & 63u) >> 3;
+#pragma unroll
+    for (int j = 0; j < CW; j += 8) {
+        const uint32_t o = base + (((c8 + (j >> 3)) ^ (row & 7u)) << 4);
+        const uint4 a = *reinterpret_cast<const uint4 *>(act_tiles + o);
+        uint4 u;
+        u.x = mask2(v[j], v[j + 1], a.x); u.y = mask2(v[j + 2], v[j + 3], a.y);
+        u.z = mask2(v[j + 4], v[j + 5], a.z); u.w = mask2(v[j + 6], v[j + 7], a.w);
+        *reinterpret_cast<uint4 *>(tiles + o) = u;
     }
 }
 // acc[row, 0..n) -> fp16 -> global row (n % 16 == 0; 32 B per 16 columns, consecutive rows are contiguous)
-__device__ __forceinline__ void epi_to_global(uint32_t taddr, __half *__restrict__ dst_row, uint32_t n, bool write) {
-    for (uint32_t c0 = 0; c0 < n; c0 += 16) {
+__device__ __forceinline__ void epi_to_global(uint32_t taddr, __half *__restrict__ dst_row, uint32_t cbeg, uint32_t cend, bool write) {
+    for (uint32_t c0 = cbeg; c0 < cend; c0 += 16) {
         float v[16];
         tmem_ld16(taddr + c0, v);
         if (write) {
@@ -192,73 +199,78 @@ __host__ __device__ inline uint32_t tmem_cols_pow2(uint32_t n) {
 // ==========================================================================================================
 // forward / inference
 // ==========================================================================================================
-template <typename WT>
-__global__ void __launch_bounds__(128) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
-                                                   const mlp_t m, uint32_t ntiles, uint32_t tmem_cols) {
+template <int HID> struct split_of { static constexpr int NS = HID >= 64 ? 4 : (HID == 32 ? 2 : 1); };
+
+__device__ __forceinline__ void pipe_sync(uint32_t id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+
+// One CTA per SM runs NP independent tile pipelines (one warpgroup of 128 threads each) that share the staged
+// weights: measured on B200 a layer step is latency bound (each tcgen05.mma of this size takes ~80-100 cycles to
+// ISSUE, the accumulator round trip another ~600), so throughput comes from tiles in flight, not from a
+// faster single chain.  Pipeline p: rows = its tile, TMEM columns [p*accw, (p+1)*accw), mbarrier p, named barrier 1+p.
+template <typename WT, int HID>
+__global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
+                                                    const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, uint32_t accw) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
-    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ __align__(8) uint64_t s_bar[8];
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
     const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes;
     uint8_t *sw = smem;
-    uint8_t *sx[2] = {smem + m.wbytes, smem + m.wbytes + xbytes};
-    uint8_t *sa = smem + m.wbytes + 2 * xbytes;
-    (void)abytes;
+    uint8_t *sx = smem + m.wbytes + pipe * (xbytes + abytes);
+    uint8_t *sa = sx + xbytes;
 
-    uint32_t tile = blockIdx.x;
-    if (tile < ntiles) load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
-    cp_async_commit();
     stage_weights<WT>(sw, w, m, tid, blockDim.x);
     if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
-    if (tid == 0) {
-        mbar_init(&s_bar, 1);
-        mbar_init_fence();
-    }
+    if (tid < np) mbar_init(&s_bar[tid], 1);
+    if (tid == 0) mbar_init_fence();
     fence_proxy_async();
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tmem = s_tmem;
-    const uint32_t trow = tmem + ((warp * 32u) << 16);  // this warp's 32 TMEM lanes
-    uint32_t phase = 0, buf = 0;
+    const uint32_t tmem = s_tmem + pipe * accw;
+    const uint32_t trow = tmem + (((warp & 3u) * 32u) << 16);  // this warp's 32 TMEM lanes
+    uint64_t *bar = &s_bar[pipe];
+    const uint32_t bid = 1u + pipe;
+    uint32_t phase = 0;
 
-    for (; tile < ntiles; tile += gridDim.x, buf ^= 1u) {
-        const uint32_t next = tile + gridDim.x;
-        if (next < ntiles) load_rows_async(sx[buf ^ 1u], x, next * kTileRows, m.B, m.in, tid, blockDim.x);
+    for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
+        load_rows_async(sx, x, tile * kTileRows, m.B, m.in, row, 128);
         cp_async_commit();
-        cp_async_wait<1>();  // this tile's rows have landed
+        cp_async_wait<0>();
         fence_proxy_async();
-        __syncthreads();
-        if (tid == 0) {
+        pipe_sync(bid);
+        if (row == 0) {
             fence_after_sync();
-            issue_fwd(tmem, sx[buf], sw + m.soff[0], m.hid, m.in);
-            mma_commit(&s_bar);
+            issue_fwd(tmem, sx, sw + m.soff[0], m.hid, m.in);
+            mma_commit(bar);
         }
         for (uint32_t l = 0; l < m.nl; ++l) {
-            mbar_wait(&s_bar, phase);
+            mbar_wait(bar, phase);
             phase ^= 1u;
             fence_after_sync();
-            epi_relu_to_tile(trow, sa, tid, m.hid);
+            constexpr int CW = HID < 32 ? HID : 32;  // 1024 threads per CTA: <= 64 registers, drain 32 columns at a time
+#pragma unroll
+            for (int c0 = 0; c0 < HID; c0 += CW) epi_relu_to_tile<CW>(trow, sa, row, c0);
             fence_proxy_async();
             fence_before_sync();
-            __syncthreads();
-            if (tid == 0) {
+            pipe_sync(bid);
+            if (row == 0) {
                 fence_after_sync();
                 issue_fwd(tmem, sa, sw + m.soff[l + 1], m.rows[l + 1], m.hid);
-                mma_commit(&s_bar);
+                mma_commit(bar);
             }
         }
-        mbar_wait(&s_bar, phase);
+        mbar_wait(bar, phase);
         phase ^= 1u;
         fence_after_sync();
-        const uint32_t grow = tile * kTileRows + tid;
-        epi_to_global(trow, y + (size_t)grow * m.out, m.out, grow < m.B);
+        const uint32_t grow = tile * kTileRows + row;
+        epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, grow < m.B);
         fence_before_sync();
-        __syncthreads();  // accumulator drained before the next tile's first MMA overwrites it
+        pipe_sync(bid);  // accumulator drained before this pipeline's next first MMA overwrites it
     }
-    cp_async_wait<0>();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+    if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
 }
 
 // ==========================================================================================================
@@ -280,8 +292,8 @@ __host__ __device__ inline void make_bwd_cols(const mlp_t &m, bool calc_dx, bwd_
     c.total = o;
 }
 
-template <typename WT>
-__global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
+template <typename WT, int HID>
+__global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                    __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                    int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
                                                    uint32_t nbuf) {
@@ -289,7 +301,9 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
     __shared__ __align__(8) uint64_t s_bar;
+    constexpr int NS = split_of<HID>::NS, CW = HID / NS;
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t row = tid & 127u, cg = tid >> 7;
     const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes, obytes = ktiles(m.out) * kActTileBytes;
     uint8_t *sw = smem;
     uint8_t *p = smem + m.wbytes;
@@ -322,7 +336,7 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = s_tmem;
-    const uint32_t trow = tmem + ((warp * 32u) << 16);
+    const uint32_t trow = tmem + (((warp & 3u) * 32u) << 16);
     uint32_t phase = 0, buf = 0, first = 1;
 
     for (; tile < ntiles; tile += gridDim.x, buf ^= (nbuf - 1u)) {
@@ -352,7 +366,7 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
             mbar_wait(&s_bar, phase);
             phase ^= 1u;
             fence_after_sync();
-            epi_relu_to_tile(trow + tc.acc, sh + l * abytes, tid, m.hid);
+            epi_relu_to_tile<CW>(trow + tc.acc, sh + l * abytes, row, cg * CW);
             fence_proxy_async();
             fence_before_sync();
             __syncthreads();
@@ -373,7 +387,7 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
             mbar_wait(&s_bar, phase);
             phase ^= 1u;
             fence_after_sync();
-            epi_mask_to_tile(trow + tc.acc, sh + (uint32_t)l * abytes, g, tid, m.hid);  // G_l = dH_l * (H_l > 0)
+            epi_mask_to_tile<CW>(trow + tc.acc, sh + (uint32_t)l * abytes, g, row, cg * CW);  // G_l = dH_l * (H_l > 0)
             fence_proxy_async();
             fence_before_sync();
             __syncthreads();
@@ -394,8 +408,9 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
         phase ^= 1u;
         fence_after_sync();
         if (calc_dx) {
-            const uint32_t grow = tile * kTileRows + tid;
-            epi_to_global(trow + tc.acc, grad_x + (size_t)grow * m.in, m.in, grow < m.B);
+            const uint32_t grow = tile * kTileRows + row;
+            for (uint32_t c0 = cg * 16u; c0 < m.in; c0 += NS * 16u)
+                epi_to_global(trow + tc.acc, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < m.B);
         }
         fence_before_sync();
         __syncthreads();
@@ -407,11 +422,11 @@ __global__ void __launch_bounds__(128) k_ffmlp_bwd(const __half *__restrict__ gr
     if (!first) {
         for (uint32_t i = 0; i <= m.nl; ++i) {
             const uint32_t rows = m.rows[i], K = m.K[i];
-            for (uint32_t c0 = 0; c0 < K; c0 += 16) {  // warp-uniform trip count: tcgen05.ld is .sync.aligned
+            for (uint32_t c0 = cg * 16u; c0 < K; c0 += NS * 16u) {  // warp-uniform trip count: tcgen05.ld is .sync.aligned
                 float v[16];
                 tmem_ld16(trow + tc.dw[i] + c0, v);
-                if (tid < rows) {
-                    float *d = ws + m.woff[i] + (size_t)tid * K + c0;
+                if (row < rows) {
+                    float *d = ws + m.woff[i] + (size_t)row * K + c0;
 #pragma unroll
                     for (int j = 0; j < 16; j += 4)
                         asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3]) : "memory");
@@ -480,26 +495,40 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     if (rc != NGP_OK) return rc;
     mlp_t m;
     make_mlp(m, B, in, out, hid, nl);
-    const size_t smem = m.wbytes + 2 * (size_t)ktiles(in) * kActTileBytes + (size_t)ktiles(hid) * kActTileBytes;
-    if (smem + 1024 > kMaxSmem) { set_error("%s: configuration needs %zu bytes of shared memory (> %zu)", fn, smem, kMaxSmem); return NGP_EUNSUPPORTED; }
-    const uint32_t cols = tmem_cols_pow2(hid > out ? hid : out);
+    const size_t per_pipe = ((size_t)ktiles(in) + ktiles(hid)) * kActTileBytes;
+    uint32_t accw = hid > out ? hid : out;
+    accw = (accw + 31u) & ~31u;
     const uint32_t ntiles = div_round_up(B, kTileRows);
-    uint32_t per_sm = (uint32_t)(kMaxSmem / (smem + 1024));
-    if (per_sm > 512 / cols) per_sm = 512 / cols;
-    if (per_sm > 8) per_sm = 8;
-    if (per_sm < 1) per_sm = 1;
-    uint32_t grid = (uint32_t)sm_count() * per_sm;
-    if (grid > ntiles) grid = ntiles;
+    if (m.wbytes + per_pipe + 1024 > kMaxSmem) { set_error("%s: configuration needs %zu bytes of shared memory (> %zu)", fn, m.wbytes + per_pipe + 1024, kMaxSmem); return NGP_EUNSUPPORTED; }
+    uint32_t np = (uint32_t)((kMaxSmem - 1024 - m.wbytes) / per_pipe);
+    if (np > 512 / accw) np = 512 / accw;
+    if (np > 8) np = 8;
+    const int np_opt = get_option("ffmlp_fwd_pipes", 0);
+    if (np_opt > 0 && (uint32_t)np_opt < np) np = (uint32_t)np_opt;
+    const uint32_t per_cta_need = div_round_up(ntiles, (uint32_t)sm_count());  // tiles each SM gets anyway
+    if (np > per_cta_need) np = per_cta_need;
+    const size_t smem = m.wbytes + np * per_pipe;
+    const uint32_t cols = tmem_cols_pow2(np * accw);
+    uint32_t grid = div_round_up(ntiles, np);
+    if (grid > (uint32_t)sm_count()) grid = (uint32_t)sm_count();
     cudaStream_t st = (cudaStream_t)stream;
-    if (wdtype == NGP_DTYPE_F16) {
-        rc = set_smem(k_ffmlp_fwd<__half>, smem);
-        if (rc != NGP_OK) return rc;
-        { NGP_PROF("k_ffmlp_fwd", st); k_ffmlp_fwd<__half><<<grid, 128, smem, st>>>((const __half *)inputs, (const __half *)weights, (__half *)outputs, m, ntiles, cols); }
-    } else {
-        rc = set_smem(k_ffmlp_fwd<float>, smem);
-        if (rc != NGP_OK) return rc;
-        { NGP_PROF("k_ffmlp_fwd", st); k_ffmlp_fwd<float><<<grid, 128, smem, st>>>((const __half *)inputs, (const float *)weights, (__half *)outputs, m, ntiles, cols); }
+#define NGP_FWD_CASE(WT_, HID_)                                                                                              \
+    {                                                                                                                        \
+        rc = set_smem(k_ffmlp_fwd<WT_, HID_>, smem);                                                                         \
+        if (rc != NGP_OK) return rc;                                                                                         \
+        NGP_PROF("k_ffmlp_fwd", st);                                                                                         \
+        k_ffmlp_fwd<WT_, HID_><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw); \
     }
+#define NGP_FWD_HID(WT_)                                         \
+    switch (hid) {                                               \
+        case 16: NGP_FWD_CASE(WT_, 16) break;                    \
+        case 32: NGP_FWD_CASE(WT_, 32) break;                    \
+        case 64: NGP_FWD_CASE(WT_, 64) break;                    \
+        default: NGP_FWD_CASE(WT_, 128) break;                   \
+    }
+    if (wdtype == NGP_DTYPE_F16) NGP_FWD_HID(__half) else NGP_FWD_HID(float)
+#undef NGP_FWD_HID
+#undef NGP_FWD_CASE
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -572,17 +601,24 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
     uint32_t grid = (uint32_t)sm_count() * per_sm;
     if (grid > ntiles) grid = ntiles;
     const int gf32 = grad_weights_dtype == NGP_DTYPE_F32;
-    if (weights_dtype == NGP_DTYPE_F16) {
-        rc = set_smem(k_ffmlp_bwd<__half>, smem);
-        if (rc != NGP_OK) return rc;
-        { NGP_PROF("k_ffmlp_bwd", st); k_ffmlp_bwd<__half><<<grid, 128, smem, st>>>((const __half *)grad, (const __half *)inputs, (const __half *)weights, (__half *)grad_inputs,
-                                                    (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf); }
-    } else {
-        rc = set_smem(k_ffmlp_bwd<float>, smem);
-        if (rc != NGP_OK) return rc;
-        { NGP_PROF("k_ffmlp_bwd", st); k_ffmlp_bwd<float><<<grid, 128, smem, st>>>((const __half *)grad, (const __half *)inputs, (const float *)weights, (__half *)grad_inputs,
-                                                  (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf); }
+#define NGP_BWD_CASE(WT_, HID_)                                                                                              \
+    {                                                                                                                        \
+        rc = set_smem(k_ffmlp_bwd<WT_, HID_>, smem);                                                                         \
+        if (rc != NGP_OK) return rc;                                                                                         \
+        NGP_PROF("k_ffmlp_bwd", st);                                                                                         \
+        k_ffmlp_bwd<WT_, HID_><<<grid, 128 * split_of<HID_>::NS, smem, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf);   \
     }
+#define NGP_BWD_HID(WT_)                                         \
+    switch (hidden_dim) {                                        \
+        case 16: NGP_BWD_CASE(WT_, 16) break;                    \
+        case 32: NGP_BWD_CASE(WT_, 32) break;                    \
+        case 64: NGP_BWD_CASE(WT_, 64) break;                    \
+        default: NGP_BWD_CASE(WT_, 128) break;                   \
+    }
+    if (weights_dtype == NGP_DTYPE_F16) NGP_BWD_HID(__half) else NGP_BWD_HID(float)
+#undef NGP_BWD_HID
+#undef NGP_BWD_CASE
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
