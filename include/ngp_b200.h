@@ -168,6 +168,36 @@ NGP_API int ngp_free_splitk(void);
 NGP_API int ngp_sh_encode_forward(const float *inputs, void *outputs, uint32_t B, uint32_t degree, uint32_t out_stride,
                           int dtype, void *stream);
 
+/* Renderer-driver glue (scope table "next" row 1: nerf/renderer.py:257-431 run_cuda, :498-598 update_extra_state;
+ * network nerf/network_ff.py:51-74; optimizer step main_nerf.py:194-197 + nerf/utils.py:974-978).  All device
+ * resident, no host reads; `state` is a float[16] device block (see nerf_step.cu) holding step count, lr, bias
+ * corrections, loss scale, found_inf flag and the loss accumulator. */
+NGP_API int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *stream);
+/* h [M,16] f16, dirs [M,3] -> sigmas [M] f32 = density_scale*exp(h0); cin [M,32] f16 = [SH4(dir) | h1..h15 | 0] */
+NGP_API int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, float *sigmas, void *cin, uint32_t M, void *stream);
+/* c [M,16] f16 -> rgbs [M,3] f32 = sigmoid(c0..c2) */
+NGP_API int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream);
+/* MSE loss of image + (1 - weights_sum) * bg against gt [N,3]; loss accumulated into *loss_out; gradients scaled by *loss_scale */
+NGP_API int ngp_nerf_loss(const float *image, const float *weights_sum, const float *gt, float bg, uint32_t N, const float *loss_scale,
+                  float *grad_image, float *grad_weights_sum, float *grad_depth, float *loss_out, void *stream);
+NGP_API int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream);
+NGP_API int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *grad_cin, float density_scale, void *grad_h,
+                          uint32_t M, void *stream);
+NGP_API int ngp_step_begin(float *state, float beta1, float beta2, void *stream);
+NGP_API int ngp_step_end(float *state, void *stream);
+/* sets state.found_inf when any gradient is inf/nan: g16 = n16 halves (n16 % 8 == 0), g32 = n32 floats (n32 % 4 == 0) */
+NGP_API int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t n32, float *state, void *stream);
+/* Adam over params[0 .. n16+n32): first n16 have fp16 gradients + an fp16 shadow copy, last n32 fp32 gradients; gradients are
+ * divided by (loss scale * grad_div), consumed and CLEARED; skipped (but still cleared) when state.found_inf */
+NGP_API int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
+                  const float *state, float beta1, float beta2, float eps, float grad_div, void *stream);
+NGP_API int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream);
+/* grid = max(grid*decay, tmp) where both >= 0; *sum_out = sum(clamp(grid, 0)) */
+NGP_API int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, float *sum_out, void *stream);
+/* packbits with thresh = min(*sum * inv_count, density_thresh) read on the device; N = output bytes (N % 4 == 0) */
+NGP_API int ngp_packbits_mean(const float *grid, uint32_t N, const float *sum, float inv_count, float density_thresh, uint8_t *bitfield,
+                      void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * diagnostics
  * ------------------------------------------------------------------------------------------- */

@@ -1,0 +1,336 @@
+"""Device-resident Instant-NGP training / rendering driver ("next" row 1 of the scope table).
+
+Restates, on top of the C-ABI ops, what /root/reference/nerf/renderer.py::run_cuda (:257-431) and
+update_extra_state (:498-598) do around the hot-path kernels, with the `network_ff` topology
+(/root/reference/nerf/network_ff.py:11-74: hash grid 16x2 -> FFMLP 32->64->64->16 -> trunc_exp | SH-16 + 15 geo
+features + pad -> FFMLP 32->64->64->64->16 -> sigmoid), the `main_nerf -O` step (fp16 autocast + GradScaler +
+Adam(lr 1e-2, betas (0.9, 0.99), eps 1e-15) + 0.1^(step/30000) decay, main_nerf.py:194-197, nerf/utils.py:960-1011)
+and the upstream density-grid schedule (every 16 steps, nerf/utils.py:820-823).
+
+B200-first differences (all below the plugin API, results equal to the autograd path through the plugin modules):
+  * every buffer is allocated once at fixed capacity; a step is a fixed launch sequence with no host reads, so it is
+    captured in ONE CUDA graph (the reference pays ~10 small kernels + dozens of ATen ops + 3 fresh zero-filled
+    [M,.] buffers + a dense Adam + a loss.item() sync per step);
+  * parameters live in one flat fp32 vector [hash table | sigma MLP | colour MLP] with an fp16 shadow of the table
+    maintained by the fused Adam kernel (the reference re-casts the 49 MB table every forward under autocast);
+  * gradients are one flat buffer [fp16 table | fp32 MLP] -> data-parallel training is one NCCL all-reduce per dtype.
+"""
+import math
+
+import numpy as np
+import torch
+
+import ngp_abi as abi
+import ffmlp as _ffmlp
+import gridencoder as _gridencoder
+import raymarching as _raymarching
+
+_ST_STEP, _ST_LR, _ST_BC1, _ST_BC2, _ST_SCALE, _ST_GROWTH, _ST_FOUND_INF, _ST_LOSS, _ST_LAST_LOSS, _ST_LR0, _ST_DECAY_STEPS, _ST_DECAY, _ST_GROWTH_INTERVAL = range(13)
+
+
+def _ck(rc):
+    abi.check(rc)
+
+
+class NGPTrainer:
+    def __init__(self, bound=1.0, num_rays=4096, device="cuda", lr=1e-2, grid_size=128, density_thresh=10.0, density_scale=1.0,
+                 min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=128.0,
+                 growth_interval=2000, decay_steps=30000, world_size=1, seed=0, use_graph=True, update_interval=16,
+                 num_levels=16, log2_hashmap_size=19, base_resolution=16):
+        self.dev = torch.device(device)
+        self.bound, self.N = float(bound), int(num_rays)
+        self.cascade = 1 + math.ceil(math.log2(bound))
+        self.H = grid_size
+        self.density_thresh, self.density_scale = density_thresh, density_scale
+        self.min_near, self.dt_gamma, self.max_steps = min_near, dt_gamma, max_steps
+        self.bg_color, self.T_thresh, self.perturb = bg_color, T_thresh, perturb
+        self.world, self.use_graph, self.update_interval = world_size, use_graph, update_interval
+        self.beta1, self.beta2, self.eps = 0.9, 0.99, 1e-15
+        dev = self.dev
+
+        # ---- parameters: [hash table | sigma net | colour net], same shapes / init as the reference modules ----
+        enc = _gridencoder.GridEncoder(num_levels=num_levels, log2_hashmap_size=log2_hashmap_size, base_resolution=base_resolution,
+                                       desired_resolution=2048 * bound)
+        self.L, self.C, self.per_level_scale, self.base_resolution = enc.num_levels, enc.level_dim, enc.per_level_scale, enc.base_resolution
+        self.S = float(np.log2(enc.per_level_scale))
+        self.offsets = enc.offsets.to(dev)
+        self.offsets_host = np.ascontiguousarray(enc.offsets.numpy().astype(np.int32))
+        self.T = int(enc.offsets[-1])
+        self.enc_dim = self.L * self.C
+        assert self.enc_dim == 32, "the network_ff topology expects a 32-wide encoding"
+        sig = _ffmlp.FFMLP(32, 16, 64, 2)
+        col = _ffmlp.FFMLP(32, 3, 64, 3)
+        self.n16 = self.T * self.C
+        self.n_sig, self.n_col = sig.num_parameters, col.num_parameters
+        self.n32 = self.n_sig + self.n_col
+        g = torch.Generator().manual_seed(seed)
+        table0 = (torch.rand(self.T, self.C, generator=g) * 2 - 1) * 1e-4
+        self.params = torch.cat([table0.reshape(-1), sig.weights.detach(), col.weights.detach()]).to(dev).contiguous()
+        self.exp_avg = torch.zeros_like(self.params)
+        self.exp_avg_sq = torch.zeros_like(self.params)
+        self.embeddings = self.params[:self.n16].view(self.T, self.C)
+        self.sigma_w = self.params[self.n16:self.n16 + self.n_sig]
+        self.color_w = self.params[self.n16 + self.n_sig:]
+        self.table16 = torch.empty(self.T, self.C, dtype=torch.half, device=dev)
+        _ck(abi.lib.ngp_cast_f16(self.params.data_ptr(), self.table16.data_ptr(), self.n16, abi.stream()))
+        self.g16 = torch.zeros(self.T, self.C, dtype=torch.half, device=dev)
+        self.g32 = torch.zeros(self.n32, device=dev)
+        self.g_sig, self.g_col = self.g32[:self.n_sig], self.g32[self.n_sig:]
+
+        # ---- scene state (nerf/renderer.py:83-100) ----
+        self.aabb = torch.tensor([-bound, -bound, -bound, bound, bound, bound], dtype=torch.float32, device=dev)
+        self.density_grid = torch.zeros(self.cascade, self.H ** 3, device=dev)
+        self.density_bitfield = torch.zeros(self.cascade * self.H ** 3 // 8, dtype=torch.uint8, device=dev)
+        self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=dev)
+        self.count_sum = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.mean_sum = torch.zeros(1, device=dev)
+        self.mean_count, self.iter_density, self.local_step, self.global_step = -1, 0, 0, 0
+
+        # ---- step state ----
+        st = torch.zeros(16)
+        st[_ST_STEP] = torch.tensor(0, dtype=torch.int32).view(torch.float32)
+        st[_ST_SCALE], st[_ST_LR0], st[_ST_LR], st[_ST_DECAY_STEPS], st[_ST_DECAY] = loss_scale, lr, lr, decay_steps, 0.1
+        st[_ST_GROWTH] = torch.tensor(0, dtype=torch.int32).view(torch.float32)
+        st[_ST_GROWTH_INTERVAL] = torch.tensor(growth_interval, dtype=torch.int32).view(torch.float32)
+        st[_ST_FOUND_INF] = torch.tensor(0, dtype=torch.int32).view(torch.float32)
+        self.state = st.to(dev)
+
+        # ---- per-ray buffers ----
+        N = self.N
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.rays_o, self.rays_d, self.gt = torch.zeros(N, 3, **f32), torch.zeros(N, 3, **f32), torch.zeros(N, 3, **f32)
+        self.nears, self.fars, self.noises = torch.empty(N, **f32), torch.empty(N, **f32), torch.zeros(N, **f32)
+        self.rays = torch.zeros(N, 3, dtype=torch.int32, device=dev)
+        self.ws, self.depth, self.image = torch.empty(N, **f32), torch.empty(N, **f32), torch.empty(N, 3, **f32)
+        self.g_image, self.g_ws, self.g_depth = torch.empty(N, 3, **f32), torch.empty(N, **f32), torch.empty(N, **f32)
+        self.march_ws = torch.zeros(max(1 << 16, abi.lib.ngp_march_rays_train_workspace_bytes(N)), dtype=torch.uint8, device=dev)
+        self.mlp_ws = torch.zeros(1 << 17, dtype=torch.uint8, device=dev)
+        self.M = 0
+        self._graph = None
+        # until the first density-grid interval has measured the sample count: room for 512 samples per ray (the reference
+        # allocates N * max_steps and trims after a host read, raymarching.py:196-231); rays that do not fit are dropped
+        self._alloc_samples(N * 512)
+        self._pool = None
+
+    # ------------------------------------------------------------------------------------------------------
+    def _alloc_samples(self, M):
+        M = int(max(1024, (M + 1023) // 1024 * 1024))
+        if M == self.M:
+            return
+        dev = self.dev
+        f32, f16 = dict(dtype=torch.float32, device=dev), dict(dtype=torch.half, device=dev)
+        self.M = M
+        self.xyzs, self.dirs, self.deltas = torch.zeros(M, 3, **f32), torch.zeros(M, 3, **f32), torch.zeros(M, 2, **f32)
+        self.x01 = torch.zeros(M, 3, **f32)
+        self.enc, self.h, self.cin, self.c = torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16)
+        self.sigmas, self.rgbs = torch.zeros(M, **f32), torch.zeros(M, 3, **f32)
+        self.g_sigmas, self.g_rgbs = torch.zeros(M, **f32), torch.zeros(M, 3, **f32)
+        self.g_c, self.g_cin, self.g_h, self.g_enc = torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16)
+        self._graph = None
+
+    # ---- network pieces on raw buffers (shared by the step, the density query and the renderer) -----------
+    def _encode(self, xyzs, x01, enc, M):
+        s = abi.stream()
+        _ck(abi.lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
+        _ck(abi.lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                            enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                            abi.LAYOUT_BLC, s))
+
+    def _sigma_forward(self, enc, h, M, inference):
+        fn = abi.lib.ngp_ffmlp_inference if inference else abi.lib.ngp_ffmlp_forward
+        _ck(fn(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, h.data_ptr(), abi.stream()))
+
+    def _color_forward(self, cin, c, M, inference):
+        fn = abi.lib.ngp_ffmlp_inference if inference else abi.lib.ngp_ffmlp_forward
+        _ck(fn(cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, c.data_ptr(), abi.stream()))
+
+    def _network_forward(self, M, inference=False):
+        """xyzs, dirs -> sigmas, rgbs on the sample buffers (network_ff.py:51-74)."""
+        s = abi.stream()
+        self._encode(self.xyzs, self.x01, self.enc, M)
+        self._sigma_forward(self.enc, self.h, M, inference)
+        _ck(abi.lib.ngp_nerf_mid_forward(self.h.data_ptr(), self.dirs.data_ptr(), self.density_scale, self.sigmas.data_ptr(), self.cin.data_ptr(), M, s))
+        self._color_forward(self.cin, self.c, M, inference)
+        _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s))
+
+    # ---- one training step as a fixed launch sequence ---------------------------------------------------------
+    def _forward_backward(self):
+        s, N, M, lib = abi.stream(), self.N, self.M, abi.lib
+        counter = self.step_counter[0]  # one slot: sample placement starts at counter[0], so it is cleared every step
+        lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s)
+        counter.zero_()
+        if self.perturb:
+            self.noises.uniform_()
+        _ck(lib.ngp_near_far_from_aabb(self.rays_o.data_ptr(), self.rays_d.data_ptr(), self.aabb.data_ptr(), N, self.min_near,
+                                       self.nears.data_ptr(), self.fars.data_ptr(), s))
+        _ck(lib.ngp_march_rays_train(self.rays_o.data_ptr(), self.rays_d.data_ptr(), self.density_bitfield.data_ptr(), self.bound, self.dt_gamma,
+                                     self.max_steps, N, self.cascade, self.H, M, self.nears.data_ptr(), self.fars.data_ptr(), self.xyzs.data_ptr(),
+                                     self.dirs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), counter.data_ptr(), self.noises.data_ptr(),
+                                     self.march_ws.data_ptr(), self.march_ws.numel(), s))
+        self.count_sum.add_(counter[:1])  # running sample count since the last density-grid update (-> mean_count)
+        self._network_forward(M)
+        _ck(lib.ngp_composite_rays_train_forward(self.sigmas.data_ptr(), self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), M, N,
+                                                 self.T_thresh, self.ws.data_ptr(), self.depth.data_ptr(), self.image.data_ptr(), s))
+        _ck(lib.ngp_nerf_loss(self.image.data_ptr(), self.ws.data_ptr(), self.gt.data_ptr(), self.bg_color, N, self.state[_ST_SCALE:].data_ptr(),
+                              self.g_image.data_ptr(), self.g_ws.data_ptr(), self.g_depth.data_ptr(), self.state[_ST_LOSS:].data_ptr(), s))
+        # ---- backward ----
+        self.g_sigmas.zero_()
+        self.g_rgbs.zero_()
+        _ck(lib.ngp_composite_rays_train_backward(self.g_ws.data_ptr(), self.g_depth.data_ptr(), self.g_image.data_ptr(), self.sigmas.data_ptr(),
+                                                  self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), self.ws.data_ptr(),
+                                                  self.depth.data_ptr(), self.image.data_ptr(), M, N, self.T_thresh, self.g_sigmas.data_ptr(),
+                                                  self.g_rgbs.data_ptr(), s))
+        _ck(lib.ngp_nerf_rgb_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_c.data_ptr(), M, s))
+        _ck(lib.ngp_ffmlp_backward(self.g_c.data_ptr(), self.cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 3, 0, 6, 1,
+                                   None, self.g_cin.data_ptr(), self.g_col.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
+        _ck(lib.ngp_nerf_mid_backward(self.g_sigmas.data_ptr(), self.h.data_ptr(), self.g_cin.data_ptr(), self.density_scale, self.g_h.data_ptr(), M, s))
+        _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 2, 0, 6, 1,
+                                   None, self.g_enc.data_ptr(), self.g_sig.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
+        # table gradient: g16 was cleared by the previous optimizer step (k_adam consumes and zeroes it)
+        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
+                                         self.offsets_host.ctypes.data, self.g16.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None,
+                                         None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+
+    def _optimizer_step(self):
+        s, lib = abi.stream(), abi.lib
+        _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
+        _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
+                              self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world), s))
+        _ck(lib.ngp_step_end(self.state.data_ptr(), s))
+
+    def _allreduce(self):
+        import torch.distributed as dist
+        dist.all_reduce(self.g16.view(-1))
+        dist.all_reduce(self.g32)
+
+    def _step_eager(self):
+        self._forward_backward()
+        if self.world > 1:
+            self._allreduce()
+        self._optimizer_step()
+
+    def _capture(self):
+        """Warm up eagerly on a side stream (lazy kernel attributes, NCCL communicators), then capture the launch sequence.
+        With several ranks the all-reduce stays outside the graphs: [forward+backward graph] -> NCCL -> [optimizer graph]."""
+        stream = torch.cuda.Stream()
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            self._step_eager()
+        torch.cuda.current_stream().wait_stream(stream)
+        torch.cuda.synchronize()
+        self._g_fb = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_fb):
+            self._forward_backward()
+        self._g_opt = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_opt):
+            self._optimizer_step()
+        self._graph = True
+        return 1  # the warm-up was a real optimisation step
+
+    def train_step(self, rays_o=None, rays_d=None, gt=None):
+        """One optimisation step.  rays_o / rays_d / gt: [N,3] tensors (device, or pinned host -> async H2D); None keeps
+        whatever is in the ray buffers (e.g. filled by next_pool_batch)."""
+        if rays_o is not None:
+            self.rays_o.copy_(rays_o, non_blocking=True)
+            self.rays_d.copy_(rays_d, non_blocking=True)
+            self.gt.copy_(gt, non_blocking=True)
+        if self.update_interval > 0 and self.global_step % self.update_interval == 0:
+            self.update_extra_state()
+        if self.use_graph:
+            if self._graph is None:
+                self._capture()
+            else:
+                self._g_fb.replay()
+                if self.world > 1:
+                    self._allreduce()
+                self._g_opt.replay()
+        else:
+            self._step_eager()
+        self.local_step += 1
+        self.global_step += 1
+
+    def loss(self):
+        """Loss of the last finished step (device -> host read)."""
+        return float(self.state[_ST_LAST_LOSS].item())
+
+    # ---- synthetic ray pool (device resident inputs for the kernel-side benchmark) ----------------------------
+    def set_pool(self, rays_o, rays_d, gt):
+        self._pool = (rays_o.contiguous(), rays_d.contiguous(), gt.contiguous())
+        self._cursor = 0
+
+    def next_pool_batch(self):
+        o, d, g = self._pool
+        P, N = o.shape[0], self.N
+        if self._cursor + N > P:
+            self._cursor = 0
+        sl = slice(self._cursor, self._cursor + N)
+        self.rays_o.copy_(o[sl]); self.rays_d.copy_(d[sl]); self.gt.copy_(g[sl])
+        self._cursor += N
+
+    # ---- density grid maintenance (nerf/renderer.py:498-598), eager, every `update_interval` steps ---------------
+    @torch.no_grad()
+    def density(self, xyz):
+        """sigma(x) * density_scale through the encoder + sigma net in inference mode; xyz [n,3] in [-bound, bound]."""
+        n = xyz.shape[0]
+        out = torch.empty(n, device=self.dev)
+        chunk = 1 << 21
+        x01 = torch.empty(min(n, chunk), 3, device=self.dev)
+        enc = torch.empty(min(n, chunk), 32, dtype=torch.half, device=self.dev)
+        h = torch.empty(min(n, chunk), 16, dtype=torch.half, device=self.dev)
+        for a in range(0, n, chunk):
+            b = min(n, a + chunk)
+            xs = xyz[a:b].contiguous()
+            self._encode(xs, x01, enc, b - a)
+            self._sigma_forward(enc, h, b - a, True)
+            out[a:b] = torch.exp(h[:b - a, 0].float()) * self.density_scale
+        return out
+
+    @torch.no_grad()
+    def update_extra_state(self, decay=0.95):
+        H, dev = self.H, self.dev
+        tmp = -torch.ones_like(self.density_grid)
+        if self.iter_density < 16:  # full sweep
+            if not hasattr(self, "_all_coords"):
+                r = torch.arange(H, dtype=torch.int32, device=dev)
+                xx, yy, zz = torch.meshgrid(r, r, r, indexing="ij")
+                self._all_coords = torch.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], -1).contiguous()
+                self._all_indices = _raymarching.morton3D(self._all_coords).long()
+            coords_l, indices_l = [self._all_coords] * self.cascade, [self._all_indices] * self.cascade
+        else:  # partial: H^3/4 uniform cells + H^3/4 cells resampled from the occupied ones, per cascade
+            n = H ** 3 // 4
+            coords_l, indices_l = [], []
+            for cas in range(self.cascade):
+                coords = torch.randint(0, H, (n, 3), device=dev, dtype=torch.int32)
+                indices = _raymarching.morton3D(coords).long()
+                occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
+                if occ.shape[0] > 0:
+                    occ = occ[torch.randint(0, occ.shape[0], [n], dtype=torch.long, device=dev)]
+                    occ_coords = _raymarching.morton3D_invert(occ.int())
+                    indices = torch.cat([indices, occ])
+                    coords = torch.cat([coords, occ_coords])
+                coords_l.append(coords)
+                indices_l.append(indices)
+        for cas in range(self.cascade):
+            coords, indices = coords_l[cas], indices_l[cas]
+            xyzs = 2 * coords.float() / (H - 1) - 1
+            bound = min(2 ** cas, self.bound)
+            hgs = bound / H
+            cas_xyzs = xyzs * (bound - hgs)
+            cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * hgs
+            tmp[cas, indices] = self.density(cas_xyzs)
+        n_cells = self.density_grid.numel()
+        _ck(abi.lib.ngp_density_ema(self.density_grid.data_ptr(), tmp.data_ptr(), decay, n_cells, self.mean_sum.data_ptr(), abi.stream()))
+        _ck(abi.lib.ngp_packbits_mean(self.density_grid.data_ptr(), n_cells // 8, self.mean_sum.data_ptr(), 1.0 / n_cells, self.density_thresh,
+                                      self.density_bitfield.data_ptr(), abi.stream()))
+        self.iter_density += 1
+        # sample budget for the next interval (the one host read of the schedule, nerf/renderer.py:593-596)
+        if self.local_step > 0:
+            self.mean_count = int(self.count_sum.item() / self.local_step)
+            need = int(self.mean_count * 1.25) + 4096
+            if need > self.M or need < self.M // 2:
+                self._alloc_samples(need)
+        self.count_sum.zero_()
+        self.local_step = 0
+
+    def mean_density(self):
+        return float(self.mean_sum.item()) / self.density_grid.numel()

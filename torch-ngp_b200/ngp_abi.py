@@ -50,6 +50,19 @@ SIGNATURES = {
     "ngp_allocate_splitk": (_int, [_sz]),
     "ngp_free_splitk": (_int, []),
     "ngp_sh_encode_forward": (_int, [_vp, _vp, _u32, _u32, _u32, _int, _vp]),
+    "ngp_nerf_x01": (_int, [_vp, _f32, _vp, _u32, _vp]),
+    "ngp_nerf_mid_forward": (_int, [_vp, _vp, _f32, _vp, _vp, _u32, _vp]),
+    "ngp_nerf_rgb_forward": (_int, [_vp, _vp, _u32, _vp]),
+    "ngp_nerf_loss": (_int, [_vp, _vp, _vp, _f32, _u32, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ngp_nerf_rgb_backward": (_int, [_vp, _vp, _vp, _u32, _vp]),
+    "ngp_nerf_mid_backward": (_int, [_vp, _vp, _vp, _f32, _vp, _u32, _vp]),
+    "ngp_step_begin": (_int, [_vp, _f32, _f32, _vp]),
+    "ngp_step_end": (_int, [_vp, _vp]),
+    "ngp_found_inf": (_int, [_vp, _sz, _vp, _sz, _vp, _vp]),
+    "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _vp]),
+    "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
+    "ngp_density_ema": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
+    "ngp_packbits_mean": (_int, [_vp, _u32, _vp, _f32, _f32, _vp, _vp]),
     "ngp_umma_selftest": (_int, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp]),
 }
 
