@@ -253,8 +253,152 @@ class HashGridWorkload:
                 "sample": f"{n} x fwd+bwd of 2^16 points (same table), oracle/ngp_oracle.c with OpenMP on all host cores"}
 
 
-WORKLOADS = {"hashgrid": HashGridWorkload}
-DEFAULT_WORKLOAD = "hashgrid"
+# ==================================================================================================
+# workload: NeRF training step (BASELINE.json configs[1] at N=1, configs[2] at N>1)
+# ==================================================================================================
+class NerfTrainWorkload:
+    """`main_nerf -O --ff` step on the synthetic gyroid scene: 4096 rays/batch on one GPU (configs[1]); with N>1 ranks
+    2^18 rays/step global, data-parallel over rays, NCCL all-reduce of the table + MLP gradients (configs[2]).
+    The model is pre-trained for `--pretrain` steps before the warm-up so that the occupancy grid (and with it the
+    samples per ray) is that of a scene in training, not of the random initialisation."""
+    name = "nerf_train"
+    metric = "train rays/s"
+    unit = "rays/s"
+    dtype = "f16"
+
+    def __init__(self, args):
+        self.args = args
+        self.scaling = "weak" if args.rays else "strong"
+
+    def setup(self, dev, rank, world):
+        import torch
+        import nerf
+        from nerf import synthetic
+        self.torch, self.dev, self.world = torch, dev, world
+        self.N = self.args.rays or (4096 if world == 1 else (1 << 18) // world)
+        self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=self.N, device=dev, world_size=world, seed=0, use_graph=not self.args.no_graph)
+        n_batches = 16
+        views = max(16, n_batches * self.N // 4096)
+        o, d, gt = synthetic.make_pool(views, n_batches * self.N // views, dev, seed=1000 + rank)
+        tr.set_pool(o, d, gt)
+        self.pool_host = tuple(t.cpu().pin_memory() for t in (o, d, gt))
+        self.cursor = 0
+        for _ in range(self.args.pretrain):
+            tr.next_pool_batch()
+            tr.train_step()
+        torch.cuda.synchronize()
+        self.units_per_step = self.N
+        self.h2d_bytes = 3 * self.N * 3 * 4
+        self.d2h_bytes = 4
+        self.T = tr.T
+
+    def config(self, world):
+        tr = getattr(self, "tr", None)
+        c = {"workload": ("main_nerf -O --ff training step (hash grid 16x2 T=2^19 + FFMLP 64x2 / 64x3 + cuda_ray marcher, fp16 + GradScaler + Adam), "
+                          "synthetic 800x800 gyroid scene, " + ("4096 rays/batch, 1 GPU (configs[1])" if world == 1 and not self.args.rays else
+                                                                "2^18 rays/step global, data-parallel (configs[2])" if not self.args.rays else
+                                                                f"{self.args.rays} rays per GPU per step")),
+             "parallelism": f"dp{world}" + (" (NCCL all-reduce of fp16 table + fp32 MLP gradients)" if world > 1 else ""),
+             "l2": "flushed between steps (256 MiB memset outside the per-step events)", "pretrain_steps": self.args.pretrain}
+        if tr is not None:
+            c.update({"rays_per_gpu": self.N, "global_rays": self.N * world, "samples_per_ray": round(tr.mean_count / self.N, 2),
+                      "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph), "density_grid_update": f"every {tr.update_interval} steps, inside the timed region",
+                      "last_loss": tr.loss()})
+        return c
+
+    def step_device(self):
+        self.tr.next_pool_batch()
+        self.tr.train_step()
+
+    def step_e2e(self):
+        """Public API: NGPTrainer.train_step(rays_o, rays_d, gt) with pinned host batches, loss read back."""
+        o, d, g = self.pool_host
+        if self.cursor + self.N > o.shape[0]:
+            self.cursor = 0
+        sl = slice(self.cursor, self.cursor + self.N)
+        self.cursor += self.N
+        self.tr.train_step(o[sl], d[sl], g[sl])
+        return self.tr.loss()
+
+    def profile_mode(self, on):
+        """per-launch CUDA events cannot be recorded inside a graph replay: the profile pass runs the same launches eagerly."""
+        self._saved = getattr(self, "_saved", self.tr.use_graph)
+        self.tr.use_graph = False if on else self._saved
+
+    def launches_per_step(self):
+        """Kernels of this library in one step (graph replays do not pass through the host-side counter)."""
+        import ngp_abi as abi
+        saved, self.tr.use_graph = self.tr.use_graph, False
+        upd, self.tr.update_interval = self.tr.update_interval, 0
+        n0 = abi.launch_count()
+        self.step_device()
+        n = abi.launch_count() - n0
+        self.tr.use_graph, self.tr.update_interval = saved, upd
+        self.tr.global_step -= 1  # keep the density-grid cadence of the timed region
+        return n
+
+    def roofline(self, prof, peaks, steps):
+        """Dominant kernel (largest share of the step) against the roofline that bounds it.  Algorithmic work per launch,
+        S = samples actually marched per step (not the padded capacity), s = 2 B (fp16 table / activations):
+          k_grid_fwd / k_grid_bwd  S * (12 + 8*L*C*s + L*C*s) bytes          
+          k_adam                   n16 * (3*4 read + 3*4 write + 2 grad + 2 shadow) + n32 * 32 bytes
+          k_found_inf              n16 * 2 + n32 * 4 bytes
+          k_ffmlp_fwd              2 * W * S flop ; k_ffmlp_bwd  6 * W * S flop (recompute + dX + dW), W = weights of the net"""
+        tr = self.tr
+        S = max(1, tr.mean_count)
+        w_sig, w_col = tr.n_sig, tr.n_col
+        hb = S * (12 + 9 * tr.L * tr.C * 2)
+        table = {"k_grid_fwd": ("hbm", hb), "k_grid_bwd": ("hbm", hb), "k_adam": ("hbm", tr.n16 * 28 + tr.n32 * 32),
+                 "k_found_inf": ("hbm", tr.n16 * 2 + tr.n32 * 4),
+                 "k_ffmlp_fwd": ("tensor", 2 * (w_sig + w_col) / 2 * S), "k_ffmlp_bwd": ("tensor", 6 * (w_sig + w_col) / 2 * S)}
+        cand = {k: v for k, v in prof.items() if any(k.startswith(p) for p in table)}
+        if not cand:
+            return None
+        name = max(cand, key=lambda k: cand[k][1])
+        cnt, ms = cand[name]
+        bound, work = next(v for p, v in table.items() if name.startswith(p))
+        sec = ms / cnt * 1e-3
+        total_ms = sum(v[1] for v in prof.values())
+        if bound == "hbm":
+            ach, peak, unit = work / sec / 1e9, peaks["hbm_gbs"], "GB/s"
+        else:
+            ach, peak, unit = work / sec / 1e12, peaks["tflops"], "TFLOP/s"
+        return {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": None,
+                "peak_source": peaks["source"], "algorithmic_work_per_launch": work, "us_per_launch": sec * 1e6,
+                "share_of_step_kernel_time": ms / total_ms if total_ms else None, "samples_per_step": S}
+
+    # ---- CPU baseline: the oracle's restatement of the same step, all host cores, bounded sample ----
+    def cpu_baseline(self, budget_s=15.0):
+        from oracle import cpu_ref, nerf_step_ref as R
+        import scenes
+        cpu_ref.build()
+        offs, pls = cpu_ref.make_offsets(desired_resolution=2048)
+        rng = np.random.default_rng(0)
+        table = ((rng.random((offs[-1], 2)) * 2 - 1) * 1e-4).astype(np.float32)
+        k = np.sqrt(3 / 64)
+        st = R.RefState(table, ((rng.random(64 * (32 + 64 + 16)) * 2 - 1) * k).astype(np.float32),
+                        ((rng.random(64 * (32 + 128 + 16)) * 2 - 1) * k).astype(np.float32), offs, pls, 16)
+        H, n_rays = 128, 512
+        bits = scenes.bitfield_from_grid(scenes.density_grid(H=H), 0.01)
+        batches = []
+        for i in range(4):
+            ro, rd = scenes.camera_rays(n_rays, seed=i)
+            batches.append((ro, rd, rng.random((n_rays, 3)).astype(np.float32)))
+        R.train_step(st, *batches[0], bits, 1, H, n_rays * 128)  # warm-up
+        t_total, n, samples = 0.0, 0, 0
+        while t_total < budget_s and n < 64:
+            t0 = time.perf_counter()
+            _, ns = R.train_step(st, *batches[n % 4], bits, 1, H, n_rays * 128)
+            t_total += time.perf_counter() - t0
+            n += 1
+            samples += ns
+        return {"value": n_rays * n / t_total, "unit": self.unit, "cores": os.cpu_count(), "kind": "port",
+                "sample": f"{n} training steps of {n_rays} rays ({samples // max(1, n)} samples/step, analytic occupancy grid, full-size table and MLPs), "
+                          "oracle/nerf_step_ref.py: C+OpenMP hash grid / marcher / compositor, numpy MLPs and Adam"}
+
+
+WORKLOADS = {"hashgrid": HashGridWorkload, "nerf_train": NerfTrainWorkload}
+DEFAULT_WORKLOAD = "nerf_train"
 
 
 # ==================================================================================================
@@ -296,7 +440,8 @@ def run_reference(wl, args, rank, world):
     vals = [wl.cpu_baseline(budget_s=per) for _ in range(max(1, min(args.steps, 4)))]
     v = float(np.median([x["value"] for x in vals]))
     cb = dict(vals[0]); cb["value"] = v
-    wl.T = getattr(wl, "T", 0)
+    if not hasattr(wl, "T"):
+        wl.T = 6119864
     line = {"impl": "reference", "metric": wl.metric, "value": v, "unit": wl.unit, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
             "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world) if hasattr(wl, "enc") or True else {},
@@ -313,6 +458,9 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("NGP_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--points", type=int, default=0, help="override the per-GPU batch (development only)")
+    ap.add_argument("--rays", type=int, default=0, help="nerf_train: rays per GPU per step (default: configs[1]/[2])")
+    ap.add_argument("--pretrain", type=int, default=512, help="nerf_train: untimed optimisation steps before the warm-up")
+    ap.add_argument("--no-graph", action="store_true", help="nerf_train: launch the step eagerly instead of replaying CUDA graphs")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -321,8 +469,6 @@ def main():
     wl = WORKLOADS[args.workload](args)
     if args.impl == "reference":
         rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-        if hasattr(wl, "T") is False:
-            wl.T = 6119864
         run_reference(wl, args, rank, world)
         return
 
@@ -345,15 +491,21 @@ def main():
     n0 = abi.launch_count()
     ms_local = timed_region(wl, args.steps, world, flush)
     launches = (abi.launch_count() - n0) / args.steps
+    if hasattr(wl, "launches_per_step") and wl.launches_per_step.__func__ is not HashGridWorkload.launches_per_step:
+        launches = wl.launches_per_step()
     clocks = sampler.stop() if sampler else None
     ms = max_over_ranks(ms_local, world)
     units = sum_over_ranks(float(wl.units_per_step), world)
 
     # per-kernel durations, live, same region re-run with the library's per-launch CUDA events enabled
+    if hasattr(wl, "profile_mode"):
+        wl.profile_mode(True)
     abi.set_option("profile_events", 1)
     timed_region(wl, args.steps, world, flush)
     prof = abi.profile_collect()
     abi.set_option("profile_events", 0)
+    if hasattr(wl, "profile_mode"):
+        wl.profile_mode(False)
     roof = wl.roofline(prof, peaks, args.steps)
 
     # end to end through the plugin API, host buffers

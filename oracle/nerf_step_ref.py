@@ -1,0 +1,106 @@
+"""CPU restatement of ONE `main_nerf -O --ff` training step -- TEST INFRASTRUCTURE (oracle), never on the product path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / `--impl reference` legs may import this.
+Composes the per-op oracles of oracle/cpu_ref.py (C + OpenMP for the hash grid, marcher and compositor; numpy for the
+MLPs) in the order of /root/reference/nerf/renderer.py::run_cuda (:257-431, training branch :293-345),
+nerf/network_ff.py::forward (:51-74), nerf/utils.py::train_step (:497-590: MSE over rgb, mean) and the optimizer step
+(main_nerf.py:194 Adam(betas=(0.9, 0.99), eps=1e-15), GradScaler unscale) -- the same sequence
+torch-ngp_b200/nerf/trainer.py launches on the device.  Parity pinned through its parts: each per-op oracle is
+checked against the reference's own CUDA extensions (tests/test_vs_reference_ext.py, tests/golden/).
+"""
+import numpy as np
+
+from . import cpu_ref
+
+
+def _h(x, dtype=np.float32):
+    """fp16 rounding point (autocast boundary)."""
+    return np.asarray(x, np.float32).astype(np.float16).astype(dtype)
+
+
+class RefState:
+    """Parameters + Adam moments + loss scale, numpy."""
+
+    def __init__(self, table, sigma_w, color_w, offsets, per_level_scale, base_resolution, lr=1e-2, loss_scale=128.0):
+        self.table, self.sigma_w, self.color_w = table.astype(np.float32), sigma_w.astype(np.float32), color_w.astype(np.float32)
+        self.offsets, self.pls, self.H0 = np.asarray(offsets, np.int32), float(per_level_scale), int(base_resolution)
+        self.m = [np.zeros_like(p) for p in self.params()]
+        self.v = [np.zeros_like(p) for p in self.params()]
+        self.t, self.lr0, self.scale = 0, lr, loss_scale
+
+    def params(self):
+        return [self.table, self.sigma_w, self.color_w]
+
+
+def network_forward(st, xyzs, dirs, bound, density_scale=1.0):
+    """-> sigmas [M], rgbs [M,3] and the saved tensors for the backward (network_ff.py:51-74 under fp16 autocast)."""
+    x01 = ((xyzs + np.float32(bound)) / np.float32(2 * bound)).astype(np.float32)
+    enc_lbc, _ = cpu_ref.grid_encode_forward(x01, _h(st.table), st.offsets, st.pls, st.H0)
+    M = xyzs.shape[0]
+    enc = _h(np.transpose(enc_lbc, (1, 0, 2)).reshape(M, -1))
+    h, _ = cpu_ref.ffmlp_forward(enc, _h(st.sigma_w), 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
+    h = _h(h)
+    sigmas = (np.float32(density_scale) * np.exp(h[:, 0])).astype(np.float32)
+    cin = np.zeros((M, 32), np.float32)
+    cin[:, :16] = _h(cpu_ref.sh_encode(dirs, 4))
+    cin[:, 16:31] = h[:, 1:]
+    c, _ = cpu_ref.ffmlp_forward(cin, _h(st.color_w), 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
+    c = _h(c)
+    rgbs = _h(1.0 / (1.0 + np.exp(-c[:, :3])))
+    return sigmas, rgbs, dict(x01=x01, enc=enc, h=h, cin=cin, c=c)
+
+
+def forward_backward(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, bound=1.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
+                     noises=None, bg_color=1.0, T_thresh=1e-4, density_scale=1.0):
+    """-> loss, (g_table [T,C], g_sigma_w, g_color_w) carrying the loss scale, n_samples."""
+    N = rays_o.shape[0]
+    aabb = np.array([-bound] * 3 + [bound] * 3, np.float32)
+    nears, fars = cpu_ref.near_far_from_aabb(rays_o, rays_d, aabb, min_near)
+    xyzs, dirs, deltas, rays, counter = cpu_ref.march_rays_train(rays_o, rays_d, bound, bitfield, cascade, grid_size, nears, fars, M, noises,
+                                                                 dt_gamma, max_steps)
+    sigmas, rgbs, sv = network_forward(st, xyzs, dirs, bound, density_scale)
+    ws, depth, image = cpu_ref.composite_rays_train_forward(sigmas, rgbs, deltas, rays, T_thresh)
+    pred = image + (1 - ws)[:, None] * np.float32(bg_color)
+    diff = (pred - gt).astype(np.float32)
+    loss = float(np.mean(diff.astype(np.float64) ** 2))
+    g_image = (np.float32(st.scale) * 2.0 / (3.0 * N) * diff).astype(np.float32)
+    g_ws = -(g_image.sum(-1) * np.float32(bg_color)).astype(np.float32)
+    g_sig, g_rgb = cpu_ref.composite_rays_train_backward(g_ws, np.zeros(N, np.float32), g_image, sigmas, rgbs, deltas, rays, ws, depth, image,
+                                                         T_thresh)
+    g_c = np.zeros((M, 16), np.float32)
+    g_c[:, :3] = _h(g_rgb * rgbs * (1 - rgbs))
+    g_cin, g_col = cpu_ref.ffmlp_backward(g_c, sv["cin"], _h(st.color_w), 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
+    g_h = np.zeros((M, 16), np.float32)
+    g_h[:, 0] = g_sig * np.float32(density_scale) * np.exp(np.clip(sv["h"][:, 0], -15, 15))
+    g_h[:, 1:] = _h(g_cin)[:, 16:31]
+    g_h = _h(g_h)
+    g_enc, g_sw = cpu_ref.ffmlp_backward(g_h, sv["enc"], _h(st.sigma_w), 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
+    g_enc = _h(g_enc)
+    L = st.offsets.shape[0] - 1
+    g_lbc = np.ascontiguousarray(np.transpose(g_enc.reshape(M, L, -1), (1, 0, 2)))
+    g_table, _ = cpu_ref.grid_encode_backward(g_lbc, sv["x01"], _h(st.table), st.offsets, st.pls, st.H0)
+    return loss, (g_table, g_sw.astype(np.float32), g_col.astype(np.float32)), int(counter[0])
+
+
+def adam_step(st, grads, grad_div=1.0, beta1=0.9, beta2=0.99, eps=1e-15, decay_steps=30000):
+    """torch.optim.Adam + LambdaLR(0.1 ** min(iter / 30000, 1)) + GradScaler.unscale_ / skip on non-finite gradients."""
+    if not all(np.isfinite(g).all() for g in grads):
+        st.scale *= 0.5
+        return False
+    lr = st.lr0 * 0.1 ** min(st.t / decay_steps, 1.0)
+    st.t += 1
+    bc1, bc2 = 1 - beta1 ** st.t, 1 - beta2 ** st.t
+    for p, m, v, g in zip(st.params(), st.m, st.v, grads):
+        g = g.reshape(p.shape).astype(np.float32) / np.float32(st.scale * grad_div)
+        m *= beta1
+        m += (1 - beta1) * g
+        v *= beta2
+        v += (1 - beta2) * g * g
+        p -= (lr / bc1) * m / (np.sqrt(v) / np.sqrt(bc2) + eps)
+    return True
+
+
+def train_step(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, **kw):
+    loss, grads, n = forward_backward(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, **kw)
+    adam_step(st, grads)
+    return loss, n
