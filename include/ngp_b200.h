@@ -59,6 +59,13 @@ NGP_API int ngp_get_option(const char *key, int *value);
  * "profile_events" is 1 (not during CUDA-graph capture) -- per-kernel CUDA-event durations, returned as
  * text lines "<kernel> <count> <total_ms>\n" (the call synchronises on the recorded events and clears them). */
 NGP_API long long ngp_launch_count(void);
+/* Device-side batch size for the per-sample ops.  While a non-NULL pointer is set (process-wide: autograd calls the
+ * backward ops from its own threads), the kernels of
+ * ngp_grid_encode_forward / _backward, ngp_ffmlp_forward / _inference / _backward and the ngp_nerf_* glue process only the first min(B, *count_dev) rows; *count_dev is read ON THE DEVICE when the kernel runs, so
+ * the sample counter that ngp_march_rays_train just wrote (counter[0]) can bound the rest of a captured step without a
+ * host read-back.  Rows past the limit are neither read nor written.  The reference sizes these launches from a host
+ * copy of the counter (raymarching.py:221-226, a D2H sync) or from a running mean (padded work).  NULL clears it. */
+NGP_API int ngp_set_batch_limit(const int32_t *count_dev);
 NGP_API int ngp_profile_collect(char *buf, size_t buf_bytes);
 
 /* ---------------------------------------------------------------------------------------------

@@ -174,3 +174,45 @@ def test_step_matches_cpu_oracle_step():
         torch.cuda.synchronize()
         assert _rel(tr.embeddings, torch.from_numpy(st.table).cuda()) < 1e-4
         assert _rel(tr.color_w, torch.from_numpy(st.color_w).cuda()) < 1e-5
+
+
+def test_device_side_batch_limit():
+    """ngp_set_batch_limit: the per-sample kernels stop at min(B, *count) read on the device; rows past it are untouched."""
+    import ngp_abi as abi
+    import gridencoder
+    import ffmlp
+    B, n = 5000, 3217
+    cnt = torch.tensor([n, 0], dtype=torch.int32, device="cuda")
+    enc = gridencoder.GridEncoder(num_levels=16, level_dim=2, base_resolution=16, log2_hashmap_size=15, desired_resolution=512).cuda()
+    with torch.no_grad():
+        enc.embeddings.uniform_(-1, 1)
+    x = torch.rand(B, 3, device="cuda") * 2 - 1
+    net = ffmlp.FFMLP(32, 16, 64, 2).cuda().train()
+    g = torch.randn(B, 16, device="cuda").half()
+
+    def run(xs, gs):
+        for p in (enc.embeddings, net.weights):
+            p.grad = None
+        with torch.autocast("cuda", dtype=torch.half):
+            y = net(enc(xs, bound=1))
+        y.backward(gs)
+        return y.detach().clone(), enc.embeddings.grad.clone(), net.weights.grad.clone()
+
+    y_ref, ge_ref, gw_ref = run(x[:n].contiguous(), g[:n].contiguous())
+    abi.check(abi.lib.ngp_set_batch_limit(cnt.data_ptr()))
+    try:
+        y, ge, gw = run(x, g)
+    finally:
+        abi.check(abi.lib.ngp_set_batch_limit(None))
+    assert torch.equal(y[:n], y_ref)
+    assert _rel(gw, gw_ref) < 1e-6
+    assert _rel(ge, ge_ref) < 1e-2  # fp16 atomics, order-dependent
+    # a limit above B is clamped to B
+    cnt[0] = 10 * B
+    abi.check(abi.lib.ngp_set_batch_limit(cnt.data_ptr()))
+    try:
+        y2, _, gw2 = run(x, g)
+    finally:
+        abi.check(abi.lib.ngp_set_batch_limit(None))
+    y_full, _, gw_full = run(x, g)
+    assert torch.equal(y2, y_full) and _rel(gw2, gw_full) < 1e-6

@@ -60,8 +60,19 @@ def test_packbits_bit_exact(oracle, shape):
     assert np.array_equal(buf[1:].cpu().numpy(), oracle.packbits(g, 0.3))
 
 
+@pytest.fixture(params=[1, 0], ids=["warp_per_ray", "thread_per_ray"])
+def variant(request):
+    """Both implementations of the training marcher / compositor must satisfy the same contract."""
+    import ngp_abi as abi
+    abi.set_option("march_variant", request.param)
+    abi.set_option("composite_variant", request.param)
+    yield request.param
+    abi.set_option("march_variant", -1)
+    abi.set_option("composite_variant", -1)
+
+
 @pytest.mark.parametrize("name,dt_gamma,perturb", [("c1", 0.0, False), ("c1", 1.0 / 128, True), ("c2", 0.0, True), ("c2", 1.0 / 128, False)])
-def test_march_rays_train_bit_exact(oracle, scene, name, dt_gamma, perturb):
+def test_march_rays_train_bit_exact(oracle, scene, name, dt_gamma, perturb, variant):
     import raymarching as rm
     s = scene[name]
     N = s["o"].shape[0]
@@ -85,7 +96,7 @@ def test_march_rays_train_bit_exact(oracle, scene, name, dt_gamma, perturb):
     assert counter[1].item() == 2 * N and counter[0].item() == 2 * ref[4][0]
 
 
-def test_march_rays_train_budget_and_api(oracle, scene):
+def test_march_rays_train_budget_and_api(oracle, scene, variant):
     import raymarching as rm
     s = scene["c1"]
     N = s["o"].shape[0]
@@ -109,7 +120,7 @@ def test_march_rays_train_budget_and_api(oracle, scene):
     assert out[3].shape == (0, 3)
 
 
-def test_composite_train_forward_backward(oracle, scene):
+def test_composite_train_forward_backward(oracle, scene, variant):
     import raymarching as rm
     s = scene["c1"]
     N = 2048
@@ -203,3 +214,27 @@ def test_raymarching_error_behaviour(scene):
     s = scene["c1"]
     n, f = rm.near_far_from_aabb(torch.from_numpy(s["o"][:10]), torch.from_numpy(s["d"][:10]), T(s["aabb"]), 0.2)
     assert n.is_cuda and np.array_equal(n.cpu().numpy(), s["nears"][:10])
+
+
+@pytest.mark.parametrize("max_steps,dt_gamma", [(40, 0.0), (100, 1.0 / 64), (1024, 0.0)])
+def test_march_rays_train_step_cap_and_full_occupancy(oracle, scene, variant, max_steps, dt_gamma):
+    """Fully occupied grid: every ray hits the max_steps cap (the `step < max_steps` half of the loop condition),
+    runs of occupied points span whole 32-point chunks, and nothing is skipped."""
+    import raymarching as rm
+    s = scene["c2"]
+    N = 1000
+    bits = np.full_like(s["bits"], 0xFF)
+    bits[::7] = 0x5A  # a few holes so that skips and runs interleave
+    noises = np.random.default_rng(5).random(N).astype(np.float32)
+    M = N * max_steps
+    ref = oracle.march_rays_train(s["o"][:N], s["d"][:N], s["bound"], bits, s["C"], s["H"], s["nears"][:N], s["fars"][:N], M, noises, dt_gamma, max_steps)
+    xyzs, dirs, deltas = torch.zeros(M, 3, device=DEV), torch.zeros(M, 3, device=DEV), torch.zeros(M, 2, device=DEV)
+    rays = torch.empty(N, 3, dtype=torch.int32, device=DEV)
+    counter = torch.zeros(2, dtype=torch.int32, device=DEV)
+    rm._backend.march_rays_train(T(s["o"][:N]), T(s["d"][:N]), T(bits), s["bound"], dt_gamma, max_steps, N, s["C"], s["H"], M, T(s["nears"][:N]),
+                                 T(s["fars"][:N]), xyzs, dirs, deltas, rays, counter, T(noises))
+    assert np.array_equal(counter.cpu().numpy(), ref[4])
+    assert (ref[3][:, 2] == max_steps).any()
+    assert np.array_equal(rays.cpu().numpy(), ref[3])
+    assert np.array_equal(xyzs.cpu().numpy(), ref[0])
+    assert np.array_equal(deltas.cpu().numpy(), ref[2])

@@ -29,7 +29,8 @@ static std::map<std::string, int> &options() {
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
-        {"march_block", 128},
+        {"march_variant", -1},         // training marcher: -1 auto / 1 warp per ray (ballot replay of the skip rule), 0 thread per ray
+        {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
         {"ffmlp_available", 1},
         {"ffmlp_fwd_pipes", 0},        // > 0: cap on the tile pipelines per CTA of the FFMLP forward (tuning)
         {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in
@@ -73,6 +74,11 @@ prof_scope::~prof_scope() {
     cudaEventRecord(g_prof_recs[slot].b, st);
 }
 
+// process-wide on purpose: autograd runs backward functions on its own worker threads
+static std::atomic<const int *> g_batch_limit{nullptr};
+const int *batch_limit() { return g_batch_limit.load(std::memory_order_acquire); }
+void set_batch_limit(const int *p) { g_batch_limit.store(p, std::memory_order_release); }
+
 int sm_count() {
     static int cached[64] = {0};
     int dev = 0;
@@ -106,6 +112,11 @@ int ngp_set_option(const char *key, int value) {
 }
 
 long long ngp_launch_count(void) { return ngp::g_launches.load(); }
+
+int ngp_set_batch_limit(const int32_t *count_dev) {
+    ngp::set_batch_limit(reinterpret_cast<const int *>(count_dev));
+    return NGP_OK;
+}
 
 // Synchronises the recorded events and writes one line per kernel name: "<name> <count> <total_ms>\n".
 // Returns the number of bytes written (excluding the NUL), or a negative error code; clears the records.

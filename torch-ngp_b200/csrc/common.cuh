@@ -12,6 +12,17 @@ namespace ngp {
 void set_error(const char *fmt, ...);
 int get_option(const char *key, int dflt);
 int sm_count();  // SMs of the current device (148 on B200), cached
+const int *batch_limit();  // device pointer set by ngp_set_batch_limit (process-wide), or nullptr
+void set_batch_limit(const int *p);
+
+// Effective batch of a per-sample kernel: min(B, *limit * mult) when a device-side limit is set.  The launch is
+// still sized for B; blocks past the limit exit at once.  `limit` was written by an earlier kernel on the stream.
+__device__ __forceinline__ uint32_t eff_batch(uint32_t B, const int *__restrict__ limit, uint32_t mult = 1u) {
+    if (limit == nullptr) return B;
+    const int v = __ldg(limit);
+    const unsigned long long lim = (unsigned long long)(v > 0 ? v : 0) * mult;
+    return lim < B ? (uint32_t)lim : B;
+}
 
 // Per-launch accounting (abi.cu).  Always counts launches (ngp_launch_count); when the option
 // "profile_events" is 1 it also brackets the launch with CUDA events on `st`, read back through

@@ -209,10 +209,13 @@ __device__ __forceinline__ void pipe_sync(uint32_t id) { asm volatile("bar.sync 
 // faster single chain.  Pipeline p: rows = its tile, TMEM columns [p*accw, (p+1)*accw), mbarrier p, named barrier 1+p.
 template <typename WT, int HID>
 __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
-                                                    const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, uint32_t accw) {
+                                                    const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, uint32_t accw,
+                                                    const int *__restrict__ limit) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar[8];
+    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_set_batch_limit)
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
     const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
     const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes;
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
     uint32_t phase = 0;
 
     for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
-        load_rows_async(sx, x, tile * kTileRows, m.B, m.in, row, 128);
+        load_rows_async(sx, x, tile * kTileRows, Beff, m.in, row, 128);
         cp_async_commit();
         cp_async_wait<0>();
         fence_proxy_async();
@@ -265,7 +268,7 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
         phase ^= 1u;
         fence_after_sync();
         const uint32_t grow = tile * kTileRows + row;
-        epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, grow < m.B);
+        epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, grow < Beff);
         fence_before_sync();
         pipe_sync(bid);  // accumulator drained before this pipeline's next first MMA overwrites it
     }
@@ -296,10 +299,12 @@ template <typename WT, int HID>
 __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                    __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                    int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
-                                                   uint32_t nbuf) {
+                                                   uint32_t nbuf, const int *__restrict__ limit) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
+    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_set_batch_limit)
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
     __shared__ __align__(8) uint64_t s_bar;
     constexpr int NS = split_of<HID>::NS, CW = HID / NS;
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
@@ -321,8 +326,8 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
 
     uint32_t tile = blockIdx.x;
     if (tile < ntiles && nbuf == 2) {
-        load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
-        load_rows_async(sgo[0], grad, tile * kTileRows, m.B, m.out, tid, blockDim.x);
+        load_rows_async(sx[0], x, tile * kTileRows, Beff, m.in, tid, blockDim.x);
+        load_rows_async(sgo[0], grad, tile * kTileRows, Beff, m.out, tid, blockDim.x);
     }
     cp_async_commit();
     stage_weights<WT>(sw, w, m, tid, blockDim.x);
@@ -343,14 +348,14 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
         if (nbuf == 2) {
             const uint32_t next = tile + gridDim.x;
             if (next < ntiles) {
-                load_rows_async(sx[buf ^ 1u], x, next * kTileRows, m.B, m.in, tid, blockDim.x);
-                load_rows_async(sgo[buf ^ 1u], grad, next * kTileRows, m.B, m.out, tid, blockDim.x);
+                load_rows_async(sx[buf ^ 1u], x, next * kTileRows, Beff, m.in, tid, blockDim.x);
+                load_rows_async(sgo[buf ^ 1u], grad, next * kTileRows, Beff, m.out, tid, blockDim.x);
             }
             cp_async_commit();
             cp_async_wait<1>();
         } else {
-            load_rows_async(sx[0], x, tile * kTileRows, m.B, m.in, tid, blockDim.x);
-            load_rows_async(sgo[0], grad, tile * kTileRows, m.B, m.out, tid, blockDim.x);
+            load_rows_async(sx[0], x, tile * kTileRows, Beff, m.in, tid, blockDim.x);
+            load_rows_async(sgo[0], grad, tile * kTileRows, Beff, m.out, tid, blockDim.x);
             cp_async_commit();
             cp_async_wait<0>();
         }
@@ -410,7 +415,7 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
         if (calc_dx) {
             const uint32_t grow = tile * kTileRows + row;
             for (uint32_t c0 = cg * 16u; c0 < m.in; c0 += NS * 16u)
-                epi_to_global(trow + tc.acc, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < m.B);
+                epi_to_global(trow + tc.acc, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < Beff);
         }
         fence_before_sync();
         __syncthreads();
@@ -517,7 +522,7 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
         rc = set_smem(k_ffmlp_fwd<WT_, HID_>, smem);                                                                         \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_fwd", st);                                                                                         \
-        k_ffmlp_fwd<WT_, HID_><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw); \
+        k_ffmlp_fwd<WT_, HID_><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
     }
 #define NGP_FWD_HID(WT_)                                         \
     switch (hid) {                                               \
@@ -607,7 +612,7 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd", st);                                                                                         \
         k_ffmlp_bwd<WT_, HID_><<<grid, 128 * split_of<HID_>::NS, smem, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf);   \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf, batch_limit());   \
     }
 #define NGP_BWD_HID(WT_)                                         \
     switch (hidden_dim) {                                        \

@@ -96,7 +96,8 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
                                                           const int *__restrict__ offsets, T *__restrict__ outputs,
                                                           uint32_t B, uint32_t L, float S, uint32_t H,
                                                           T *__restrict__ dy_dx, uint32_t gridtype, bool align_corners,
-                                                          uint32_t interp, int layout, bool pos_deriv_quirk) {
+                                                          uint32_t interp, int layout, bool pos_deriv_quirk, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     using A = typename acc_of<T>::type;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -223,7 +224,8 @@ template <typename T, uint32_t D, uint32_t C>
 __global__ void __launch_bounds__(256) k_grid_bwd_generic(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                           const int *__restrict__ offsets, T *__restrict__ grad_grid,
                                                           uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
-                                                          bool align_corners, uint32_t interp, int layout) {
+                                                          bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     using A = typename acc_of<T>::type;
     constexpr uint32_t N_C = C < 2 ? C : 2;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;

@@ -174,7 +174,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) k_grid_fwd_d3c2(const float *__restrict__ inputs, const T *__restrict__ grid,
                                                        const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B,
                                                        uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                                                       uint32_t interp, int layout, uint32_t level_begin) {
+                                                       uint32_t interp, int layout, uint32_t level_begin, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint32_t level = level_begin + blockIdx.y;
@@ -201,7 +202,8 @@ template <typename T>
 __global__ void __launch_bounds__(1024) k_grid_fwd_d3c2_smem(const float *__restrict__ inputs, const T *__restrict__ grid,
                                                              const int *__restrict__ offsets, T *__restrict__ outputs,
                                                              uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
-                                                             bool align_corners, uint32_t interp, int layout) {
+                                                             bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *tab = reinterpret_cast<T *>(smem_raw);
     const uint32_t level = blockIdx.y;
@@ -258,7 +260,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) k_grid_bwd_d3c2(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                        const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B,
                                                        uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                                                       uint32_t interp, int layout, uint32_t level_begin, int warp_agg) {
+                                                       uint32_t interp, int layout, uint32_t level_begin, int warp_agg, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x is a multiple of 32: warps exit whole or not at all
     const uint32_t level = level_begin + blockIdx.y;
     const level_t lv = level_consts(offsets, level, S, H);
@@ -317,7 +320,8 @@ template <typename T>
 __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                              const int *__restrict__ offsets, T *__restrict__ grad_grid,
                                                              uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
-                                                             bool align_corners, uint32_t interp, int layout) {
+                                                             bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *acc = reinterpret_cast<float *>(smem_raw);
     const uint32_t level = blockIdx.y;
@@ -447,7 +451,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restrict__ inputs, const T *__restrict__ grid,
                                                            const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B,
                                                            uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                                                           uint32_t interp, int layout) {
+                                                           uint32_t interp, int layout, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint32_t l0 = blockIdx.y * 4;
@@ -479,7 +484,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                            const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B,
                                                            uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                                                           uint32_t interp, int layout, int warp_agg) {
+                                                           uint32_t interp, int layout, int warp_agg, const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t l0 = blockIdx.y * 4;
     float x0 = 0.f, x1 = 0.f, x2 = 0.f;

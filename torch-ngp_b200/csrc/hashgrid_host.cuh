@@ -13,10 +13,10 @@ int launch_fwd_generic(const float *inputs, const T *emb, const int *offsets, T 
     const dim3 grid(div_round_up(B, 256u), L, 1);
     const bool quirk = get_option("hashgrid_ref_pos_deriv_quirk", 0) != 0;
     switch (C) {
-        case 1: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
-        case 2: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
-        case 4: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
-        case 8: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk); } break;
+        case 1: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
+        case 2: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
+        case 4: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 4><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
+        case 8: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 8><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
         default: set_error("GridEncoding: C must be 1, 2, 4, or 8."); return NGP_EINVAL;
     }
     NGP_CHECK_LAUNCH();
@@ -32,7 +32,7 @@ int launch_bwd_generic(const T *grad, const float *inputs, const int *offsets, T
     const uint32_t gi = div_round_up(B * D, 256u);
 #define NGP_BWD_CASE(CC)                                                                                                  \
     case CC:                                                                                                              \
-        { NGP_PROF("k_grid_bwd_generic", st); k_grid_bwd_generic<T, D, CC><<<grid, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout); } \
+        { NGP_PROF("k_grid_bwd_generic", st); k_grid_bwd_generic<T, D, CC><<<grid, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); } \
         if (dy_dx) { NGP_PROF("k_input_bwd", st); k_input_bwd<T, D, CC><<<gi, 256, 0, st>>>(grad, dy_dx, g_in, B, L, layout); }                            \
         break;
     switch (C) {
@@ -96,7 +96,7 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
              float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     const int variant = get_option("hashgrid_fwd_variant", -1);
     if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
-        { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout); }
+        { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
@@ -113,12 +113,12 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
         nb = nb < 1 ? 1 : nb;
         const uint32_t need = div_round_up(B, 1024u);
         nb = nb > need ? need : nb;
-        { NGP_PROF("k_grid_fwd_d3c2_smem", st); k_grid_fwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout); }
+        { NGP_PROF("k_grid_fwd_d3c2_smem", st); k_grid_fwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
     }
     if (ns < L) {
         { NGP_PROF("k_grid_fwd_d3c2", st); k_grid_fwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac,
-                                                                                 interp, layout, ns); }
+                                                                                 interp, layout, ns, batch_limit()); }
         NGP_CHECK_LAUNCH();
     }
     return NGP_OK;
@@ -130,7 +130,7 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
     const int variant = get_option("hashgrid_bwd_variant", -1);
     if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
-        { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg); }
+        { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, batch_limit()); }
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
@@ -147,13 +147,13 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         nb = nb < 1 ? 1 : nb;
         const uint32_t need = div_round_up(B, 1024u);
         nb = nb > need ? need : nb;
-        { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout); }
+        { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
     }
     if (ns < L) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
         { NGP_PROF("k_grid_bwd_d3c2", st); k_grid_bwd_d3c2<T><<<dim3(div_round_up(B, 256u), L - ns, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac,
-                                                                                 interp, layout, ns, warp_agg); }
+                                                                                 interp, layout, ns, warp_agg, batch_limit()); }
         NGP_CHECK_LAUNCH();
     }
     return NGP_OK;

@@ -20,7 +20,8 @@ __device__ __forceinline__ uint32_t h2(float a, float b) {
 __device__ __forceinline__ float2 unh2(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2 *>(&u)); }
 
 // x01 = (xyz + bound) / (2 bound)          (gridencoder/grid.py:807)
-__global__ void __launch_bounds__(256) k_nerf_x01(const float *__restrict__ xyzs, float bound, float *__restrict__ x01, uint32_t n3) {
+__global__ void __launch_bounds__(256) k_nerf_x01(const float *__restrict__ xyzs, float bound, float *__restrict__ x01, uint32_t n3, const int *__restrict__ limit) {
+    n3 = eff_batch(n3, limit, 3u);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n3) x01[i] = (xyzs[i] + bound) / (2 * bound);
 }
@@ -28,7 +29,8 @@ __global__ void __launch_bounds__(256) k_nerf_x01(const float *__restrict__ xyzs
 // h [M,16] f16 (sigma net output), dirs [M,3]  ->  sigmas [M] f32 = density_scale * exp(h0),
 // cin [M,32] f16 = [SH degree 4 of dir (16) | h1..h15 | 0]
 __global__ void __launch_bounds__(256) k_nerf_mid_fwd(const uint4 *__restrict__ h, const float *__restrict__ dirs, float density_scale,
-                                                      float *__restrict__ sigmas, uint4 *__restrict__ cin, uint32_t M) {
+                                                      float *__restrict__ sigmas, uint4 *__restrict__ cin, uint32_t M, const int *__restrict__ limit) {
+    M = eff_batch(M, limit);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= M) return;
     const uint4 a = __ldg(h + 2 * (size_t)i), b = __ldg(h + 2 * (size_t)i + 1);
@@ -54,7 +56,8 @@ __global__ void __launch_bounds__(256) k_nerf_mid_fwd(const uint4 *__restrict__ 
 }
 
 // c [M,16] f16 (colour net output) -> rgbs [M,3] f32 = sigmoid(c[0..2])
-__global__ void __launch_bounds__(256) k_nerf_rgb_fwd(const uint2 *__restrict__ c, float *__restrict__ rgbs, uint32_t M) {
+__global__ void __launch_bounds__(256) k_nerf_rgb_fwd(const uint2 *__restrict__ c, float *__restrict__ rgbs, uint32_t M, const int *__restrict__ limit) {
+    M = eff_batch(M, limit);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= M) return;
     const uint2 u = __ldg(c + 4 * (size_t)i);  // first 4 halves of the 32-byte row
@@ -95,7 +98,8 @@ __global__ void __launch_bounds__(256) k_nerf_loss(const float *__restrict__ ima
 
 // grad_rgbs [M,3] f32, rgbs [M,3] f32 -> grad_c [M,16] f16: g * rgb (1 - rgb) in columns 0..2, zeros elsewhere
 __global__ void __launch_bounds__(256) k_nerf_rgb_bwd(const float *__restrict__ grad_rgbs, const float *__restrict__ rgbs,
-                                                      uint4 *__restrict__ grad_c, uint32_t M) {
+                                                      uint4 *__restrict__ grad_c, uint32_t M, const int *__restrict__ limit) {
+    M = eff_batch(M, limit);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= M) return;
     float g[3];
@@ -113,7 +117,8 @@ __global__ void __launch_bounds__(256) k_nerf_rgb_bwd(const float *__restrict__ 
 //   col 0 = grad_sigma * density_scale * exp(clamp(h0, -15, 15)) ; cols 1..15 = grad_cin[16..30]
 __global__ void __launch_bounds__(256) k_nerf_mid_bwd(const float *__restrict__ grad_sigmas, const uint4 *__restrict__ h,
                                                       const uint4 *__restrict__ grad_cin, float density_scale, uint4 *__restrict__ grad_h,
-                                                      uint32_t M) {
+                                                      uint32_t M, const int *__restrict__ limit) {
+    M = eff_batch(M, limit);
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= M) return;
     const float h0 = unh2(__ldg(reinterpret_cast<const uint32_t *>(h + 2 * (size_t)i))).x;
@@ -278,7 +283,7 @@ int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *s
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(xyzs && x01, "nerf_x01: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
-    { NGP_PROF("k_nerf_x01", st); k_nerf_x01<<<NGP_GRID1(3 * M)>>>(xyzs, bound, x01, 3 * M); }
+    { NGP_PROF("k_nerf_x01", st); k_nerf_x01<<<NGP_GRID1(3 * M)>>>(xyzs, bound, x01, 3 * M, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -288,7 +293,7 @@ int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, 
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(h && dirs && sigmas && cin, "nerf_mid_forward: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
-    { NGP_PROF("k_nerf_mid_fwd", st); k_nerf_mid_fwd<<<NGP_GRID1(M)>>>((const uint4 *)h, dirs, density_scale, sigmas, (uint4 *)cin, M); }
+    { NGP_PROF("k_nerf_mid_fwd", st); k_nerf_mid_fwd<<<NGP_GRID1(M)>>>((const uint4 *)h, dirs, density_scale, sigmas, (uint4 *)cin, M, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -298,7 +303,7 @@ int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream) {
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(c && rgbs, "nerf_rgb_forward: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
-    { NGP_PROF("k_nerf_rgb_fwd", st); k_nerf_rgb_fwd<<<NGP_GRID1(M)>>>((const uint2 *)c, rgbs, M); }
+    { NGP_PROF("k_nerf_rgb_fwd", st); k_nerf_rgb_fwd<<<NGP_GRID1(M)>>>((const uint2 *)c, rgbs, M, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -319,7 +324,7 @@ int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(grad_rgbs && rgbs && grad_c, "nerf_rgb_backward: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
-    { NGP_PROF("k_nerf_rgb_bwd", st); k_nerf_rgb_bwd<<<NGP_GRID1(M)>>>(grad_rgbs, rgbs, (uint4 *)grad_c, M); }
+    { NGP_PROF("k_nerf_rgb_bwd", st); k_nerf_rgb_bwd<<<NGP_GRID1(M)>>>(grad_rgbs, rgbs, (uint4 *)grad_c, M, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
@@ -330,7 +335,7 @@ int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *g
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(grad_sigmas && h && grad_cin && grad_h, "nerf_mid_backward: null pointer argument");
     cudaStream_t st = (cudaStream_t)stream;
-    { NGP_PROF("k_nerf_mid_bwd", st); k_nerf_mid_bwd<<<NGP_GRID1(M)>>>(grad_sigmas, (const uint4 *)h, (const uint4 *)grad_cin, density_scale, (uint4 *)grad_h, M); }
+    { NGP_PROF("k_nerf_mid_bwd", st); k_nerf_mid_bwd<<<NGP_GRID1(M)>>>(grad_sigmas, (const uint4 *)h, (const uint4 *)grad_cin, density_scale, (uint4 *)grad_h, M, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

@@ -213,5 +213,6 @@ __global__ void k_packbits_tail(const float *__restrict__ grid, uint32_t n_begin
 }  // namespace ngp
 
 #include "raymarch_train.cuh"
+#include "raymarch_warp.cuh"
 #include "raymarch_infer.cuh"
 #include "raymarch_host.cuh"

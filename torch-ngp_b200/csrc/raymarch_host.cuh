@@ -68,7 +68,7 @@ int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *b
 }
 
 size_t ngp_march_rays_train_workspace_bytes(uint32_t N) {
-    return ngp::scan_ws_bytes(ngp::div_round_up(N, (uint32_t)ngp::kMarchBlock));
+    return ngp::scan_ws_bytes(ngp::div_round_up(N, (uint32_t)ngp::kWarpRays));  // the warp-per-ray variant has the most blocks
 }
 
 int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
@@ -81,12 +81,22 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
                   "march_rays_train: null pointer argument");
     NGP_CHECK_ARG(C >= 1 && C <= 16 && H >= 1 && H <= 1024, "march_rays_train: C=%u / H=%u out of range", C, H);
     NGP_CHECK_ARG(aligned(deltas, 8), "march_rays_train: deltas must be 8-byte aligned");
-    const uint32_t nb = div_round_up(N, (uint32_t)kMarchBlock);
+    const bool warp = get_option("march_variant", -1) != 0;  // -1 auto / 1: warp per ray; 0: thread per ray
+    const uint32_t nb = div_round_up(N, warp ? (uint32_t)kWarpRays : (uint32_t)kMarchBlock);
     NGP_CHECK_ARG(workspace && workspace_bytes >= scan_ws_bytes(nb), "march_rays_train: workspace too small (%zu < %zu bytes)",
                   workspace_bytes, scan_ws_bytes(nb));
     cudaStream_t st = (cudaStream_t)stream;
     march_ws_t *ws = reinterpret_cast<march_ws_t *>(workspace);
     NGP_CHECK_CUDA(cudaMemsetAsync(ws, 0, 2 * sizeof(uint32_t), st));
+    if (warp) {
+        { NGP_PROF("k_march_train_count_warp", st); k_march_train_count_warp<<<nb, kWarpRays * 32, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars,
+                                                                  noises, rays, counter, ws); }
+        NGP_CHECK_LAUNCH();
+        { NGP_PROF("k_march_train_write_warp", st); k_march_train_write_warp<<<nb, kWarpRays * 32, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears,
+                                                                  fars, noises, xyzs, dirs, deltas, rays, ws); }
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     { NGP_PROF("k_march_train_count", st); k_march_train_count<<<nb, kMarchBlock, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, noises,
                                                    rays, counter, ws); }
     NGP_CHECK_LAUNCH();
@@ -103,6 +113,12 @@ int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, con
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(rays && weights_sum && depth && image, "composite_rays_train_forward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas), "composite_rays_train_forward: null sample buffers with M=%u", M);
+    if (get_option("composite_variant", -1) != 0) {
+        { NGP_PROF("k_composite_train_fwd_warp", (cudaStream_t)stream); k_composite_train_fwd_warp<<<div_round_up(N, (uint32_t)kWarpRays), kWarpRays * 32, 0, (cudaStream_t)stream>>>(
+            sigmas, rgbs, deltas, rays, M, N, T_thresh, weights_sum, depth, image); }
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     { NGP_PROF("k_composite_train_fwd", (cudaStream_t)stream); k_composite_train_fwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(sigmas, rgbs, deltas, rays, M, N, T_thresh,
                                                                                  weights_sum, depth, image); }
     NGP_CHECK_LAUNCH();
@@ -119,6 +135,12 @@ int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float
                   "composite_rays_train_backward: null pointer argument");
     NGP_CHECK_ARG(M == 0 || (sigmas && rgbs && deltas && grad_sigmas && grad_rgbs),
                   "composite_rays_train_backward: null sample buffers with M=%u", M);
+    if (get_option("composite_variant", -1) != 0) {
+        { NGP_PROF("k_composite_train_bwd_warp", (cudaStream_t)stream); k_composite_train_bwd_warp<<<div_round_up(N, (uint32_t)kWarpRays), kWarpRays * 32, 0, (cudaStream_t)stream>>>(
+            grad_weights_sum, grad_depth, grad_image, sigmas, rgbs, deltas, rays, weights_sum, depth, image, M, N, T_thresh, grad_sigmas, grad_rgbs); }
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     { NGP_PROF("k_composite_train_bwd", (cudaStream_t)stream); k_composite_train_bwd<<<div_round_up(N, 128u), 128, 0, (cudaStream_t)stream>>>(
         grad_weights_sum, grad_depth, grad_image, sigmas, rgbs, deltas, rays, weights_sum, depth, image, M, N, T_thresh,
         grad_sigmas, grad_rgbs); }

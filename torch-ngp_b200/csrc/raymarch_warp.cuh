@@ -1,0 +1,345 @@
+// raymarch_warp.cuh -- warp-per-ray training marcher and compositor.  Included by raymarch.cu only.
+//
+// Why.  With 4096 rays per batch a thread-per-ray marcher keeps one warp per SM busy and every loop iteration waits
+// for a dependent bitfield load: ~280 us per pass on B200 for ~150 samples/ray.  The stepping rule of the reference
+// (raymarching.cu:360-399) only ever moves t by t <- t + clamp(t * dt_gamma, dt_min, dt_max), in the occupied branch
+// and in the empty-voxel skip loop alike, so the sequence of visited t values does not depend on the occupancy; the
+// occupancy only decides which of them are TESTED (those not swallowed by a skip) and, of the tested, which are
+// emitted.  A warp therefore takes 32 consecutive t values of one ray, evaluates the 32 occupancy tests (and voxel
+// exit times) in parallel with exactly the reference's per-point arithmetic, and then replays the skip rule on the
+// ballots: a handful of warp-uniform integer steps per chunk, no memory access.  Samples, deltas and counts are
+// bit-identical to the sequential loop; placement is in ray order as in raymarch_train.cuh.
+#pragma once
+
+namespace ngp {
+namespace {
+
+constexpr int kWarpRays = 8;  // rays (= warps) per block
+
+__device__ __forceinline__ float next_t(float t, const march_consts_t &c) {
+    return __fadd_rn(t, clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max));
+}
+
+// The body of one loop iteration at t (reference :360-392) without the t update: occupancy, sample position, step
+// size, and for an empty voxel the exit time tt.
+__device__ __forceinline__ bool test_point(const ray_t &r, const march_consts_t &c, float t, float &x, float &y, float &z, float &dt, float &tt) {
+    x = clampf(__fmaf_rn(t, r.dx, r.ox), -c.bound, c.bound);
+    y = clampf(__fmaf_rn(t, r.dy, r.oy), -c.bound, c.bound);
+    z = clampf(__fmaf_rn(t, r.dz, r.oz), -c.bound, c.bound);
+    dt = clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max);
+    const int level = max(mip_of(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), c.Cf), mip_of(__fmul_rn(__fmul_rn(dt, c.Hf), 0.5f), c.Cf));
+    const float mip_bound = fminf(scalbnf(1.0f, level), c.bound);
+    const float mip_rbound = __fdiv_rn(1.0f, mip_bound);
+    const int nx = cell_of(x, mip_rbound, c), ny = cell_of(y, mip_rbound, c), nz = cell_of(z, mip_rbound, c);
+    const uint32_t index = (uint32_t)__fmaf_rn((float)level, c.H3, (float)morton3D_1((uint32_t)nx, (uint32_t)ny, (uint32_t)nz));
+    const bool occ = __ldg(c.grid + (index >> 3)) & (1u << (index & 7u));
+    const float tx = exit_t(nx, r.dx, r.rdx, x, mip_bound, c);
+    const float ty = exit_t(ny, r.dy, r.rdy, y, mip_bound, c);
+    const float tz = exit_t(nz, r.dz, r.rdz, z, mip_bound, c);
+    tt = __fadd_rn(t, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    return occ;
+}
+
+__device__ __forceinline__ uint32_t mask_from(uint32_t pos) { return pos >= 32 ? 0u : (0xffffffffu << pos); }
+__device__ __forceinline__ uint32_t mask_below(uint32_t pos) { return pos >= 32 ? 0xffffffffu : ((1u << pos) - 1u); }
+
+// Marches one ray with the whole warp.  cap = most samples to emit (max_steps in the counting pass, the ray's count
+// in the writing pass).  Returns the number of samples; with WRITE also stores them at px / pd / pl.
+template <bool WRITE>
+__device__ __forceinline__ uint32_t march_ray_warp(const ray_t &r, const march_consts_t &c, float t0, float far, uint32_t cap, float *px,
+                                                   float *pd, float *pl) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t step = 0;
+    float t_base = t0, skip_tt = -FLT_MAX, last_t = t0;
+    const bool const_dt = (c.dt_gamma == 0.0f);
+    const float dt0 = clampf(0.0f, c.dt_min, c.dt_max);
+    while (step < cap) {
+        // t of this lane's point = t_base advanced `lane` times; `run` ends as the next chunk's base
+        float tl = t_base, run = t_base;
+        if (const_dt) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                if (i == (int)lane) tl = run;
+                run = __fadd_rn(run, dt0);
+            }
+        } else {
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+                if (i == (int)lane) tl = run;
+                run = next_t(run, c);
+            }
+        }
+        const bool valid = tl < far;
+        float x = 0, y = 0, z = 0, dt = 0, tt = 0;
+        bool occ = false;
+        if (valid) occ = test_point(r, c, tl, x, y, z, dt, tt);
+        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        if (vmask == 0) break;
+        const uint32_t omask = __ballot_sync(0xffffffffu, valid && occ);
+
+        // replay the skip rule over the 32 points
+        uint32_t emit = 0, pos = 0;
+        bool done = false;
+        while (pos < 32) {
+            const uint32_t ge = __ballot_sync(0xffffffffu, !(tl < skip_tt)) & mask_from(pos);  // `do t += dt while (t < tt)`
+            if (!ge) { pos = 32; break; }
+            pos = __ffs(ge) - 1;
+            if (!((vmask >> pos) & 1u)) { done = true; break; }  // t >= far: the ray is finished
+            if ((omask >> pos) & 1u) {
+                // run of consecutive occupied points: all emitted (each advances t by one step and is followed by a test)
+                const uint32_t stopm = ~omask & mask_from(pos);
+                const uint32_t e = stopm ? (uint32_t)__ffs(stopm) - 1u : 32u;
+                uint32_t runmask = mask_below(e) & mask_from(pos);
+                const uint32_t room = cap - step, cnt = __popc(runmask);
+                if (cnt >= room) {
+                    runmask = mask_below(pos + room) & mask_from(pos);
+                    emit |= runmask;
+                    step += room;
+                    done = true;
+                    break;
+                }
+                emit |= runmask;
+                step += cnt;
+                pos = e;
+            } else {
+                skip_tt = __shfl_sync(0xffffffffu, tt, pos);
+                pos += 1;  // the skip loop is a do-while: at least one advance
+            }
+        }
+        if (WRITE && emit) {
+            const float t_next = __fadd_rn(tl, dt);
+            const uint32_t below = emit & lt;
+            const int src = below ? 31 - __clz(below) : 0;
+            const float prev = __shfl_sync(0xffffffffu, t_next, src);
+            if ((emit >> lane) & 1u) {
+                const uint32_t i = (step - __popc(emit)) + __popc(below);
+                px[3 * (size_t)i] = x; px[3 * (size_t)i + 1] = y; px[3 * (size_t)i + 2] = z;
+                pd[3 * (size_t)i] = r.dx; pd[3 * (size_t)i + 1] = r.dy; pd[3 * (size_t)i + 2] = r.dz;
+                *reinterpret_cast<float2 *>(pl + 2 * (size_t)i) = make_float2(dt, __fsub_rn(t_next, below ? prev : last_t));
+            }
+            last_t = __shfl_sync(0xffffffffu, t_next, 31 - __clz(emit));
+        }
+        if (done || !(vmask >> 31)) break;
+        t_base = run;
+    }
+    return step;
+}
+
+// pass 1: one warp per ray counts; block scan over the kWarpRays counts; the last block to arrive turns the block
+// totals into exclusive prefixes (+ counter[0]) and bumps the counters (same protocol as k_march_train_count).
+__global__ void __launch_bounds__(kWarpRays * 32) k_march_train_count_warp(
+    const float *__restrict__ rays_o, const float *__restrict__ rays_d, const uint8_t *__restrict__ grid, float bound, float dt_gamma,
+    uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float *__restrict__ nears, const float *__restrict__ fars,
+    const float *__restrict__ noises, int *__restrict__ rays, int *__restrict__ counter, march_ws_t *__restrict__ ws) {
+    __shared__ uint32_t s_cnt[kWarpRays];
+    __shared__ uint32_t s_scan[kWarpRays];
+    __shared__ uint32_t s_flag;
+    const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kWarpRays + wid;
+    uint32_t num_steps = 0;
+    if (n < N) {
+        const march_consts_t c = make_consts(bound, dt_gamma, max_steps, C, H, grid);
+        const ray_t r = load_ray(rays_o, rays_d, n);
+        num_steps = march_ray_warp<false>(r, c, start_t(nears[n], c, noises[n]), fars[n], max_steps, nullptr, nullptr, nullptr);
+    }
+    if (lane == 0) s_cnt[wid] = num_steps;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kWarpRays; ++w) {
+            s_scan[w] = run;
+            run += s_cnt[w];
+        }
+        ws->block_sums[blockIdx.x] = run;
+        __threadfence();
+        s_flag = (atomicAdd(&ws->done, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (lane == 0 && n < N) {
+        rays[3 * (size_t)n] = (int)n;
+        rays[3 * (size_t)n + 1] = (int)s_scan[wid];  // block-local; pass 2 adds the block prefix
+        rays[3 * (size_t)n + 2] = (int)num_steps;
+    }
+    if (!s_flag) return;
+
+    // last block: exclusive scan of the gridDim.x block totals, contiguous chunks per thread
+    __threadfence();
+    const uint32_t nb = gridDim.x, nt = kWarpRays * 32;
+    const uint32_t chunk = div_round_up(nb, nt);
+    const uint32_t lo = min(threadIdx.x * chunk, nb), hi = min(lo + chunk, nb);
+    uint32_t sum = 0;
+    for (uint32_t i = lo; i < hi; ++i) sum += __ldcg(ws->block_sums + i);
+    // two-level scan: warp scan + warp totals
+    uint32_t incl = warp_incl_scan(sum);
+    __shared__ uint32_t s_wtot[kWarpRays];
+    if (lane == 31) s_wtot[wid] = incl;
+    __syncthreads();
+    uint32_t base = 0, grand = 0;
+#pragma unroll
+    for (int w = 0; w < kWarpRays; ++w) {
+        const uint32_t tw = s_wtot[w];
+        if ((uint32_t)w < wid) base += tw;
+        grand += tw;
+    }
+    uint32_t run = base + incl - sum + (uint32_t)counter[0];
+    __syncthreads();  // every thread has read counter[0] before thread 0 updates it
+    for (uint32_t i = lo; i < hi; ++i) {
+        const uint32_t v = __ldcg(ws->block_sums + i);
+        ws->block_sums[i] = run;
+        run += v;
+    }
+    if (threadIdx.x == 0) {
+        counter[0] += (int)grand;
+        counter[1] += (int)N;
+        ws->done = 0;
+    }
+}
+
+// pass 2: re-march with the warp and write the samples
+__global__ void __launch_bounds__(kWarpRays * 32) k_march_train_write_warp(
+    const float *__restrict__ rays_o, const float *__restrict__ rays_d, const uint8_t *__restrict__ grid, float bound, float dt_gamma,
+    uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *__restrict__ nears, const float *__restrict__ fars,
+    const float *__restrict__ noises, float *__restrict__ xyzs, float *__restrict__ dirs, float *__restrict__ deltas, int *__restrict__ rays,
+    const march_ws_t *__restrict__ ws) {
+    const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kWarpRays + wid;
+    if (n >= N) return;
+    const uint32_t num_steps = (uint32_t)rays[3 * (size_t)n + 2];
+    const uint32_t point_index = (uint32_t)rays[3 * (size_t)n + 1] + ws->block_sums[blockIdx.x];
+    __syncwarp();
+    if (lane == 0) rays[3 * (size_t)n + 1] = (int)point_index;
+    if (num_steps == 0 || point_index + num_steps > M) return;
+    const march_consts_t c = make_consts(bound, dt_gamma, max_steps, C, H, grid);
+    const ray_t r = load_ray(rays_o, rays_d, n);
+    march_ray_warp<true>(r, c, start_t(nears[n], c, noises[n]), fars[n], num_steps, xyzs + 3 * (size_t)point_index,
+                         dirs + 3 * (size_t)point_index, deltas + 2 * (size_t)point_index);
+}
+
+// ---- compositor, one warp per ray (reference :500-577 / :601-691) ---------------------------------------------
+// The sequential recurrences (T *= 1 - alpha; running sums) become warp scans over chunks of 32 samples; sums and
+// products are re-associated (relative differences ~1e-7, tolerance 1e-5).
+__device__ __forceinline__ float warp_incl_sum(float v, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= (uint32_t)o) v += u;
+    }
+    return v;
+}
+__device__ __forceinline__ float warp_incl_prod(float v, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= (uint32_t)o) v *= u;
+    }
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(kWarpRays * 32) k_composite_train_fwd_warp(const float *__restrict__ sigmas, const float *__restrict__ rgbs,
+                                                                             const float *__restrict__ deltas, const int *__restrict__ rays,
+                                                                             uint32_t M, uint32_t N, float T_thresh, float *__restrict__ weights_sum,
+                                                                             float *__restrict__ depth, float *__restrict__ image) {
+    const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kWarpRays + wid;
+    if (n >= N) return;
+    const uint32_t index = (uint32_t)rays[3 * (size_t)n], offset = (uint32_t)rays[3 * (size_t)n + 1], num_steps = (uint32_t)rays[3 * (size_t)n + 2];
+    float r = 0, g = 0, b = 0, ws = 0, d = 0;  // per-lane partial sums
+    if (!(num_steps == 0 || offset + num_steps > M)) {
+        const float *ps = sigmas + offset, *pc = rgbs + 3 * (size_t)offset, *pl = deltas + 2 * (size_t)offset;
+        float T = 1.0f, t = 0.0f;  // carried across chunks (warp-uniform)
+        for (uint32_t base = 0; base < num_steps; base += 32) {
+            const uint32_t i = base + lane;
+            const bool valid = i < num_steps;
+            float alpha = 0.f, dy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+            if (valid) {
+                const float2 dl = *reinterpret_cast<const float2 *>(pl + 2 * (size_t)i);
+                alpha = 1.0f - __expf(-ps[i] * dl.x);
+                dy = dl.y;
+                c0 = pc[3 * (size_t)i]; c1 = pc[3 * (size_t)i + 1]; c2 = pc[3 * (size_t)i + 2];
+            }
+            const float P = warp_incl_prod(1.0f - alpha, lane);  // prod_{j <= lane}
+            float E = __shfl_up_sync(0xffffffffu, P, 1);
+            if (lane == 0) E = 1.0f;
+            const float T_before = T * E, T_after = T * P;
+            const float tc = t + warp_incl_sum(dy, lane);
+            // the reference stops after the first sample that brings T below the threshold
+            const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+            const bool active = valid && (!stop || lane <= (uint32_t)(__ffs(stop) - 1));
+            if (active) {
+                const float w = alpha * T_before;
+                r += w * c0; g += w * c1; b += w * c2;
+                d += w * tc;
+                ws += w;
+            }
+            if (stop) break;
+            T = __shfl_sync(0xffffffffu, T_after, 31);
+            t = __shfl_sync(0xffffffffu, tc, 31);
+        }
+        r = warp_sum(r); g = warp_sum(g); b = warp_sum(b); ws = warp_sum(ws); d = warp_sum(d);
+    }
+    if (lane == 0) {
+        weights_sum[index] = ws;
+        depth[index] = d;
+        image[3 * (size_t)index] = r; image[3 * (size_t)index + 1] = g; image[3 * (size_t)index + 2] = b;
+    }
+}
+
+__global__ void __launch_bounds__(kWarpRays * 32) k_composite_train_bwd_warp(
+    const float *__restrict__ grad_weights_sum, const float *__restrict__ grad_depth, const float *__restrict__ grad_image,
+    const float *__restrict__ sigmas, const float *__restrict__ rgbs, const float *__restrict__ deltas, const int *__restrict__ rays,
+    const float *__restrict__ weights_sum, const float *__restrict__ depth, const float *__restrict__ image, uint32_t M, uint32_t N,
+    float T_thresh, float *__restrict__ grad_sigmas, float *__restrict__ grad_rgbs) {
+    const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kWarpRays + wid;
+    if (n >= N) return;
+    const uint32_t index = (uint32_t)rays[3 * (size_t)n], offset = (uint32_t)rays[3 * (size_t)n + 1], num_steps = (uint32_t)rays[3 * (size_t)n + 2];
+    if (num_steps == 0 || offset + num_steps > M) return;
+    const float gi0 = grad_image[3 * (size_t)index], gi1 = grad_image[3 * (size_t)index + 1], gi2 = grad_image[3 * (size_t)index + 2];
+    const float gws = grad_weights_sum[index], gd = grad_depth[index];
+    const float r_final = image[3 * (size_t)index], g_final = image[3 * (size_t)index + 1], b_final = image[3 * (size_t)index + 2];
+    const float ws_final = weights_sum[index], d_final = depth[index];
+    const float *ps = sigmas + offset, *pc = rgbs + 3 * (size_t)offset, *pl = deltas + 2 * (size_t)offset;
+    float *gs = grad_sigmas + offset, *gc = grad_rgbs + 3 * (size_t)offset;
+    float T = 1.0f, t = 0.0f, r = 0.f, g = 0.f, b = 0.f, d = 0.f;  // carried across chunks (warp-uniform)
+    for (uint32_t base = 0; base < num_steps; base += 32) {
+        const uint32_t i = base + lane;
+        const bool valid = i < num_steps;
+        float alpha = 0.f, dx = 0.f, dy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+        if (valid) {
+            const float2 dl = *reinterpret_cast<const float2 *>(pl + 2 * (size_t)i);
+            alpha = 1.0f - __expf(-ps[i] * dl.x);
+            dx = dl.x; dy = dl.y;
+            c0 = pc[3 * (size_t)i]; c1 = pc[3 * (size_t)i + 1]; c2 = pc[3 * (size_t)i + 2];
+        }
+        const float P = warp_incl_prod(1.0f - alpha, lane);
+        float E = __shfl_up_sync(0xffffffffu, P, 1);
+        if (lane == 0) E = 1.0f;
+        const float T_before = T * E, T_after = T * P;
+        const float tc = t + warp_incl_sum(dy, lane);
+        const float w = alpha * T_before;
+        const float rc = r + warp_incl_sum(w * c0, lane), gc_ = g + warp_incl_sum(w * c1, lane), bc = b + warp_incl_sum(w * c2, lane);
+        const float dc = d + warp_incl_sum(w * tc, lane);
+        const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+        const bool active = valid && (!stop || lane <= (uint32_t)(__ffs(stop) - 1));
+        if (active) {
+            gc[3 * (size_t)i] = gi0 * w; gc[3 * (size_t)i + 1] = gi1 * w; gc[3 * (size_t)i + 2] = gi2 * w;
+            gs[i] = dx * (gi0 * (T_after * c0 - (r_final - rc)) + gi1 * (T_after * c1 - (g_final - gc_)) + gi2 * (T_after * c2 - (b_final - bc)) +
+                          gd * (T_after * tc - (d_final - dc)) + gws * (1 - ws_final));
+        }
+        if (stop) break;
+        T = __shfl_sync(0xffffffffu, T_after, 31);
+        t = __shfl_sync(0xffffffffu, tc, 31);
+        r = __shfl_sync(0xffffffffu, rc, 31); g = __shfl_sync(0xffffffffu, gc_, 31); b = __shfl_sync(0xffffffffu, bc, 31);
+        d = __shfl_sync(0xffffffffu, dc, 31);
+    }
+}
+
+}  // namespace
+}  // namespace ngp

@@ -168,6 +168,15 @@ class NGPTrainer:
                                      self.dirs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), counter.data_ptr(), self.noises.data_ptr(),
                                      self.march_ws.data_ptr(), self.march_ws.numel(), s))
         self.count_sum.add_(counter[:1])  # running sample count since the last density-grid update (-> mean_count)
+        # everything per-sample below runs on min(M, counter[0]) rows, read on the device: no host sync, no padded work
+        lib.ngp_set_batch_limit(counter.data_ptr())
+        try:
+            self._samples_forward_backward(counter)
+        finally:
+            lib.ngp_set_batch_limit(None)
+
+    def _samples_forward_backward(self, counter):
+        s, N, M, lib = abi.stream(), self.N, self.M, abi.lib
         self._network_forward(M)
         _ck(lib.ngp_composite_rays_train_forward(self.sigmas.data_ptr(), self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), M, N,
                                                  self.T_thresh, self.ws.data_ptr(), self.depth.data_ptr(), self.image.data_ptr(), s))
@@ -326,8 +335,8 @@ class NGPTrainer:
         # sample budget for the next interval (the one host read of the schedule, nerf/renderer.py:593-596)
         if self.local_step > 0:
             self.mean_count = int(self.count_sum.item() / self.local_step)
-            need = int(self.mean_count * 1.25) + 4096
-            if need > self.M or need < self.M // 2:
+            need = int(self.mean_count * 1.15) + 4096  # capacity only: the kernels stop at the device-side count
+            if need > self.M or need < 0.7 * self.M:
                 self._alloc_samples(need)
         self.count_sum.zero_()
         self.local_step = 0
