@@ -275,6 +275,7 @@ class NerfTrainWorkload:
         import nerf
         from nerf import synthetic
         self.torch, self.dev, self.world = torch, dev, world
+        torch.manual_seed(1000 + rank)  # ray jitter and density-grid probes; fp16 atomics still make runs differ in the last bits
         self.N = self.args.rays or (4096 if world == 1 else (1 << 18) // world)
         self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=self.N, device=dev, world_size=world, seed=0, use_graph=not self.args.no_graph)
         n_batches = 16
@@ -302,7 +303,7 @@ class NerfTrainWorkload:
              "l2": "flushed between steps (256 MiB memset outside the per-step events)", "pretrain_steps": self.args.pretrain}
         if tr is not None:
             c.update({"rays_per_gpu": self.N, "global_rays": self.N * world, "samples_per_ray": round(tr.mean_count / self.N, 2),
-                      "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph), "density_grid_update": f"every {tr.update_interval} steps, inside the timed region",
+                      "samples_per_step_per_gpu": tr.mean_count, "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph), "density_grid_update": f"every {tr.update_interval} steps, inside the timed region",
                       "last_loss": tr.loss()})
         return c
 
@@ -459,7 +460,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--points", type=int, default=0, help="override the per-GPU batch (development only)")
     ap.add_argument("--rays", type=int, default=0, help="nerf_train: rays per GPU per step (default: configs[1]/[2])")
-    ap.add_argument("--pretrain", type=int, default=512, help="nerf_train: untimed optimisation steps before the warm-up")
+    ap.add_argument("--pretrain", type=int, default=1024, help="nerf_train: untimed optimisation steps before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="nerf_train: launch the step eagerly instead of replaying CUDA graphs")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -265,3 +265,29 @@ def test_error_behaviour():
         be.grid_encode_forward(xc, e.to(DEV), oc.long(), out.to(DEV), 4, 3, 2, 1, 1.0, 4, None, 0, False, 0)
     # empty batch is a no-op
     be.grid_encode_forward(torch.empty(0, 3, device=DEV), e.to(DEV), oc, torch.empty(1, 0, 2, device=DEV), 0, 3, 2, 1, 1.0, 4, None, 0, False, 0)
+
+
+@pytest.mark.parametrize("layout", [0, 1])
+def test_segmented_warp_reduction_short_rays(oracle, layout):
+    """Runs of equal cells that start and end at arbitrary lanes, with out-of-range points in between (segmented scan)."""
+    offsets, pls = oracle.make_offsets(desired_resolution=2048)
+    rng = np.random.default_rng(3)
+    segs = []
+    for i in range(300):
+        n = int(rng.integers(1, 90))
+        o, d = rng.random(3) * 0.6 + 0.2, rng.standard_normal(3)
+        d /= np.linalg.norm(d)
+        p = o + d * (np.arange(n)[:, None] * 0.0034)
+        segs.append(p)
+        if i % 7 == 0:
+            segs.append(np.array([[-0.2, 0.5, 0.5], [0.5, 1.3, 0.5]]))  # skipped by the kernels (outside [0,1])
+    x = np.concatenate(segs).astype(np.float32)
+    B = x.shape[0]
+    emb = rng.standard_normal((offsets[-1], 2)).astype(np.float32)
+    g = rng.standard_normal((16, B, 2)).astype(np.float32)
+    ref_ge, _ = oracle.grid_encode_backward(g, x, emb, offsets, pls, 16)
+    g_t = torch.from_numpy(g).to(DEV)
+    if layout == 1:
+        g_t = g_t.permute(1, 0, 2).contiguous()
+    ge, _ = _run_bwd(g_t, torch.from_numpy(x).to(DEV), torch.from_numpy(emb).to(DEV), torch.from_numpy(offsets).to(DEV), pls, 16, layout=layout)
+    assert np.allclose(ge.cpu().numpy(), ref_ge, rtol=1e-4, atol=1e-4 * np.abs(ref_ge).max())

@@ -516,16 +516,36 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__
             make_rows3(g, o, r);
             key = (unsigned long long)o.p0 | ((unsigned long long)o.p1 << 21) | ((unsigned long long)o.p2 << 42);
         }
-        int uniform = 0;
-        if (warp_agg) __match_all_sync(0xffffffffu, key, &uniform);
-        if (uniform) {  // whole warp in one cell (coherent samples on coarse levels): reduce first
+        // Segmented warp reduction.  Lanes are consecutive points; samples marched along a ray stay in one cell of a
+        // coarse level for many steps (cell / dt ~ 37 samples at resolution 16, ~2 at 256), so equal keys form runs of
+        // adjacent lanes.  Each run is summed with a segmented shuffle scan and its last lane issues ONE set of
+        // reductions: the L2 atomic units see 1/run-length of the traffic (they, not bytes, bound this kernel), and
+        // the fp16 table gradient gets one rounding per run instead of one per sample.
+        uint32_t heads = 0xffffffffu;
+        const uint32_t lane = threadIdx.x & 31u;
+        if (warp_agg) {
+            const unsigned long long prev = __shfl_up_sync(0xffffffffu, key, 1);
+            heads = __ballot_sync(0xffffffffu, lane == 0 || prev != key);
+        }
+        if (__popc(heads) <= 20) {
+            const int start = 31 - __clz((int)(heads & (0xffffffffu >> (31u - lane))));  // first lane of my run
             float s[16];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                s[4 * q + 0] = warp_sum(r.w0[q] * gv[k].x); s[4 * q + 1] = warp_sum(r.w0[q] * gv[k].y);
-                s[4 * q + 2] = warp_sum(r.w1[q] * gv[k].x); s[4 * q + 3] = warp_sum(r.w1[q] * gv[k].y);
+                s[4 * q + 0] = valid ? r.w0[q] * gv[k].x : 0.f; s[4 * q + 1] = valid ? r.w0[q] * gv[k].y : 0.f;
+                s[4 * q + 2] = valid ? r.w1[q] * gv[k].x : 0.f; s[4 * q + 3] = valid ? r.w1[q] * gv[k].y : 0.f;
             }
-            if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const bool take = (int)lane - d >= start;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float u = __shfl_up_sync(0xffffffffu, s[j], d);
+                    if (take) s[j] += u;
+                }
+            }
+            const bool tail = lane == 31u || ((heads >> (lane + 1u)) & 1u);
+            if (tail && valid) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     if ((r.i0[q] ^ r.i1[q]) == 1u) {
