@@ -1,0 +1,85 @@
+// umma_issue_bench.cu -- how long does one tcgen05.mma (kind::f16, M=128, K=16) take to ISSUE and to EXECUTE on B200 as a
+// function of N and of how the descriptors reach the instruction?  Informs the FFMLP kernel design.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o benchmarks/_build/umma_issue_bench benchmarks/umma_issue_bench.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../torch-ngp_b200/csrc/umma.cuh"
+using namespace ngp::umma;
+
+// mode 0: descriptors rebuilt from a runtime address per MMA (what issue_kmajor does)
+// mode 1: one descriptor pair reused (pure instruction rate)
+// mode 2: descriptor low words advanced by a constant (add only)
+template <int MODE>
+__global__ void __launch_bounds__(128) k_bench(uint32_t N, uint32_t reps, uint32_t nk, long long *out, uint32_t m_mn) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_bar;
+    for (uint32_t i = threadIdx.x; i < 48 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(smem)[i] = 0;
+    if (threadIdx.x < 32) tmem_alloc(&s_tmem, 512);
+    if (threadIdx.x == 0) { mbar_init(&s_bar, 1); mbar_init_fence(); }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    const uint32_t idesc = make_idesc(128, N, m_mn != 0, m_mn != 0);
+    const uint32_t a0 = smem_u32(smem), b0 = smem_u32(smem + 16384);
+    long long t0 = 0, t1 = 0, t2 = 0;
+    uint32_t phase = 0;
+    if (threadIdx.x == 0) {
+        t0 = clock64();
+        for (uint32_t r = 0; r < reps; ++r) {
+            if (MODE == 0) {
+                for (uint32_t k = 0; k < nk; ++k) {
+                    const uint64_t ad = make_desc(a0 + (k >> 2) * 16384u * 0u + (k & 3u) * 32u, 0, kAtomBytes);
+                    const uint64_t bd = make_desc(b0 + (k & 3u) * 32u, 0, kAtomBytes);
+                    mma_f16(tmem, ad, bd, idesc, k > 0 ? 1u : 0u);
+                }
+            } else if (MODE == 1) {
+                const uint64_t ad = make_desc(a0, 0, kAtomBytes), bd = make_desc(b0, 0, kAtomBytes);
+                for (uint32_t k = 0; k < nk; ++k) mma_f16(tmem, ad, bd, idesc, 1u);
+            } else {
+                uint64_t ad = make_desc(a0, 0, kAtomBytes), bd = make_desc(b0, 0, kAtomBytes);
+#pragma unroll 4
+                for (uint32_t k = 0; k < nk; ++k) {
+                    mma_f16(tmem, ad, bd, idesc, 1u);
+                    ad += 2; bd += 2;
+                    if ((k & 3u) == 3u) { ad -= 8; bd -= 8; }
+                }
+            }
+        }
+        t1 = clock64();
+        mma_commit(&s_bar);
+    }
+    mbar_wait(&s_bar, phase);
+    if (threadIdx.x == 0) {
+        t2 = clock64();
+        out[0] = t1 - t0;
+        out[1] = t2 - t0;
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(tmem, 512);
+}
+
+int main() {
+    long long *out;
+    cudaMallocManaged(&out, 16);
+    const uint32_t reps = 64, nk = 8;
+    for (int mn = 0; mn < 2; ++mn)
+        for (uint32_t N : {16u, 32u, 64u, 128u, 256u})
+            for (int mode = 0; mode < 3; ++mode) {
+                auto run = [&](auto kern) {
+                    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn);
+                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn);
+                    cudaError_t e = cudaDeviceSynchronize();
+                    if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return; }
+                    printf("major=%s N=%3u mode=%d  issue %.1f cyc/mma   complete %.1f cyc/mma\n", mn ? "MN" : "K ", N, mode, (double)out[0] / (reps * nk),
+                           (double)out[1] / (reps * nk));
+                };
+                if (mode == 0) run(k_bench<0>); else if (mode == 1) run(k_bench<1>); else run(k_bench<2>);
+            }
+    return 0;
+}

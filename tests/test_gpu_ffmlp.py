@@ -67,9 +67,18 @@ def test_forward_vs_twin(oracle, cfg, B):
         assert torch.equal(y, y_inf)
 
 
+@pytest.fixture(params=[1, 0], ids=["multi_pipeline", "single_tile"])
+def bwd_variant(request):
+    """Both backward kernels (one MMA-issuer warp + up to 4 tiles in flight / one tile per CTA) satisfy the same contract."""
+    import ngp_abi as abi
+    abi.set_option("ffmlp_bwd_variant", request.param)
+    yield request.param
+    abi.set_option("ffmlp_bwd_variant", -1)
+
+
 @pytest.mark.parametrize("cfg", CONFIGS)
 @pytest.mark.parametrize("B", [1000, 131])
-def test_backward_vs_twin(oracle, cfg, B):
+def test_backward_vs_twin(oracle, cfg, B, bwd_variant):
     in_dim, out_dim, hid, nl = cfg
     torch.manual_seed(B + 1)
     x = (torch.randn(B, in_dim, device=DEV) * 0.7).half()
@@ -89,7 +98,7 @@ def test_backward_vs_twin(oracle, cfg, B):
     assert np.abs(gw2.float().cpu().numpy() - gw_ref).max() / np.abs(gw_ref).max() < 1e-2
 
 
-def test_many_tiles_persistent_loop_and_accumulation(oracle):
+def test_many_tiles_persistent_loop_and_accumulation(oracle, bwd_variant):
     """More tiles than resident CTAs: exercises the per-CTA tile loop, the prefetch ring and the TMEM dW accumulation."""
     in_dim, out_dim, hid, nl = 32, 16, 64, 3
     B = 128 * 1500 + 37

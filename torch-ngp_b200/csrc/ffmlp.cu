@@ -82,15 +82,16 @@ __device__ __forceinline__ void stage_weights(uint8_t *sw, const WT *__restrict_
 
 // rows [row0, row0+128) of a row-major fp16 [B x cols] matrix -> swizzled activation tiles, asynchronously;
 // rows >= B are zero-filled (cp.async src-size 0)
+// off8: first 16-byte chunk of the tile row to fill (packs two narrow operands side by side in one tile)
 __device__ __forceinline__ void load_rows_async(uint8_t *tiles, const __half *__restrict__ g, uint32_t row0, uint32_t B, uint32_t cols,
-                                                uint32_t tid, uint32_t nth) {
+                                                uint32_t tid, uint32_t nth, uint32_t off8 = 0) {
     const uint32_t cpr = cols >> 3;
     for (uint32_t q = tid; q < kTileRows * cpr; q += nth) {
-        const uint32_t r = q / cpr, c8 = q - r * cpr;
+        const uint32_t r = q / cpr, c8 = q - r * cpr, d8 = c8 + off8;
         const uint32_t grow = row0 + r;
         const bool ok = grow < B;
         const __half *src = g + (size_t)(ok ? grow : 0u) * cols + c8 * 8;
-        const uint32_t dst = smem_u32(tiles + (c8 >> 3) * kActTileBytes + swz_off(r, c8 & 7u));
+        const uint32_t dst = smem_u32(tiles + (d8 >> 3) * kActTileBytes + swz_off(r, d8 & 7u));
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16u : 0u) : "memory");
     }
 }
@@ -458,6 +459,211 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
     if (tid == 0) *counter = 0u;
 }
 
+
+// ==========================================================================================================
+// backward, multi-pipeline variant
+// ==========================================================================================================
+// The single-tile kernel above serialises, per tile, 2*nl+1 round trips (MMA issue -> commit -> TMEM drain ->
+// st.shared -> barrier); measured on B200 it spends ~200 cycles of SM time per tcgen05.mma against a 32-cycle
+// floor.  Here one CTA per SM keeps NP tiles in flight: warp 0 is the only MMA issuer of the CTA (so the dW
+// accumulators in TMEM can be shared by all pipelines -- one thread's tcgen05.mma stream is ordered), and NP
+// warpgroups of 128 threads each own one tile: they drain the accumulator, apply ReLU / the ReLU mask and hand the
+// operands of the next layer step back through an mbarrier.  Per pipeline: full[p] (128 arrivals: operands in shared
+// memory) -> issuer -> done[p] (tcgen05.commit: accumulator ready).  G_l overwrites H_l in place (each round's
+// commit covers the dW MMA that still reads H_l), which is what makes room for 3-4 tiles in 227 KB.
+template <typename WT, int HID>
+__global__ void __launch_bounds__(32 + 128 * 6) k_ffmlp_bwd_mp(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
+                                                               __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
+                                                               int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
+                                                               uint32_t np, uint32_t ns, uint32_t accw, const int *__restrict__ limit) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ uint32_t s_last;
+    __shared__ __align__(8) uint64_t s_full[4];
+    __shared__ __align__(8) uint64_t s_done[4];
+    constexpr int STEP = HID >= 32 ? 32 : 16;  // accumulator columns drained per tcgen05.ld
+    const uint32_t cw = m.hid / ns;            // columns of a row owned by one of the ns threads that share it
+    const uint32_t Beff = eff_batch(m.B, limit);
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t xbytes = ktiles(m.in) * kActTileBytes, abytes = ktiles(m.hid) * kActTileBytes, obytes = ktiles(m.out) * kActTileBytes;
+    // narrow nets: dY [128 x out] rides in the unused columns of the X tile ([X | dY | pad], in + out <= 64)
+    const bool packed = m.in + m.out <= 64u;
+    const uint32_t goff = packed ? m.in * 2u : xbytes;  // byte offset of the dY operand from the X tile
+    const uint32_t per_pipe = xbytes + (packed ? 0u : obytes) + m.nl * abytes;
+    const uint32_t hoff = per_pipe - m.nl * abytes;
+    uint8_t *sw = smem;
+    uint32_t dwc[kMaxLayers + 1];
+    {
+        uint32_t o = np * accw;
+        for (uint32_t i = 0; i <= m.nl; ++i) {
+            dwc[i] = o;
+            o += (m.K[i] + 31u) & ~31u;
+        }
+    }
+    stage_weights<WT>(sw, w, m, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid < np) {
+        mbar_init(&s_full[tid], 4 * ns);
+        mbar_init(&s_done[tid], 1);
+    }
+    if (tid == 0) mbar_init_fence();
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    const uint32_t stride = gridDim.x * np;
+
+    if (warp == 0) {
+        // ---- the MMA issuer ----
+        uint32_t left[4], rnd[4], ph[4], active = 0, started = 0;
+        for (uint32_t p = 0; p < 4; ++p) {
+            const uint32_t t0 = blockIdx.x * np + p;
+            left[p] = (p < np && t0 < ntiles) ? (ntiles - t0 + stride - 1) / stride : 0u;
+            rnd[p] = 0; ph[p] = 0;
+            active += left[p] ? 1u : 0u;
+        }
+        while (active) {
+#pragma unroll
+            for (uint32_t p = 0; p < 4; ++p) {
+                // warp-uniform on purpose (vote): the descriptors below must stay in uniform registers, or every
+                // tcgen05.mma pays a register->uniform-register broadcast loop (measured: ~250 instead of ~64 cycles/MMA)
+                const bool go = p < np && left[p] && mbar_test(&s_full[p], ph[p]);
+                if (!__any_sync(0xffffffffu, go)) continue;
+                ph[p] ^= 1u;
+                fence_after_sync();
+                {
+                    uint8_t *sx = smem + m.wbytes + p * per_pipe, *sgo = sx + goff, *sh = sx + hoff;
+                    const uint32_t acc = tmem + p * accw, rr = rnd[p];
+                    if (rr == 0) {
+                        if (lane == 0) issue_fwd(acc, sx, sw + m.soff[0], m.hid, m.in);
+                    } else if (rr < m.nl) {
+                        if (lane == 0) issue_fwd(acc, sh + (rr - 1) * abytes, sw + m.soff[rr], m.hid, m.hid);
+                    } else if (rr == m.nl) {  // dH_{nl-1} = dY W_last ; dW_last += dY^T H_{nl-1}
+                        if (lane == 0) {
+                            issue_bwd_dx(acc, sgo, sw + m.soff[m.nl], m.hid, m.out);
+                            issue_dw(tmem + dwc[m.nl], sgo, sh + (m.nl - 1) * abytes, m.out, m.hid, (started >> m.nl) & 1u);
+                        }
+                        started |= 1u << m.nl;
+                    } else {
+                        const uint32_t l = 2 * m.nl - rr;  // G_l sits where H_l was
+                        uint8_t *g = sh + l * abytes;
+                        if (lane == 0) {
+                            if (l > 0) {
+                                issue_bwd_dx(acc, g, sw + m.soff[l], m.hid, m.hid);
+                                issue_dw(tmem + dwc[l], g, sh + (l - 1) * abytes, m.hid, m.hid, (started >> l) & 1u);
+                            } else {
+                                if (calc_dx) issue_bwd_dx(acc, g, sw + m.soff[0], m.in, m.hid);
+                                issue_dw(tmem + dwc[0], g, sx, m.hid, m.in, started & 1u);
+                            }
+                        }
+                        started |= 1u << l;
+                    }
+                    if (lane == 0) mma_commit(&s_done[p]);
+                }
+                __syncwarp();
+                if (++rnd[p] == 2 * m.nl + 1) {
+                    rnd[p] = 0;
+                    if (--left[p] == 0) --active;
+                }
+            }
+        }
+    } else {
+        // ---- tile pipelines ----
+        // pipeline p = 4*ns consecutive warps; warp w drains TMEM lanes 32*(w%4).. (hardware rule) = tile rows, and the
+        // column group cg = (warp within pipeline) / 4 of width cw, so one row is handled by ns threads in parallel
+        const uint32_t wpp = 4u * ns, p = (warp - 1) / wpp, wp = (warp - 1) - p * wpp, cg = wp >> 2, q = warp & 3u;
+        const uint32_t row = q * 32u + lane, ptid = wp * 32u + lane, nth = 128u * ns;
+        if (p < np) {
+            uint8_t *sx = smem + m.wbytes + p * per_pipe, *sh = sx + hoff;
+            const uint32_t trow = tmem + p * accw + ((q * 32u) << 16);
+            uint32_t phase = 0;
+            for (uint32_t tile = blockIdx.x * np + p; tile < ntiles; tile += stride) {
+                load_rows_async(sx, x, tile * kTileRows, Beff, m.in, ptid, nth);
+                if (packed) load_rows_async(sx, grad, tile * kTileRows, Beff, m.out, ptid, nth, m.in >> 3);
+                else load_rows_async(sx + xbytes, grad, tile * kTileRows, Beff, m.out, ptid, nth);
+                cp_async_commit();
+                cp_async_wait<0>();
+                fence_proxy_async();
+                __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                for (uint32_t l = 0; l < m.nl; ++l) {  // forward recompute: H_l = ReLU(W_l H_{l-1})
+                    mbar_wait(&s_done[p], phase);
+                    phase ^= 1u;
+                    fence_after_sync();
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0);
+                    fence_proxy_async();
+                    fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                }
+                for (int l = (int)m.nl - 1; l >= 0; --l) {  // G_l = dH_l * (H_l > 0), in place
+                    mbar_wait(&s_done[p], phase);
+                    phase ^= 1u;
+                    fence_after_sync();
+                    uint8_t *h = sh + (uint32_t)l * abytes;
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_mask_to_tile<STEP>(trow, h, h, row, c0);
+                    fence_proxy_async();
+                    fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                }
+                mbar_wait(&s_done[p], phase);
+                phase ^= 1u;
+                fence_after_sync();
+                if (calc_dx) {
+                    const uint32_t grow = tile * kTileRows + row;
+                    for (uint32_t c0 = cg * 16u; c0 < m.in; c0 += ns * 16u)
+                        epi_to_global(trow, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < Beff);
+                }
+                fence_before_sync();
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+
+    // ---- flush the CTA's dW accumulators: TMEM lane = output row of the matrix; pipeline index = column group ----
+    if (warp > 0 && blockIdx.x * np < ntiles) {
+        const uint32_t grp = (warp - 1) >> 2, ngrp = np * ns, q = warp & 3u, row = q * 32u + lane;
+        if (grp < ngrp) {
+            const uint32_t trow = tmem + ((q * 32u) << 16);
+            for (uint32_t i = 0; i <= m.nl; ++i) {
+                const uint32_t rows = m.rows[i], K = m.K[i];
+                for (uint32_t c0 = grp * 16u; c0 < K; c0 += ngrp * 16u) {  // warp-uniform trip count: tcgen05.ld is .sync.aligned
+                    float v[16];
+                    tmem_ld16(trow + dwc[i] + c0, v);
+                    if (row < rows) {
+                        float *d = ws + m.woff[i] + (size_t)row * K + c0;
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3]) : "memory");
+                    }
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __threadfence();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+    // ---- last CTA: fp32 sum -> grad_weights (requested dtype); leave the workspace zeroed for the next call ----
+    uint32_t *counter = reinterpret_cast<uint32_t *>(ws + ((m.nweights + 3u) & ~3u));
+    if (tid == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (uint32_t i = tid; i < m.nweights; i += blockDim.x) {
+        const float v = __ldcg(ws + i);
+        if (grad_w_f32) reinterpret_cast<float *>(grad_w)[i] = v;
+        else reinterpret_cast<__half *>(grad_w)[i] = __float2half_rn(v);
+        ws[i] = 0.f;
+    }
+    if (tid == 0) *counter = 0u;
+}
+
 }  // namespace
 }  // namespace ngp
 
@@ -606,6 +812,56 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
     uint32_t grid = (uint32_t)sm_count() * per_sm;
     if (grid > ntiles) grid = ntiles;
     const int gf32 = grad_weights_dtype == NGP_DTYPE_F32;
+    // ---- multi-pipeline variant: NP tiles in flight per CTA, one CTA per SM ----
+    {
+        const int variant = get_option("ffmlp_bwd_variant", -1);
+        const bool packed = input_dim + output_dim <= 64;
+        const size_t per_pipe = ((size_t)ktiles(input_dim) + (packed ? 0 : ktiles(output_dim)) + (size_t)num_layers * ktiles(hidden_dim)) * kActTileBytes;
+        uint32_t accw = hidden_dim > input_dim ? hidden_dim : input_dim;
+        accw = (accw + 31u) & ~31u;
+        uint32_t dwcols = 0;
+        for (uint32_t i = 0; i <= num_layers; ++i) dwcols += (m.K[i] + 31u) & ~31u;
+        uint32_t np = 0;
+        if (m.wbytes + 2048 < kMaxSmem) np = (uint32_t)((kMaxSmem - 2048 - m.wbytes) / per_pipe);  // 2 KB: static shared + alignment
+        if (dwcols < 512) { if (np > (512 - dwcols) / accw) np = (512 - dwcols) / accw; } else np = 0;
+        if (np > 4) np = 4;
+        // ns threads share a row's epilogue (latency); 32 + 128 * np * ns <= 800 threads keeps 80 registers per thread
+        uint32_t ns = hidden_dim >= 64 ? 2u : 1u;
+        const int ns_opt = get_option("ffmlp_bwd_split", 0);
+        if (ns_opt == 1 || ns_opt == 2) ns = (uint32_t)ns_opt;
+        if (hidden_dim / ns < 32 && hidden_dim >= 32) ns = hidden_dim / 32;
+        if (hidden_dim < 32) ns = 1;
+        if (np * ns > 6) np = 6 / ns;
+        const uint32_t per_cta_need = div_round_up(ntiles, (uint32_t)sm_count());
+        if (variant != 1 && np > per_cta_need) np = per_cta_need;  // forced (tests): as many pipelines as fit, whatever the batch
+        if (np > ntiles) np = ntiles;
+        if (variant != 0 && (np >= 2 || (variant == 1 && np >= 1))) {
+            const size_t smem_mp = m.wbytes + np * per_pipe;
+            const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
+            uint32_t grid_mp = div_round_up(ntiles, np);
+            if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();
+#define NGP_BWDMP_CASE(WT_, HID_)                                                                                            \
+    {                                                                                                                        \
+        rc = set_smem(k_ffmlp_bwd_mp<WT_, HID_>, smem_mp);                                                                   \
+        if (rc != NGP_OK) return rc;                                                                                         \
+        NGP_PROF("k_ffmlp_bwd_mp", st);                                                                                      \
+        k_ffmlp_bwd_mp<WT_, HID_><<<grid_mp, 32 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, batch_limit());   \
+    }
+#define NGP_BWDMP_HID(WT_)                                         \
+    switch (hidden_dim) {                                          \
+        case 16: NGP_BWDMP_CASE(WT_, 16) break;                    \
+        case 32: NGP_BWDMP_CASE(WT_, 32) break;                    \
+        case 64: NGP_BWDMP_CASE(WT_, 64) break;                    \
+        default: NGP_BWDMP_CASE(WT_, 128) break;                   \
+    }
+            if (weights_dtype == NGP_DTYPE_F16) NGP_BWDMP_HID(__half) else NGP_BWDMP_HID(float)
+#undef NGP_BWDMP_HID
+#undef NGP_BWDMP_CASE
+            NGP_CHECK_LAUNCH();
+            return NGP_OK;
+        }
+    }
 #define NGP_BWD_CASE(WT_, HID_)                                                                                              \
     {                                                                                                                        \
         rc = set_smem(k_ffmlp_bwd<WT_, HID_>, smem);                                                                         \

@@ -208,9 +208,8 @@ class NGPTrainer:
         _ck(lib.ngp_step_end(self.state.data_ptr(), s))
 
     def _allreduce(self):
-        import torch.distributed as dist
-        dist.all_reduce(self.g16.view(-1))
-        dist.all_reduce(self.g32)
+        from .parallel import allreduce_gradients
+        allreduce_gradients(self.g16, self.g32)
 
     def _step_eager(self):
         self._forward_backward()
