@@ -108,6 +108,9 @@ NGP_API int ngp_packbits(const float *grid, uint32_t N, float density_thresh, ui
  *     bit-identical; counter[0] += total, counter[1] += N exactly as the reference leaves them);
  *   - needs `workspace` of ngp_march_rays_train_workspace_bytes(N) bytes (chained-scan state). */
 NGP_API size_t ngp_march_rays_train_workspace_bytes(uint32_t N);
+/* larger workspace that also holds per-ray emit masks: pass 2 of the marcher replays them instead of re-testing the
+ * occupancy grid (optional; with the smaller workspace above the samples are re-marched) */
+NGP_API size_t ngp_march_rays_train_workspace_bytes_ex(uint32_t N, float bound, uint32_t max_steps);
 NGP_API int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
                          uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
                          const float *fars, float *xyzs, float *dirs, float *deltas, int *rays, int *counter,

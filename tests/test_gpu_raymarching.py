@@ -60,15 +60,17 @@ def test_packbits_bit_exact(oracle, shape):
     assert np.array_equal(buf[1:].cpu().numpy(), oracle.packbits(g, 0.3))
 
 
-@pytest.fixture(params=[1, 0], ids=["warp_per_ray", "thread_per_ray"])
+@pytest.fixture(params=[(1, 1), (1, 0), (0, 0)], ids=["warp_per_ray_masks", "warp_per_ray_remarch", "thread_per_ray"])
 def variant(request):
-    """Both implementations of the training marcher / compositor must satisfy the same contract."""
+    """Every implementation of the training marcher / compositor must satisfy the same contract."""
     import ngp_abi as abi
-    abi.set_option("march_variant", request.param)
-    abi.set_option("composite_variant", request.param)
+    abi.set_option("march_variant", request.param[0])
+    abi.set_option("composite_variant", request.param[0])
+    abi.set_option("march_masks", request.param[1])
     yield request.param
     abi.set_option("march_variant", -1)
     abi.set_option("composite_variant", -1)
+    abi.set_option("march_masks", 1)
 
 
 @pytest.mark.parametrize("name,dt_gamma,perturb", [("c1", 0.0, False), ("c1", 1.0 / 128, True), ("c2", 0.0, True), ("c2", 1.0 / 128, False)])

@@ -30,6 +30,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_variant", -1},         // training marcher: -1 auto / 1 warp per ray (ballot replay of the skip rule), 0 thread per ray
+        {"march_masks", 1},            // warp marcher: record emit masks in pass 1 when the workspace has room (0: always re-march)
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
         {"ffmlp_available", 1},
         {"ffmlp_bwd_variant", -1},     // -1 auto / 1: multi-pipeline backward (one MMA-issuer warp, up to 4 tiles in flight), 0: one tile per CTA

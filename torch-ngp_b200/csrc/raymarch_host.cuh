@@ -5,6 +5,13 @@ namespace ngp {
 namespace {
 inline size_t scan_ws_bytes(uint32_t nblocks) { return sizeof(uint32_t) * (2 + (size_t)(nblocks ? nblocks : 1)); }
 inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+// Emit masks of the warp-per-ray marcher: a ray visits at most (far - near) / dt_min + 1 <= bound * max_steps + 1 points
+// (aabb diagonal 2*sqrt(3)*bound, dt_min = 2*sqrt(3)/max_steps); + slack for rounding, + the leading count word.
+inline uint32_t mask_words_for(float bound, uint32_t max_steps) {
+    const double pts = (double)(bound < 1.f ? 1.f : bound) * (double)max_steps + 8.0;
+    return (uint32_t)((pts + 31.0) / 32.0) + 2u;
+}
+inline size_t mask_ws_offset(uint32_t N) { return (scan_ws_bytes(div_round_up(N, 8u)) + 15u) & ~(size_t)15u; }
 }  // namespace
 }  // namespace ngp
 
@@ -71,6 +78,10 @@ size_t ngp_march_rays_train_workspace_bytes(uint32_t N) {
     return ngp::scan_ws_bytes(ngp::div_round_up(N, (uint32_t)ngp::kWarpRays));  // the warp-per-ray variant has the most blocks
 }
 
+size_t ngp_march_rays_train_workspace_bytes_ex(uint32_t N, float bound, uint32_t max_steps) {
+    return ngp::mask_ws_offset(N) + (size_t)N * ngp::mask_words_for(bound, max_steps) * sizeof(uint32_t);
+}
+
 int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
                          uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
                          const float *fars, float *xyzs, float *dirs, float *deltas, int *rays, int *counter,
@@ -89,11 +100,17 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
     march_ws_t *ws = reinterpret_cast<march_ws_t *>(workspace);
     NGP_CHECK_CUDA(cudaMemsetAsync(ws, 0, 2 * sizeof(uint32_t), st));
     if (warp) {
+        // a workspace sized by ngp_march_rays_train_workspace_bytes_ex also carries the per-ray emit masks: pass 2 then
+        // replays them instead of repeating the occupancy tests
+        const uint32_t mw = mask_words_for(bound, max_steps);
+        uint32_t *masks = nullptr;
+        if (workspace_bytes >= mask_ws_offset(N) + (size_t)N * mw * sizeof(uint32_t) && get_option("march_masks", 1))
+            masks = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(workspace) + mask_ws_offset(N));
         { NGP_PROF("k_march_train_count_warp", st); k_march_train_count_warp<<<nb, kWarpRays * 32, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars,
-                                                                  noises, rays, counter, ws); }
+                                                                  noises, rays, counter, ws, masks, mw); }
         NGP_CHECK_LAUNCH();
         { NGP_PROF("k_march_train_write_warp", st); k_march_train_write_warp<<<nb, kWarpRays * 32, 0, st>>>(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears,
-                                                                  fars, noises, xyzs, dirs, deltas, rays, ws); }
+                                                                  fars, noises, xyzs, dirs, deltas, rays, ws, masks, mw); }
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }

@@ -27,8 +27,9 @@ __device__ __forceinline__ bool test_point(const ray_t &r, const march_consts_t 
     y = clampf(__fmaf_rn(t, r.dy, r.oy), -c.bound, c.bound);
     z = clampf(__fmaf_rn(t, r.dz, r.oz), -c.bound, c.bound);
     dt = clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max);
-    const int level = max(mip_of(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), c.Cf), mip_of(__fmul_rn(__fmul_rn(dt, c.Hf), 0.5f), c.Cf));
-    const float mip_bound = fminf(scalbnf(1.0f, level), c.bound);
+    // one cascade: mip_of clamps to [0, C-1] = 0 whatever its argument -- skip the two frexp and the scalbn
+    const int level = c.Cf == 1.0f ? 0 : max(mip_of(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), c.Cf), mip_of(__fmul_rn(__fmul_rn(dt, c.Hf), 0.5f), c.Cf));
+    const float mip_bound = fminf(c.Cf == 1.0f ? 1.0f : scalbnf(1.0f, level), c.bound);
     const float mip_rbound = __fdiv_rn(1.0f, mip_bound);
     const int nx = cell_of(x, mip_rbound, c), ny = cell_of(y, mip_rbound, c), nz = cell_of(z, mip_rbound, c);
     const uint32_t index = (uint32_t)__fmaf_rn((float)level, c.H3, (float)morton3D_1((uint32_t)nx, (uint32_t)ny, (uint32_t)nz));
@@ -45,10 +46,15 @@ __device__ __forceinline__ uint32_t mask_below(uint32_t pos) { return pos >= 32 
 
 // Marches one ray with the whole warp.  cap = most samples to emit (max_steps in the counting pass, the ray's count
 // in the writing pass).  Returns the number of samples; with WRITE also stores them at px / pd / pl.
+// masks (counting pass only, may be null): word 0 = number of 32-point chunks recorded (kMaskOverflow when the ray
+// needed more than mask_words - 1), word 1 + c = emit mask of chunk c -- lets the writing pass skip the occupancy tests.
+constexpr uint32_t kMaskOverflow = 0xffffffffu;
 template <bool WRITE>
 __device__ __forceinline__ uint32_t march_ray_warp(const ray_t &r, const march_consts_t &c, float t0, float far, uint32_t cap, float *px,
-                                                   float *pd, float *pl) {
+                                                   float *pd, float *pl, uint32_t *masks = nullptr, uint32_t mask_words = 0) {
     const uint32_t lane = threadIdx.x & 31;
+    uint32_t chunk = 0;
+    bool mask_ok = true;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t step = 0;
     float t_base = t0, skip_tt = -FLT_MAX, last_t = t0;
@@ -120,10 +126,64 @@ __device__ __forceinline__ uint32_t march_ray_warp(const ray_t &r, const march_c
             }
             last_t = __shfl_sync(0xffffffffu, t_next, 31 - __clz(emit));
         }
+        if (!WRITE && masks != nullptr) {
+            if (chunk + 1 < mask_words) { if (lane == 0) masks[1 + chunk] = emit; }
+            else mask_ok = false;
+            ++chunk;
+        }
         if (done || !(vmask >> 31)) break;
         t_base = run;
     }
+    if (!WRITE && masks != nullptr && lane == 0) masks[0] = mask_ok ? chunk : kMaskOverflow;
     return step;
+}
+
+// Writing pass from the recorded emit masks: regenerate the t sequence (cheap, sequential adds) and evaluate only the
+// sample positions -- no occupancy loads, no skip-rule replay.  Same arithmetic per emitted point as march_ray_warp.
+__device__ __forceinline__ void replay_ray_warp(const ray_t &r, const march_consts_t &c, float t0, const uint32_t *__restrict__ masks,
+                                                float *px, float *pd, float *pl) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t nchunks = masks[0];
+    uint32_t step = 0;
+    float t_base = t0, last_t = t0;
+    const bool const_dt = (c.dt_gamma == 0.0f);
+    const float dt0 = clampf(0.0f, c.dt_min, c.dt_max);
+    for (uint32_t ch = 0; ch < nchunks; ++ch) {
+        float tl = t_base, run = t_base;
+        if (const_dt) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                if (i == (int)lane) tl = run;
+                run = __fadd_rn(run, dt0);
+            }
+        } else {
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+                if (i == (int)lane) tl = run;
+                run = next_t(run, c);
+            }
+        }
+        const uint32_t emit = masks[1 + ch];
+        if (emit) {
+            const float dt = clampf(__fmul_rn(tl, c.dt_gamma), c.dt_min, c.dt_max);
+            const float t_next = __fadd_rn(tl, dt);
+            const uint32_t below = emit & lt;
+            const int src = below ? 31 - __clz(below) : 0;
+            const float prev = __shfl_sync(0xffffffffu, t_next, src);
+            if ((emit >> lane) & 1u) {
+                const uint32_t i = step + __popc(below);
+                px[3 * (size_t)i] = clampf(__fmaf_rn(tl, r.dx, r.ox), -c.bound, c.bound);
+                px[3 * (size_t)i + 1] = clampf(__fmaf_rn(tl, r.dy, r.oy), -c.bound, c.bound);
+                px[3 * (size_t)i + 2] = clampf(__fmaf_rn(tl, r.dz, r.oz), -c.bound, c.bound);
+                pd[3 * (size_t)i] = r.dx; pd[3 * (size_t)i + 1] = r.dy; pd[3 * (size_t)i + 2] = r.dz;
+                *reinterpret_cast<float2 *>(pl + 2 * (size_t)i) = make_float2(dt, __fsub_rn(t_next, below ? prev : last_t));
+            }
+            last_t = __shfl_sync(0xffffffffu, t_next, 31 - __clz(emit));
+            step += __popc(emit);
+        }
+        t_base = run;
+    }
 }
 
 // pass 1: one warp per ray counts; block scan over the kWarpRays counts; the last block to arrive turns the block
@@ -131,7 +191,8 @@ __device__ __forceinline__ uint32_t march_ray_warp(const ray_t &r, const march_c
 __global__ void __launch_bounds__(kWarpRays * 32) k_march_train_count_warp(
     const float *__restrict__ rays_o, const float *__restrict__ rays_d, const uint8_t *__restrict__ grid, float bound, float dt_gamma,
     uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float *__restrict__ nears, const float *__restrict__ fars,
-    const float *__restrict__ noises, int *__restrict__ rays, int *__restrict__ counter, march_ws_t *__restrict__ ws) {
+    const float *__restrict__ noises, int *__restrict__ rays, int *__restrict__ counter, march_ws_t *__restrict__ ws,
+    uint32_t *__restrict__ masks, uint32_t mask_words) {
     __shared__ uint32_t s_cnt[kWarpRays];
     __shared__ uint32_t s_scan[kWarpRays];
     __shared__ uint32_t s_flag;
@@ -141,7 +202,8 @@ __global__ void __launch_bounds__(kWarpRays * 32) k_march_train_count_warp(
     if (n < N) {
         const march_consts_t c = make_consts(bound, dt_gamma, max_steps, C, H, grid);
         const ray_t r = load_ray(rays_o, rays_d, n);
-        num_steps = march_ray_warp<false>(r, c, start_t(nears[n], c, noises[n]), fars[n], max_steps, nullptr, nullptr, nullptr);
+        num_steps = march_ray_warp<false>(r, c, start_t(nears[n], c, noises[n]), fars[n], max_steps, nullptr, nullptr, nullptr,
+                                          masks ? masks + (size_t)n * mask_words : nullptr, mask_words);
     }
     if (lane == 0) s_cnt[wid] = num_steps;
     __syncthreads();
@@ -202,7 +264,7 @@ __global__ void __launch_bounds__(kWarpRays * 32) k_march_train_write_warp(
     const float *__restrict__ rays_o, const float *__restrict__ rays_d, const uint8_t *__restrict__ grid, float bound, float dt_gamma,
     uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *__restrict__ nears, const float *__restrict__ fars,
     const float *__restrict__ noises, float *__restrict__ xyzs, float *__restrict__ dirs, float *__restrict__ deltas, int *__restrict__ rays,
-    const march_ws_t *__restrict__ ws) {
+    const march_ws_t *__restrict__ ws, const uint32_t *__restrict__ masks, uint32_t mask_words) {
     const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kWarpRays + wid;
     if (n >= N) return;
@@ -213,8 +275,12 @@ __global__ void __launch_bounds__(kWarpRays * 32) k_march_train_write_warp(
     if (num_steps == 0 || point_index + num_steps > M) return;
     const march_consts_t c = make_consts(bound, dt_gamma, max_steps, C, H, grid);
     const ray_t r = load_ray(rays_o, rays_d, n);
-    march_ray_warp<true>(r, c, start_t(nears[n], c, noises[n]), fars[n], num_steps, xyzs + 3 * (size_t)point_index,
-                         dirs + 3 * (size_t)point_index, deltas + 2 * (size_t)point_index);
+    float *px = xyzs + 3 * (size_t)point_index, *pd = dirs + 3 * (size_t)point_index, *pl = deltas + 2 * (size_t)point_index;
+    if (masks != nullptr && masks[(size_t)n * mask_words] != kMaskOverflow) {
+        replay_ray_warp(r, c, start_t(nears[n], c, noises[n]), masks + (size_t)n * mask_words, px, pd, pl);
+        return;
+    }
+    march_ray_warp<true>(r, c, start_t(nears[n], c, noises[n]), fars[n], num_steps, px, pd, pl);
 }
 
 // ---- compositor, one warp per ray (reference :500-577 / :601-691) ---------------------------------------------

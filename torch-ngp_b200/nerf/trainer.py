@@ -103,7 +103,7 @@ class NGPTrainer:
         self.rays = torch.zeros(N, 3, dtype=torch.int32, device=dev)
         self.ws, self.depth, self.image = torch.empty(N, **f32), torch.empty(N, **f32), torch.empty(N, 3, **f32)
         self.g_image, self.g_ws, self.g_depth = torch.empty(N, 3, **f32), torch.empty(N, **f32), torch.empty(N, **f32)
-        self.march_ws = torch.zeros(max(1 << 16, abi.lib.ngp_march_rays_train_workspace_bytes(N)), dtype=torch.uint8, device=dev)
+        self.march_ws = torch.zeros(max(1 << 16, abi.lib.ngp_march_rays_train_workspace_bytes_ex(N, self.bound, self.max_steps)), dtype=torch.uint8, device=dev)
         self.mlp_ws = torch.zeros(1 << 17, dtype=torch.uint8, device=dev)
         self.M = 0
         self._graph = None

@@ -37,6 +37,7 @@ SIGNATURES = {
     "ngp_morton3D_invert": (_int, [_vp, _u32, _vp, _vp]),
     "ngp_packbits": (_int, [_vp, _u32, _f32, _vp, _vp]),
     "ngp_march_rays_train_workspace_bytes": (_sz, [_u32]),
+    "ngp_march_rays_train_workspace_bytes_ex": (_sz, [_u32, _f32, _u32]),
     "ngp_march_rays_train": (_int, [_vp, _vp, _vp, _f32, _f32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ngp_composite_rays_train_forward": (_int, [_vp, _vp, _vp, _vp, _u32, _u32, _f32, _vp, _vp, _vp, _vp]),
     "ngp_composite_rays_train_backward": (_int, [_vp] * 10 + [_u32, _u32, _f32, _vp, _vp, _vp]),

@@ -69,7 +69,11 @@ def march_rays_train(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, 
     abi.check_tensor(rays, "rays", _i32, "an int", 3 * N)
     abi.check_tensor(counter, "counter", _i32, "an int", 2)
     abi.check_tensor(noises, "noises", _f32, "a float", N)
-    nbytes = abi.lib.ngp_march_rays_train_workspace_bytes(N)
+    # the larger workspace also carries the emit masks of pass 1 (pass 2 replays them); fall back to the scan-only one
+    # when that would be unreasonably large (many rays x large bound)
+    nbytes = abi.lib.ngp_march_rays_train_workspace_bytes_ex(N, float(bound), max_steps)
+    if nbytes > (256 << 20):
+        nbytes = abi.lib.ngp_march_rays_train_workspace_bytes(N)
     ws = _workspace(rays_o.device, nbytes)
     abi.check(abi.lib.ngp_march_rays_train(
         rays_o.data_ptr(), rays_d.data_ptr(), grid.data_ptr(), float(bound), float(dt_gamma), max_steps, N, C, H, M,
