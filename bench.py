@@ -98,6 +98,8 @@ def dist_setup(n_gpus):
         torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo", rank=rank, world_size=world)
@@ -398,7 +400,104 @@ class NerfTrainWorkload:
                           "oracle/nerf_step_ref.py: C+OpenMP hash grid / marcher / compositor, numpy MLPs and Adam"}
 
 
-WORKLOADS = {"hashgrid": HashGridWorkload, "nerf_train": NerfTrainWorkload}
+# ==================================================================================================
+# workload: inference rendering (BASELINE.json configs[3])
+# ==================================================================================================
+class RenderWorkload:
+    """1920x1080 frames of the synthetic scene from a 128^3 density bitfield: march_rays / composite_rays loop with the
+    network_ff model (briefly pre-trained so that the occupancy grid is that of a scene).  Each rank renders one
+    contiguous band of rows (nerf/parallel.py::row_band), no collective; a step is one frame (one band per rank)."""
+    name = "render"
+    metric = "render Mrays/s"
+    unit = "Mrays/s"
+    dtype = "f16"
+    scaling = "strong"
+
+    def __init__(self, args):
+        self.args = args
+        self.W, self.Hh = (1920, 1080) if not args.points else (args.points, args.points * 9 // 16)
+
+    def setup(self, dev, rank, world):
+        import torch
+        import nerf
+        from nerf import synthetic
+        from nerf.parallel import row_band
+        self.torch, self.dev = torch, dev
+        torch.manual_seed(7)
+        self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=4096, device=dev, seed=0, use_graph=True)
+        o, d, gt = synthetic.make_pool(16, 4096, dev, seed=1)
+        tr.set_pool(o, d, gt)
+        for _ in range(self.args.pretrain):
+            tr.next_pool_batch()
+            tr.train_step()
+        self.band = row_band(self.Hh, rank, world)
+        self.frames = [synthetic.frame_rays(self.W, self.Hh, dev, pose_index=i * 7, rows=self.band) for i in range(4)]
+        self.frames_host = [(o.cpu().pin_memory(), d.cpu().pin_memory()) for o, d in self.frames]
+        self.i = 0
+        self.units_per_step = (self.band[1] - self.band[0]) * self.W
+        self.h2d_bytes = self.units_per_step * 6 * 4
+        self.d2h_bytes = self.units_per_step * 4 * 4
+        self.T = tr.T
+        self.out_host = torch.empty(self.units_per_step, 3).pin_memory()
+        self.depth_host = torch.empty(self.units_per_step).pin_memory()
+
+    def config(self, world):
+        c = {"workload": f"inference render {self.W}x{self.Hh} frames, march_rays/composite_rays from a 128^3 bitfield + network_ff shading (configs[3])",
+             "parallelism": f"{world} row bands, no collective", "l2": "flushed between steps (256 MiB memset outside the per-step events)",
+             "pretrain_steps": self.args.pretrain}
+        if hasattr(self, "tr"):
+            c.update({"rows_per_gpu": self.band[1] - self.band[0], "loop_iterations": getattr(self.tr, "last_render_iters", None)})
+        return c
+
+    def step_device(self):
+        o, d = self.frames[self.i % 4]
+        self.i += 1
+        self.tr.render(o, d)
+
+    def step_e2e(self):
+        o, d = self.frames_host[self.i % 4]
+        self.i += 1
+        img, depth = self.tr.render(o.to(self.dev, non_blocking=True), d.to(self.dev, non_blocking=True))
+        self.out_host.copy_(img, non_blocking=True)
+        self.depth_host.copy_(depth, non_blocking=True)
+        self.torch.cuda.synchronize()
+        return float(self.out_host[0, 0])
+
+    def roofline(self, prof, peaks, steps):
+        cand = {k: v for k, v in prof.items() if k.startswith(("k_grid_fwd", "k_ffmlp_fwd", "k_march_rays", "k_composite_rays"))}
+        if not cand:
+            return None
+        name = max(cand, key=lambda k: cand[k][1])
+        cnt, ms = cand[name]
+        total_ms = sum(v[1] for v in prof.values())
+        return {"bound": "hbm", "kernel": name, "achieved": None, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
+                "peak_source": peaks["source"], "us_per_launch": ms / cnt * 1e3, "launches_per_step": cnt / steps,
+                "share_of_step_kernel_time": ms / total_ms if total_ms else None,
+                "note": "per-iteration sample counts vary; algorithmic bytes are reported for the training workload"}
+
+    def cpu_baseline(self, budget_s=15.0):
+        from oracle import cpu_ref, nerf_step_ref as R
+        import scenes
+        cpu_ref.build()
+        offs, pls = cpu_ref.make_offsets(desired_resolution=2048)
+        rng = np.random.default_rng(0)
+        k = np.sqrt(3 / 64)
+        st = R.RefState(((rng.random((offs[-1], 2)) * 2 - 1) * 1e-4).astype(np.float32), ((rng.random(64 * 112) * 2 - 1) * k).astype(np.float32),
+                        ((rng.random(64 * 176) * 2 - 1) * k).astype(np.float32), offs, pls, 16)
+        bits = scenes.bitfield_from_grid(scenes.density_grid(H=128), 0.01)
+        W, Hh = 96, 54
+        ro, rd = scenes.frame_rays(W, Hh, pose_index=3)
+        t_total, n = 0.0, 0
+        while t_total < budget_s and n < 16:
+            t0 = time.perf_counter()
+            R.render(st, ro, rd, bits, 1, 128)
+            t_total += time.perf_counter() - t0
+            n += 1
+        return {"value": W * Hh * n / t_total / 1e6, "unit": self.unit, "cores": os.cpu_count(), "kind": "port",
+                "sample": f"{n} frames of {W}x{Hh} rays (1/400 of a 1920x1080 frame), oracle/nerf_step_ref.py::render on the analytic occupancy grid"}
+
+
+WORKLOADS = {"hashgrid": HashGridWorkload, "nerf_train": NerfTrainWorkload, "render": RenderWorkload}
 DEFAULT_WORKLOAD = "nerf_train"
 
 

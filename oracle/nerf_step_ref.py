@@ -27,24 +27,32 @@ class RefState:
         self.m = [np.zeros_like(p) for p in self.params()]
         self.v = [np.zeros_like(p) for p in self.params()]
         self.t, self.lr0, self.scale = 0, lr, loss_scale
+        self._h16 = None
 
     def params(self):
         return [self.table, self.sigma_w, self.color_w]
+
+    def half(self):
+        """fp16-rounded copies of the parameters (what the kernels read under autocast), cached until the next update."""
+        if self._h16 is None:
+            self._h16 = (_h(self.table), _h(self.sigma_w), _h(self.color_w))
+        return self._h16
 
 
 def network_forward(st, xyzs, dirs, bound, density_scale=1.0):
     """-> sigmas [M], rgbs [M,3] and the saved tensors for the backward (network_ff.py:51-74 under fp16 autocast)."""
     x01 = ((xyzs + np.float32(bound)) / np.float32(2 * bound)).astype(np.float32)
-    enc_lbc, _ = cpu_ref.grid_encode_forward(x01, _h(st.table), st.offsets, st.pls, st.H0)
+    table16, sigma16, color16 = st.half()
+    enc_lbc, _ = cpu_ref.grid_encode_forward(x01, table16, st.offsets, st.pls, st.H0)
     M = xyzs.shape[0]
     enc = _h(np.transpose(enc_lbc, (1, 0, 2)).reshape(M, -1))
-    h, _ = cpu_ref.ffmlp_forward(enc, _h(st.sigma_w), 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
+    h, _ = cpu_ref.ffmlp_forward(enc, sigma16, 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
     h = _h(h)
     sigmas = (np.float32(density_scale) * np.exp(h[:, 0])).astype(np.float32)
     cin = np.zeros((M, 32), np.float32)
     cin[:, :16] = _h(cpu_ref.sh_encode(dirs, 4))
     cin[:, 16:31] = h[:, 1:]
-    c, _ = cpu_ref.ffmlp_forward(cin, _h(st.color_w), 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
+    c, _ = cpu_ref.ffmlp_forward(cin, color16, 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
     c = _h(c)
     rgbs = _h(1.0 / (1.0 + np.exp(-c[:, :3])))
     return sigmas, rgbs, dict(x01=x01, enc=enc, h=h, cin=cin, c=c)
@@ -69,16 +77,16 @@ def forward_backward(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, bo
                                                          T_thresh)
     g_c = np.zeros((M, 16), np.float32)
     g_c[:, :3] = _h(g_rgb * rgbs * (1 - rgbs))
-    g_cin, g_col = cpu_ref.ffmlp_backward(g_c, sv["cin"], _h(st.color_w), 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
+    g_cin, g_col = cpu_ref.ffmlp_backward(g_c, sv["cin"], st.half()[2], 32, 16, 64, 3, dtype=np.float32, round_activations_fp16=True)
     g_h = np.zeros((M, 16), np.float32)
     g_h[:, 0] = g_sig * np.float32(density_scale) * np.exp(np.clip(sv["h"][:, 0], -15, 15))
     g_h[:, 1:] = _h(g_cin)[:, 16:31]
     g_h = _h(g_h)
-    g_enc, g_sw = cpu_ref.ffmlp_backward(g_h, sv["enc"], _h(st.sigma_w), 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
+    g_enc, g_sw = cpu_ref.ffmlp_backward(g_h, sv["enc"], st.half()[1], 32, 16, 64, 2, dtype=np.float32, round_activations_fp16=True)
     g_enc = _h(g_enc)
     L = st.offsets.shape[0] - 1
     g_lbc = np.ascontiguousarray(np.transpose(g_enc.reshape(M, L, -1), (1, 0, 2)))
-    g_table, _ = cpu_ref.grid_encode_backward(g_lbc, sv["x01"], _h(st.table), st.offsets, st.pls, st.H0)
+    g_table, _ = cpu_ref.grid_encode_backward(g_lbc, sv["x01"], st.half()[0], st.offsets, st.pls, st.H0)
     return loss, (g_table, g_sw.astype(np.float32), g_col.astype(np.float32)), int(counter[0])
 
 
@@ -89,6 +97,7 @@ def adam_step(st, grads, grad_div=1.0, beta1=0.9, beta2=0.99, eps=1e-15, decay_s
         return False
     lr = st.lr0 * 0.1 ** min(st.t / decay_steps, 1.0)
     st.t += 1
+    st._h16 = None
     bc1, bc2 = 1 - beta1 ** st.t, 1 - beta2 ** st.t
     for p, m, v, g in zip(st.params(), st.m, st.v, grads):
         g = g.reshape(p.shape).astype(np.float32) / np.float32(st.scale * grad_div)
@@ -104,3 +113,27 @@ def train_step(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, **kw):
     loss, grads, n = forward_backward(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, **kw)
     adam_step(st, grads)
     return loss, n
+
+
+def render(st, rays_o, rays_d, bitfield, cascade, grid_size, bound=1.0, min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4,
+           density_scale=1.0):
+    """Inference loop of nerf/renderer.py:346-431 on the per-op oracles -> image [N,3], depth [N]."""
+    N = rays_o.shape[0]
+    aabb = np.array([-bound] * 3 + [bound] * 3, np.float32)
+    nears, fars = cpu_ref.near_far_from_aabb(rays_o, rays_d, aabb, min_near)
+    ws, depth, image = np.zeros(N, np.float32), np.zeros(N, np.float32), np.zeros((N, 3), np.float32)
+    alive = np.arange(N, dtype=np.int32)
+    rays_t = nears.copy()
+    step = 0
+    while step < max_steps and alive.size > 0:
+        n_alive = alive.size
+        n_step = max(min(N // n_alive, 8), 1)
+        xyzs, dirs, deltas = cpu_ref.march_rays(n_alive, n_step, alive, rays_t, rays_o, rays_d, bound, bitfield, cascade, grid_size, nears, fars,
+                                                dt_gamma=dt_gamma, max_steps=max_steps)
+        sigmas, rgbs, _ = network_forward(st, xyzs, dirs, bound, density_scale)
+        cpu_ref.composite_rays(n_alive, n_step, alive, rays_t, sigmas, rgbs, deltas, ws, depth, image, T_thresh)
+        alive = alive[alive >= 0]
+        step += n_step
+    image = image + (1 - ws)[:, None] * np.float32(bg_color)
+    depth = np.clip(depth - nears, 0, None) / (fars - nears)
+    return image, depth

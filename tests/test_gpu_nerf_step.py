@@ -216,3 +216,45 @@ def test_device_side_batch_limit():
         abi.check(abi.lib.ngp_set_batch_limit(None))
     y_full, _, gw_full = run(x, g)
     assert torch.equal(y2, y_full) and _rel(gw2, gw_full) < 1e-6
+
+
+def test_inference_render_matches_training_quadrature_and_band_sharding():
+    """NGPTrainer.render (march_rays / composite_rays loop with device-side compaction) against the training-path
+    quadrature of the same rays, and a frame rendered as two row bands against the frame rendered at once."""
+    import nerf
+    import raymarching
+    from nerf import synthetic
+    from nerf.parallel import row_band
+    tr = nerf.NGPTrainer(bound=1.0, num_rays=2048, use_graph=False, log2_hashmap_size=17)
+    o, d, gt = synthetic.make_pool(16, 2048, "cuda", seed=9)
+    tr.set_pool(o, d, gt)
+    for _ in range(96):
+        tr.next_pool_batch()
+        tr.train_step()
+    W = H = 48
+    ro, rd = synthetic.frame_rays(W, H, "cuda", pose_index=7)
+    img, depth = tr.render(ro, rd)
+    assert img.shape == (W * H, 3) and torch.isfinite(img).all() and torch.isfinite(depth).all()
+    # the same rays through the training ops (no perturbation): identical samples, same network, same threshold
+    nears, fars = raymarching.near_far_from_aabb(ro, rd, tr.aabb, tr.min_near)
+    xyzs, dirs, deltas, rays = raymarching.march_rays_train(ro, rd, tr.bound, tr.density_bitfield, tr.cascade, tr.H, nears, fars, None, -1, False,
+                                                             128, True, tr.dt_gamma, tr.max_steps)
+    M = xyzs.shape[0]
+    x01 = torch.empty(M, 3, device="cuda"); enc = torch.empty(M, 32, dtype=torch.half, device="cuda")
+    h = torch.empty(M, 16, dtype=torch.half, device="cuda"); cin = torch.empty(M, 32, dtype=torch.half, device="cuda"); c = torch.empty_like(h)
+    sig = torch.empty(M, device="cuda"); rgb = torch.empty(M, 3, device="cuda")
+    import ngp_abi as abi
+    tr._encode(xyzs.contiguous(), x01, enc, M)
+    tr._sigma_forward(enc, h, M, True)
+    abi.check(abi.lib.ngp_nerf_mid_forward(h.data_ptr(), dirs.contiguous().data_ptr(), tr.density_scale, sig.data_ptr(), cin.data_ptr(), M, abi.stream()))
+    tr._color_forward(cin, c, M, True)
+    abi.check(abi.lib.ngp_nerf_rgb_forward(c.data_ptr(), rgb.data_ptr(), M, abi.stream()))
+    ws, dep, im = raymarching.composite_rays_train(sig, rgb, deltas, rays, 1e-4)
+    ref = im + (1 - ws).unsqueeze(-1) * tr.bg_color
+    assert (img - ref).abs().max() < 2e-3, float((img - ref).abs().max())
+    # two bands == whole frame (inference shards rows over the ranks, no collective)
+    parts = []
+    for r in range(2):
+        r0, r1 = row_band(H, r, 2)
+        parts.append(tr.render(ro[r0 * W:r1 * W], rd[r0 * W:r1 * W])[0])
+    assert torch.allclose(torch.cat(parts), img, atol=1e-5)

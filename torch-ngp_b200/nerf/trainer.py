@@ -342,3 +342,61 @@ class NGPTrainer:
 
     def mean_density(self):
         return float(self.mean_sum.item()) / self.density_grid.numel()
+
+    # ---- inference rendering (nerf/renderer.py:346-431, the `not self.training` branch of run_cuda) ----------------
+    @torch.no_grad()
+    def render(self, rays_o, rays_d, perturb=False, T_thresh=1e-4, max_iters=None):
+        """Image [N,3], depth [N] for the given rays (one row band of a frame per rank when sharded, nerf/parallel.py).
+        The loop of the reference: march up to n_step samples for every ray still alive, shade them, composite in place,
+        drop the finished rays -- here on buffers allocated once per call, with the alive list compacted on the device
+        (raymarching.compact_alive) and one 4-byte read of the alive count per iteration to size the next launch."""
+        lib, s, dev = abi.lib, abi.stream(), self.dev
+        rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
+        N = rays_o.shape[0]
+        f32 = dict(dtype=torch.float32, device=dev)
+        nears, fars = torch.empty(N, **f32), torch.empty(N, **f32)
+        _ck(lib.ngp_near_far_from_aabb(rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(), N, self.min_near, nears.data_ptr(), fars.data_ptr(), s))
+        ws, depth, image = torch.zeros(N, **f32), torch.zeros(N, **f32), torch.zeros(N, 3, **f32)
+        alive = [torch.arange(N, dtype=torch.int32, device=dev), torch.empty(N, dtype=torch.int32, device=dev)]
+        n_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        rays_t = nears.clone()
+        cap = N * 8 + 128  # n_alive * n_step <= N by construction (n_step = min(N // n_alive, 8)) except n_step = 1: <= N
+        cap = max(cap, N + 128)
+        xyzs, dirs, deltas = torch.zeros(cap, 3, **f32), torch.zeros(cap, 3, **f32), torch.zeros(cap, 2, **f32)
+        x01 = torch.empty(cap, 3, **f32)
+        f16 = dict(dtype=torch.half, device=dev)
+        enc, h, cin, c = torch.empty(cap, 32, **f16), torch.empty(cap, 16, **f16), torch.empty(cap, 32, **f16), torch.empty(cap, 16, **f16)
+        sigmas, rgbs = torch.empty(cap, **f32), torch.empty(cap, 3, **f32)
+        cws = torch.empty(max(1 << 16, lib.ngp_compact_alive_workspace_bytes(N)), dtype=torch.uint8, device=dev)
+        noises = torch.rand(N, **f32) if perturb else torch.zeros(N, **f32)
+        zeros_n = torch.zeros(N, **f32)
+        n_alive, step, cur, it = N, 0, 0, 0
+        while step < self.max_steps and n_alive > 0:
+            n_step = max(min(N // n_alive, 8), 1)
+            M = n_alive * n_step
+            deltas[:M].zero_()  # a zero delta ends a ray's samples in composite_rays (the reference allocates zeroed buffers every iteration)
+            _ck(lib.ngp_march_rays(n_alive, None, n_step, alive[cur].data_ptr(), rays_t.data_ptr(), rays_o.data_ptr(), rays_d.data_ptr(), self.bound,
+                                   self.dt_gamma, self.max_steps, self.cascade, self.H, self.density_bitfield.data_ptr(), nears.data_ptr(),
+                                   fars.data_ptr(), xyzs.data_ptr(), dirs.data_ptr(), deltas.data_ptr(), (noises if step == 0 else zeros_n).data_ptr(), s))
+            # shade M samples (inference kernels: no activations kept)
+            _ck(lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
+            _ck(lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                            enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                            abi.LAYOUT_BLC, s))
+            _ck(lib.ngp_ffmlp_inference(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, h.data_ptr(), s))
+            _ck(lib.ngp_nerf_mid_forward(h.data_ptr(), dirs.data_ptr(), self.density_scale, sigmas.data_ptr(), cin.data_ptr(), M, s))
+            _ck(lib.ngp_ffmlp_inference(cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, c.data_ptr(), s))
+            _ck(lib.ngp_nerf_rgb_forward(c.data_ptr(), rgbs.data_ptr(), M, s))
+            _ck(lib.ngp_composite_rays(n_alive, None, n_step, T_thresh, alive[cur].data_ptr(), rays_t.data_ptr(), sigmas.data_ptr(), rgbs.data_ptr(),
+                                       deltas.data_ptr(), ws.data_ptr(), depth.data_ptr(), image.data_ptr(), s))
+            _ck(lib.ngp_compact_alive(alive[cur].data_ptr(), n_alive, None, alive[cur ^ 1].data_ptr(), n_dev.data_ptr(), cws.data_ptr(), cws.numel(), s))
+            cur ^= 1
+            n_alive = int(n_dev.item())
+            step += n_step
+            it += 1
+            if max_iters is not None and it >= max_iters:
+                break
+        image = image + (1 - ws).unsqueeze(-1) * self.bg_color
+        depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+        self.last_render_iters = it
+        return image, depth
