@@ -366,9 +366,21 @@ class NerfTrainWorkload:
             ach, peak, unit = work / sec / 1e9, peaks["hbm_gbs"], "GB/s"
         else:
             ach, peak, unit = work / sec / 1e12, peaks["tflops"], "TFLOP/s"
-        return {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": None,
+        return {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": self._traffic(name, S),
                 "peak_source": peaks["source"], "algorithmic_work_per_launch": work, "us_per_launch": sec * 1e6,
                 "share_of_step_kernel_time": ms / total_ms if total_ms else None, "samples_per_step": S}
+
+    def _traffic(self, name, S):
+        """DRAM bytes (read + write) per launch of that kernel from the committed `ncu --set full` capture
+        (profiles/r1_nerf_train_ncu_summary.json), scaled per sample to this run's sample count; None if absent."""
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_nerf_train_ncu_summary.json")) as f:
+                cap = json.load(f)
+            runs = next(v for k, v in cap["kernels"].items() if name.startswith(k))
+            per = sum(r["dram_read_bytes"] + r["dram_write_bytes"] for r in runs) / len(runs)
+            return per if name.startswith(("k_adam", "k_found_inf")) else per * S / cap["samples"]
+        except Exception:
+            return None
 
     # ---- CPU baseline: the oracle's restatement of the same step, all host cores, bounded sample ----
     def cpu_baseline(self, budget_s=15.0):

@@ -398,16 +398,27 @@ template <> struct group_io<__half> {
     }
 };
 
+__device__ __forceinline__ float2 pick_word_h2(const uint4 &u, uint32_t e) {
+    const uint32_t lo = (e & 1u) ? u.y : u.x, hi = (e & 1u) ? u.w : u.z;
+    const uint32_t w = (e & 2u) ? hi : lo;
+    return __half22float2(*reinterpret_cast<const __half2 *>(&w));
+}
 template <typename T>
 __device__ __forceinline__ float2 gather8_v2(const T *__restrict__ tab, const rows3_t &r) {
     float2 v0[4], v1[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         if ((r.i0[k] >> 2) == (r.i1[k] >> 2)) {  // same 4-entry group: one sector-wide access
-            float v[8];
-            group_io<T>::load4(tab, r.i0[k] & ~3u, v);
-            v0[k] = pick4(v, r.i0[k] & 3u);
-            v1[k] = pick4(v, r.i1[k] & 3u);
+            if constexpr (sizeof(T) == 2) {  // fp16: select the 32-bit entry first, convert only what is used
+                const uint4 u = __ldg(reinterpret_cast<const uint4 *>(tab + 2 * (size_t)(r.i0[k] & ~3u)));
+                v0[k] = pick_word_h2(u, r.i0[k] & 3u);
+                v1[k] = pick_word_h2(u, r.i1[k] & 3u);
+            } else {
+                float v[8];
+                group_io<T>::load4(tab, r.i0[k] & ~3u, v);
+                v0[k] = pick4(v, r.i0[k] & 3u);
+                v1[k] = pick4(v, r.i1[k] & 3u);
+            }
         } else {
             v0[k] = entry_io<T>::load1_nc(tab, r.i0[k]);
             v1[k] = entry_io<T>::load1_nc(tab, r.i1[k]);
@@ -454,8 +465,17 @@ __global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restri
                                                            uint32_t interp, int layout, const int *__restrict__ limit) {
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
     const uint32_t l0 = blockIdx.y * 4;
+    // the block's 4 levels: constants (exp2f, strides, hashed / dense) evaluated once, not once per thread
+    __shared__ level_t s_lv[4];
+    __shared__ geo3_t s_g[4];
+    if (threadIdx.x < 4) {
+        const level_t lv = level_consts(offsets, l0 + threadIdx.x, S, H);
+        s_lv[threadIdx.x] = lv;
+        s_g[threadIdx.x] = make_geo3(lv, gridtype, align_corners);
+    }
+    __syncthreads();
+    if (b >= B) return;
     const float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
     const bool oob = (x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
     float2 res[4];
@@ -463,8 +483,8 @@ __global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restri
     for (int k = 0; k < 4; ++k) {
         res[k] = make_float2(0.f, 0.f);
         if (oob) continue;
-        const level_t lv = level_consts(offsets, l0 + k, S, H);
-        const geo3_t g = make_geo3(lv, gridtype, align_corners);
+        const level_t lv = s_lv[k];
+        const geo3_t g = s_g[k];
         loc3_t o;
         locate3x(x0, x1, x2, lv.scale, align_corners, interp, o);
         rows3_t r;
@@ -488,6 +508,14 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t l0 = blockIdx.y * 4;
+    __shared__ level_t s_lv[4];
+    __shared__ geo3_t s_g[4];
+    if (threadIdx.x < 4) {
+        const level_t lv = level_consts(offsets, l0 + threadIdx.x, S, H);
+        s_lv[threadIdx.x] = lv;
+        s_g[threadIdx.x] = make_geo3(lv, gridtype, align_corners);
+    }
+    __syncthreads();
     float x0 = 0.f, x1 = 0.f, x2 = 0.f;
     if (b < B) { x0 = inputs[3 * (size_t)b]; x1 = inputs[3 * (size_t)b + 1]; x2 = inputs[3 * (size_t)b + 2]; }
     const bool valid = (b < B) && !(x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
@@ -505,8 +533,8 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const level_t lv = level_consts(offsets, l0 + k, S, H);
-        const geo3_t g = make_geo3(lv, gridtype, align_corners);
+        const level_t lv = s_lv[k];
+        const geo3_t g = s_g[k];
         T *tab = grad_grid + (size_t)lv.offset * 2;
         loc3_t o;
         rows3_t r;
