@@ -193,14 +193,18 @@ NGP_API int ngp_nerf_loss(const float *image, const float *weights_sum, const fl
 NGP_API int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream);
 NGP_API int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *grad_cin, float density_scale, void *grad_h,
                           uint32_t M, void *stream);
+/* SDF regression loss (sdf/utils.py:217-225, loss.py:7-15 mape_loss, mean over B): h [B,16] f16 (column 0 = prediction),
+ * target [B] f32 -> *loss_out += loss, grad_h [B,16] f16 (scaled by *loss_scale) */
+NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream);
 NGP_API int ngp_step_begin(float *state, float beta1, float beta2, void *stream);
 NGP_API int ngp_step_end(float *state, void *stream);
 /* sets state.found_inf when any gradient is inf/nan: g16 = n16 halves (n16 % 8 == 0), g32 = n32 floats (n32 % 4 == 0) */
 NGP_API int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t n32, float *state, void *stream);
 /* Adam over params[0 .. n16+n32): first n16 have fp16 gradients + an fp16 shadow copy, last n32 fp32 gradients; gradients are
- * divided by (loss scale * grad_div), consumed and CLEARED; skipped (but still cleared) when state.found_inf */
+ * divided by (loss scale * grad_div), consumed and CLEARED; skipped (but still cleared) when state.found_inf;
+ * weight_decay32: torch.optim.Adam's L2 weight decay for the fp32-gradient group (main_sdf.py:51-54), 0 for NeRF */
 NGP_API int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
-                  const float *state, float beta1, float beta2, float eps, float grad_div, void *stream);
+                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream);
 NGP_API int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream);
 /* grid = max(grid*decay, tmp) where both >= 0; *sum_out = sum(clamp(grid, 0)) */
 NGP_API int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, float *sum_out, void *stream);

@@ -134,6 +134,30 @@ __global__ void __launch_bounds__(256) k_nerf_mid_bwd(const float *__restrict__ 
 }
 
 
+
+// SDF regression (sdf/utils.py:217-225 with loss.py:7-15 mape_loss, mean): pred = h[:, 0] (fp16 MLP output row of 16),
+//   loss += |pred - y| / (|y| + 1e-2) / B ;  grad_h[:, 0] = scale * sign(pred - y) / (|y| + 1e-2) / B, other columns 0
+__global__ void __launch_bounds__(256) k_sdf_loss(const uint4 *__restrict__ h, const float *__restrict__ target, uint32_t B,
+                                                  const float *__restrict__ loss_scale, uint4 *__restrict__ grad_h, float *__restrict__ loss_out,
+                                                  const int *__restrict__ limit) {
+    B = eff_batch(B, limit);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float l = 0.f;
+    if (i < B) {
+        const float pred = unh2(__ldg(reinterpret_cast<const uint32_t *>(h + 2 * (size_t)i))).x;
+        const float y = target[i];
+        const float w = 1.0f / (fabsf(y) + 1e-2f), d = pred - y;
+        l = fabsf(d) * w;
+        const float s = loss_scale ? *loss_scale : 1.0f;
+        const float g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+        grad_h[2 * (size_t)i] = make_uint4(h2(s * g * w / (float)B, 0.f), 0u, 0u, 0u);
+        grad_h[2 * (size_t)i + 1] = make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+    if ((threadIdx.x & 31) == 0 && l != 0.f) atomicAdd(loss_out, l / (float)B);
+}
+
 // ---- optimizer ---------------------------------------------------------------------------------------------
 // Device-resident step state (float[16], ints bit-cast), so a captured step needs no host-side scalars:
 //   [0] optimizer step count (int)   [1] lr for this step      [2] 1 - beta1^t        [3] 1 - beta2^t
@@ -198,7 +222,7 @@ __global__ void __launch_bounds__(256) k_found_inf(const uint4 *__restrict__ g16
 //   m = b1 m + (1-b1) g ; v = b2 v + (1-b2) g^2 ; p -= lr / bc1 * m / (sqrt(v) / sqrt(bc2) + eps)
 __global__ void __launch_bounds__(256) k_adam(float4 *__restrict__ p, float4 *__restrict__ m, float4 *__restrict__ v, uint2 *__restrict__ g16,
                                               float4 *__restrict__ g32, uint2 *__restrict__ shadow, size_t n16_4, size_t n32_4,
-                                              const float *__restrict__ st, float beta1, float beta2, float eps, float grad_div) {
+                                              const float *__restrict__ st, float beta1, float beta2, float eps, float grad_div, float wd32) {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n16_4 + n32_4) return;
     const bool skip = __float_as_int(st[ST_FOUND_INF]) != 0;
@@ -218,9 +242,10 @@ __global__ void __launch_bounds__(256) k_adam(float4 *__restrict__ p, float4 *__
     const float lr = st[ST_LR], bc1 = st[ST_BC1], rbc2 = rsqrtf(st[ST_BC2]);
     float4 pp = p[i], mm = m[i], vv = v[i];
     float *pf = &pp.x, *mf = &mm.x, *vf = &vv.x;
+    const float wd = i < n16_4 ? 0.f : wd32;  // torch.optim.Adam weight_decay (L2 term added to the gradient), MLP group only
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float gk = g[k] * inv;
+        const float gk = g[k] * inv + wd * pf[k];
         mf[k] = beta1 * mf[k] + (1.0f - beta1) * gk;
         vf[k] = beta2 * vf[k] + (1.0f - beta2) * gk * gk;
         pf[k] -= (lr / bc1) * mf[k] / (sqrtf(vf[k]) * rbc2 + eps);
@@ -340,6 +365,16 @@ int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *g
     return NGP_OK;
 }
 
+int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream) {
+    using namespace ngp;
+    if (B == 0) return NGP_OK;
+    NGP_CHECK_ARG(h && target && grad_h && loss_out, "sdf_loss: null pointer argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    { NGP_PROF("k_sdf_loss", st); k_sdf_loss<<<NGP_GRID1(B)>>>((const uint4 *)h, target, B, loss_scale, (uint4 *)grad_h, loss_out, batch_limit()); }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
 int ngp_step_begin(float *state, float beta1, float beta2, void *stream) {
     using namespace ngp;
     NGP_CHECK_ARG(state, "step_begin: null pointer argument");
@@ -374,7 +409,7 @@ int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t n32, flo
 }
 
 int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
-                  const float *state, float beta1, float beta2, float eps, float grad_div, void *stream) {
+                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream) {
     using namespace ngp;
     NGP_CHECK_ARG(params && exp_avg && exp_avg_sq && state && (n16 == 0 || (g16 && shadow16)) && (n32 == 0 || g32), "adam_step: null pointer argument");
     NGP_CHECK_ARG(n16 % 4 == 0 && n32 % 4 == 0, "adam_step: segment sizes must be multiples of 4");
@@ -382,7 +417,7 @@ int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, f
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n4 = (n16 + n32) / 4;
     { NGP_PROF("k_adam", st); k_adam<<<(uint32_t)((n4 + 255) / 256), 256, 0, st>>>((float4 *)params, (float4 *)exp_avg, (float4 *)exp_avg_sq, (uint2 *)g16, (float4 *)g32,
-                                                           (uint2 *)shadow16, n16 / 4, n32 / 4, state, beta1, beta2, eps, grad_div); }
+                                                           (uint2 *)shadow16, n16 / 4, n32 / 4, state, beta1, beta2, eps, grad_div, weight_decay32); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

@@ -61,7 +61,8 @@ SIGNATURES = {
     "ngp_step_begin": (_int, [_vp, _f32, _f32, _vp]),
     "ngp_step_end": (_int, [_vp, _vp]),
     "ngp_found_inf": (_int, [_vp, _sz, _vp, _sz, _vp, _vp]),
-    "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _vp]),
+    "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _f32, _vp]),
+    "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp]),
     "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
     "ngp_density_ema": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
     "ngp_packbits_mean": (_int, [_vp, _u32, _vp, _f32, _f32, _vp, _vp]),
