@@ -6,7 +6,7 @@ One JSON line on stdout (rank 0).  Workloads (BASELINE.json `configs`):
     hashgrid    configs[0]  GridEncoder fwd+bwd, 2^18 random points, L=16 F=2 log2_hashmap=19, fp32
     nerf_train  configs[1]/[2]  NeRF training step (hash grid + cuda_ray + fp16), 4096 rays per GPU per step
     render      configs[3]  1920x1080 inference frame, row bands sharded over the GPUs
-    sdf         configs[4]  hash-grid SDF + FFMLP, 2^20 points per GPU per step
+    sdf         configs[4]  hash-grid SDF + FFMLP training step, 2^20 points per GPU per step
 A "step" is one pass of the hot path over one batch of synthetic input.  `value` is timed with inputs
 resident in HBM; `e2e` is the same metric through the public plugin API with pinned HOST inputs, the
 H2D copy and a D2H read of the result inside the timed region.  `--impl reference` times the CPU
@@ -98,8 +98,9 @@ def dist_setup(n_gpus):
         torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            os.environ.pop("NCCL_DEBUG")  # both levels print "NCCL version ..." on stdout; keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo", rank=rank, world_size=world)
@@ -509,7 +510,109 @@ class RenderWorkload:
                 "sample": f"{n} frames of {W}x{Hh} rays (1/400 of a 1920x1080 frame), oracle/nerf_step_ref.py::render on the analytic occupancy grid"}
 
 
-WORKLOADS = {"hashgrid": HashGridWorkload, "nerf_train": NerfTrainWorkload, "render": RenderWorkload}
+# ==================================================================================================
+# workload: hash-grid SDF training step with the FFMLP tensor-core path (BASELINE.json configs[4])
+# ==================================================================================================
+class SDFWorkload:
+    """main_sdf --fp16 --ff on an analytic torus: 2^20 points per GPU per step (surface / near-surface / uniform samples),
+    hash grid 16x2 T=2^19 -> FFMLP 32->64x3->1, mape loss, GradScaler + Adam; data-parallel over points with N>1."""
+    name = "sdf"
+    metric = "sdf train Mpts/s"
+    unit = "Mpts/s"
+    dtype = "f16"
+    scaling = "weak"
+
+    def __init__(self, args):
+        self.args = args
+        self.B = args.points or (1 << 20)
+
+    def setup(self, dev, rank, world):
+        import torch
+        from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
+        self.torch, self.dev = torch, dev
+        self.tr = SDFTrainer(batch=self.B, device=dev, world_size=world, use_graph=not self.args.no_graph)
+        self.batches = [sample_sdf_batch(self.B, dev, seed=100 * rank + i) for i in range(4)]
+        self.batches_host = [(p.cpu().pin_memory(), y.cpu().pin_memory()) for p, y in self.batches]
+        self.i = 0
+        for _ in range(8):
+            self.step_device()
+        self.units_per_step = self.B
+        self.h2d_bytes, self.d2h_bytes = self.B * 16, 4
+        self.T = self.tr.T
+
+    def config(self, world):
+        c = {"workload": "main_sdf --fp16 --ff training step, analytic torus SDF, 2^20 points/batch per GPU (configs[4])",
+             "parallelism": f"dp{world}" + (" (NCCL all-reduce of table + MLP gradients)" if world > 1 else ""),
+             "l2": "flushed between steps (256 MiB memset outside the per-step events)", "points_per_gpu": self.B}
+        if hasattr(self, "tr"):
+            c["last_loss"] = self.tr.loss()
+        return c
+
+    def step_device(self):
+        p, y = self.batches[self.i % 4]
+        self.i += 1
+        self.tr.train_step(p, y)
+
+    def step_e2e(self):
+        p, y = self.batches_host[self.i % 4]
+        self.i += 1
+        self.tr.train_step(p, y)
+        return self.tr.loss()
+
+    def profile_mode(self, on):
+        self._saved = getattr(self, "_saved", self.tr.use_graph)
+        self.tr.use_graph = False if on else self._saved
+
+    def launches_per_step(self):
+        import ngp_abi as abi
+        saved, self.tr.use_graph = self.tr.use_graph, False
+        n0 = abi.launch_count()
+        self.step_device()
+        n = abi.launch_count() - n0
+        self.tr.use_graph = saved
+        return n
+
+    def roofline(self, prof, peaks, steps):
+        tr, B = self.tr, self.B
+        hb = B * (12 + 9 * tr.L * tr.C * 2)
+        table = {"k_grid_fwd": ("hbm", hb), "k_grid_bwd": ("hbm", hb), "k_adam": ("hbm", tr.n16 * 28 + tr.n32 * 32),
+                 "k_ffmlp_fwd": ("tensor", 2 * tr.n32 * B), "k_ffmlp_bwd": ("tensor", 6 * tr.n32 * B)}
+        cand = {k: v for k, v in prof.items() if any(k.startswith(p) for p in table)}
+        if not cand:
+            return None
+        name = max(cand, key=lambda k: cand[k][1])
+        cnt, ms = cand[name]
+        bound, work = next(v for p, v in table.items() if name.startswith(p))
+        sec = ms / cnt * 1e-3
+        total_ms = sum(v[1] for v in prof.values())
+        ach, peak, unit = (work / sec / 1e9, peaks["hbm_gbs"], "GB/s") if bound == "hbm" else (work / sec / 1e12, peaks["tflops"], "TFLOP/s")
+        return {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": None,
+                "peak_source": peaks["source"], "algorithmic_work_per_launch": work, "us_per_launch": sec * 1e6,
+                "share_of_step_kernel_time": ms / total_ms if total_ms else None}
+
+    def cpu_baseline(self, budget_s=15.0):
+        from oracle import cpu_ref, nerf_step_ref as R
+        cpu_ref.build()
+        offs, pls = cpu_ref.make_offsets(desired_resolution=2048)
+        rng = np.random.default_rng(0)
+        st = R.SDFRefState(((rng.random((offs[-1], 2)) * 2 - 1) * 1e-4).astype(np.float32),
+                           ((rng.random(64 * (32 + 128 + 16)) * 2 - 1) * np.sqrt(3 / 64)).astype(np.float32), offs, pls, 16)
+        Bs = 1 << 15
+        p = (rng.random((Bs, 3)) * 2 - 1).astype(np.float32)
+        y = (np.linalg.norm(np.stack([np.hypot(p[:, 0], p[:, 2]) - 0.5, p[:, 1]], -1), axis=-1) - 0.2).astype(np.float32)
+        loss, grads = R.sdf_forward_backward(st, p, y)
+        t_total, n = 0.0, 0
+        while t_total < budget_s and n < 32:
+            t0 = time.perf_counter()
+            loss, grads = R.sdf_forward_backward(st, p, y)
+            R.sdf_adam_step(st, grads)
+            t_total += time.perf_counter() - t0
+            n += 1
+        return {"value": Bs * n / t_total / 1e6, "unit": self.unit, "cores": os.cpu_count(), "kind": "port",
+                "sample": f"{n} training steps of 2^15 points (full-size table and MLP), oracle/nerf_step_ref.py::sdf_forward_backward + sdf_adam_step"}
+
+
+WORKLOADS = {"hashgrid": HashGridWorkload, "nerf_train": NerfTrainWorkload, "render": RenderWorkload, "sdf": SDFWorkload}
 DEFAULT_WORKLOAD = "nerf_train"
 
 

@@ -137,3 +137,47 @@ def render(st, rays_o, rays_d, bitfield, cascade, grid_size, bound=1.0, min_near
     image = image + (1 - ws)[:, None] * np.float32(bg_color)
     depth = np.clip(depth - nears, 0, None) / (fars - nears)
     return image, depth
+
+
+# ---- SDF step (main_sdf.py --fp16 --ff): hash grid -> FFMLP 32 -> 64 x 3 -> 1, mape loss ------------------------------------
+class SDFRefState:
+    def __init__(self, table, mlp_w, offsets, per_level_scale, base_resolution, lr=1e-4, loss_scale=65536.0, weight_decay=1e-6):
+        self.table, self.mlp_w = table.astype(np.float32), mlp_w.astype(np.float32)
+        self.offsets, self.pls, self.H0 = np.asarray(offsets, np.int32), float(per_level_scale), int(base_resolution)
+        self.m, self.v = [np.zeros_like(self.table), np.zeros_like(self.mlp_w)], [np.zeros_like(self.table), np.zeros_like(self.mlp_w)]
+        self.t, self.lr, self.scale, self.wd = 0, lr, loss_scale, weight_decay
+
+
+def sdf_forward_backward(st, points, sdfs, hid=64, nl=3):
+    """-> loss, (g_table, g_mlp) carrying the loss scale (sdf/utils.py:217-225 + loss.py:7-15, fp16 autocast)."""
+    B = points.shape[0]
+    x01 = ((points + np.float32(1)) / np.float32(2)).astype(np.float32)
+    t16, w16 = _h(st.table), _h(st.mlp_w)
+    enc_lbc, _ = cpu_ref.grid_encode_forward(x01, t16, st.offsets, st.pls, st.H0)
+    enc = _h(np.transpose(enc_lbc, (1, 0, 2)).reshape(B, -1))
+    h, _ = cpu_ref.ffmlp_forward(enc, w16, 32, 16, hid, nl, dtype=np.float32, round_activations_fp16=True)
+    pred = _h(h)[:, 0]
+    w = 1.0 / (np.abs(sdfs) + np.float32(1e-2))
+    d = pred - sdfs
+    loss = float(np.mean(np.abs(d) * w))
+    g_h = np.zeros((B, 16), np.float32)
+    g_h[:, 0] = _h(np.float32(st.scale) * np.sign(d) * w / np.float32(B))
+    g_enc, g_w = cpu_ref.ffmlp_backward(g_h, enc, w16, 32, 16, hid, nl, dtype=np.float32, round_activations_fp16=True)
+    L = st.offsets.shape[0] - 1
+    g_lbc = np.ascontiguousarray(np.transpose(_h(g_enc).reshape(B, L, -1), (1, 0, 2)))
+    g_table, _ = cpu_ref.grid_encode_backward(g_lbc, x01, t16, st.offsets, st.pls, st.H0)
+    return loss, (g_table, g_w.astype(np.float32))
+
+
+def sdf_adam_step(st, grads, grad_div=1.0, beta1=0.9, beta2=0.99, eps=1e-15):
+    if not all(np.isfinite(g).all() for g in grads):
+        st.scale *= 0.5
+        return False
+    st.t += 1
+    bc1, bc2 = 1 - beta1 ** st.t, 1 - beta2 ** st.t
+    for k, (p, g) in enumerate(zip((st.table, st.mlp_w), grads)):
+        g = g.reshape(p.shape).astype(np.float32) / np.float32(st.scale * grad_div) + (np.float32(st.wd) * p if k == 1 else 0)
+        st.m[k] = beta1 * st.m[k] + (1 - beta1) * g
+        st.v[k] = beta2 * st.v[k] + (1 - beta2) * g * g
+        p -= (st.lr / bc1) * st.m[k] / (np.sqrt(st.v[k]) / np.sqrt(bc2) + eps)
+    return True

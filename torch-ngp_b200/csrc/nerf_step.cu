@@ -153,9 +153,18 @@ __global__ void __launch_bounds__(256) k_sdf_loss(const uint4 *__restrict__ h, c
         grad_h[2 * (size_t)i] = make_uint4(h2(s * g * w / (float)B, 0.f), 0u, 0u, 0u);
         grad_h[2 * (size_t)i + 1] = make_uint4(0u, 0u, 0u, 0u);
     }
+    // one atomic per block (2^20 points would otherwise queue 32768 same-address atomics)
+    __shared__ float s_part[8];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-    if ((threadIdx.x & 31) == 0 && l != 0.f) atomicAdd(loss_out, l / (float)B);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += s_part[w];
+        if (t != 0.f) atomicAdd(loss_out, t / (float)B);
+    }
 }
 
 // ---- optimizer ---------------------------------------------------------------------------------------------

@@ -1,0 +1,147 @@
+"""Device-resident hash-grid SDF training step (BASELINE.json configs[4]; /root/reference/main_sdf.py --fp16 --ff).
+
+Network: sdf/netowrk_ff.py:9-50 -- hash grid (16 x 2, T = 2^19, desired resolution 2048) -> FFMLP 32 -> 64 x 3 -> 1.
+Step: sdf/utils.py:217-225 (pred = model(X); mape_loss, loss.py:7-15) under fp16 autocast + GradScaler,
+Adam(lr 1e-4, betas (0.9, 0.99), eps 1e-15, weight_decay 1e-6 on the MLP; main_sdf.py:51-54).
+Same construction as nerf/trainer.py: flat parameters, fp16 table shadow, fixed launch sequence in two CUDA graphs.
+The EMA of the weights (torch_ema, evaluation only) and the per-epoch StepLR are host-side and out of scope."""
+import numpy as np
+import torch
+
+import ngp_abi as abi
+import ffmlp as _ffmlp
+import gridencoder as _gridencoder
+
+from .trainer import _ST_LAST_LOSS, _ST_LOSS, _ST_SCALE, _ST_LR, _ST_LR0, _ST_DECAY_STEPS, _ST_DECAY, _ST_GROWTH_INTERVAL, _ck
+
+
+class SDFTrainer:
+    def __init__(self, batch=1 << 20, device="cuda", lr=1e-4, weight_decay=1e-6, loss_scale=65536.0, growth_interval=2000, world_size=1, seed=0,
+                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19):
+        self.dev = dev = torch.device(device)
+        self.B, self.world, self.use_graph = int(batch), world_size, use_graph
+        self.beta1, self.beta2, self.eps, self.wd = 0.9, 0.99, 1e-15, weight_decay
+        self.nl, self.hid = num_layers, hidden_dim
+        enc = _gridencoder.GridEncoder(num_levels=16, log2_hashmap_size=log2_hashmap_size, desired_resolution=2048)
+        self.L, self.C, self.base_resolution = enc.num_levels, enc.level_dim, enc.base_resolution
+        self.S = float(np.log2(enc.per_level_scale))
+        self.per_level_scale = enc.per_level_scale
+        self.offsets = enc.offsets.to(dev)
+        self.offsets_host = np.ascontiguousarray(enc.offsets.numpy().astype(np.int32))
+        self.T = int(enc.offsets[-1])
+        net = _ffmlp.FFMLP(32, 1, hidden_dim, num_layers)
+        self.n16, self.n32 = self.T * self.C, net.num_parameters
+        g = torch.Generator().manual_seed(seed)
+        table0 = (torch.rand(self.T, self.C, generator=g) * 2 - 1) * 1e-4
+        self.params = torch.cat([table0.reshape(-1), net.weights.detach()]).to(dev).contiguous()
+        self.exp_avg, self.exp_avg_sq = torch.zeros_like(self.params), torch.zeros_like(self.params)
+        self.embeddings = self.params[:self.n16].view(self.T, self.C)
+        self.mlp_w = self.params[self.n16:]
+        self.table16 = torch.empty(self.T, self.C, dtype=torch.half, device=dev)
+        _ck(abi.lib.ngp_cast_f16(self.params.data_ptr(), self.table16.data_ptr(), self.n16, abi.stream()))
+        self.g16 = torch.zeros(self.T, self.C, dtype=torch.half, device=dev)
+        self.g32 = torch.zeros(self.n32, device=dev)
+        st = torch.zeros(16)
+        i32 = lambda v: torch.tensor(v, dtype=torch.int32).view(torch.float32)
+        st[0], st[5], st[6], st[_ST_GROWTH_INTERVAL] = i32(0), i32(0), i32(0), i32(growth_interval)
+        st[_ST_SCALE], st[_ST_LR0], st[_ST_LR], st[_ST_DECAY_STEPS], st[_ST_DECAY] = loss_scale, lr, lr, 1e30, 1.0  # constant lr inside an epoch
+        self.state = st.to(dev)
+        B = self.B
+        f16 = dict(dtype=torch.half, device=dev)
+        self.points, self.sdfs = torch.zeros(B, 3, device=dev), torch.zeros(B, device=dev)
+        self.x01 = torch.empty(B, 3, device=dev)
+        self.enc, self.h = torch.empty(B, 32, **f16), torch.empty(B, 16, **f16)
+        self.g_h, self.g_enc = torch.empty(B, 16, **f16), torch.empty(B, 32, **f16)
+        self.mlp_ws = torch.zeros(1 << 17, dtype=torch.uint8, device=dev)
+        self._graph = None
+        self.global_step = 0
+
+    def _forward_backward(self):
+        s, lib, B = abi.stream(), abi.lib, self.B
+        _ck(lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s))
+        _ck(lib.ngp_nerf_x01(self.points.data_ptr(), 1.0, self.x01.data_ptr(), B, s))  # encoder(x, bound=1): (x + 1) / 2
+        _ck(lib.ngp_grid_encode_forward(self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                        self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                        abi.LAYOUT_BLC, s))
+        _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s))
+        _ck(lib.ngp_sdf_loss(self.h.data_ptr(), self.sdfs.data_ptr(), B, self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(),
+                             self.state[_ST_LOSS:].data_ptr(), s))
+        _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, None, B, 32, 16, self.hid, self.nl, 0, 6, 1,
+                                   None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
+        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
+                                         self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
+                                         None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+
+    def _optimizer_step(self):
+        s, lib = abi.stream(), abi.lib
+        _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
+        _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
+                              self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world),
+                              self.wd, s))
+        _ck(lib.ngp_step_end(self.state.data_ptr(), s))
+
+    def _step_eager(self):
+        self._forward_backward()
+        if self.world > 1:
+            from .parallel import allreduce_gradients
+            allreduce_gradients(self.g16, self.g32)
+        self._optimizer_step()
+
+    def train_step(self, points=None, sdfs=None):
+        """points [B,3] in [-1,1], sdfs [B] (device or pinned host tensors); None keeps the current batch buffers."""
+        if points is not None:
+            self.points.copy_(points, non_blocking=True)
+            self.sdfs.copy_(sdfs, non_blocking=True)
+        if self.use_graph and self._graph is None:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._step_eager()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            self._g_fb, self._g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._g_fb):
+                self._forward_backward()
+            with torch.cuda.graph(self._g_opt):
+                self._optimizer_step()
+            self._graph = True
+        elif self.use_graph:
+            self._g_fb.replay()
+            if self.world > 1:
+                from .parallel import allreduce_gradients
+                allreduce_gradients(self.g16, self.g32)
+            self._g_opt.replay()
+        else:
+            self._step_eager()
+        self.global_step += 1
+
+    def loss(self):
+        return float(self.state[_ST_LAST_LOSS].item())
+
+    @torch.no_grad()
+    def predict(self, points):
+        n = points.shape[0]
+        x01, enc, h = torch.empty(n, 3, device=self.dev), torch.empty(n, 32, dtype=torch.half, device=self.dev), torch.empty(n, 16, dtype=torch.half, device=self.dev)
+        s = abi.stream()
+        _ck(abi.lib.ngp_nerf_x01(points.contiguous().data_ptr(), 1.0, x01.data_ptr(), n, s))
+        _ck(abi.lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data, enc.data_ptr(),
+                                            n, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+        _ck(abi.lib.ngp_ffmlp_inference(enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, n, 32, 16, self.hid, self.nl, 0, 6, None, h.data_ptr(), s))
+        return h[:, 0].float()
+
+
+# ---- synthetic data: analytic torus, sampled like sdf/provider.py:60-90 (surface, near-surface, uniform) -----------------
+def torus_sdf(p, R=0.5, r=0.2):
+    q = torch.stack([torch.sqrt(p[..., 0] ** 2 + p[..., 2] ** 2) - R, p[..., 1]], -1)
+    return q.norm(dim=-1) - r
+
+
+def sample_sdf_batch(n, device, seed=0, R=0.5, r=0.2):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    ns = n * 7 // 8
+    u, v = torch.rand(ns, generator=g) * 2 * np.pi, torch.rand(ns, generator=g) * 2 * np.pi
+    surf = torch.stack([(R + r * torch.cos(v)) * torch.cos(u), r * torch.sin(v), (R + r * torch.cos(v)) * torch.sin(u)], -1)
+    surf[ns // 2:] += 0.01 * torch.randn(ns - ns // 2, 3, generator=g)  # perturbed surface points
+    unif = torch.rand(n - ns, 3, generator=g) * 2 - 1
+    p = torch.cat([surf, unif]).clamp(-1, 1).float().contiguous().to(device)
+    return p, torus_sdf(p, R, r).contiguous()

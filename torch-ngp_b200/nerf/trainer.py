@@ -30,6 +30,7 @@ _ST_STEP, _ST_LR, _ST_BC1, _ST_BC2, _ST_SCALE, _ST_GROWTH, _ST_FOUND_INF, _ST_LO
 
 def _ck(rc):
     abi.check(rc)
+    return rc
 
 
 class NGPTrainer:
