@@ -17,7 +17,7 @@ for (B, i, o, h, nl) in [(1 << 20, 32, 16, 64, 3), (1 << 20, 32, 16, 64, 2)]:
     nw = h * (i + h * (nl - 1) + o)
     w = ((torch.rand(nw, device="cuda") * 2 - 1) * np.sqrt(3 / h))
     gx = torch.empty_like(x); gw = torch.empty(nw, device="cuda")
-    for variant, split in [(0, 0), (1, 1), (1, 2)]:
-        abi.set_option("ffmlp_bwd_variant", variant); abi.set_option("ffmlp_bwd_split", split)
+    for variant, split, iss in [(0, 0, 1), (1, 1, 1), (1, 2, 1), (1, 1, 2), (1, 2, 2)]:
+        abi.set_option("ffmlp_bwd_variant", variant); abi.set_option("ffmlp_bwd_split", split); abi.set_option("ffmlp_bwd_issuers", iss)
         us = t(lambda: be.ffmlp_backward(g, x, w, None, B, i, o, h, nl, 0, 6, True, None, gx, gw))
-        print(f"net {i}->{h}x{nl}->{o} variant {variant} split {split}: {us:.1f} us")
+        print(f"net {i}->{h}x{nl}->{o} variant {variant} split {split} issuers {iss}: {us:.1f} us")

@@ -34,6 +34,7 @@ static std::map<std::string, int> &options() {
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
         {"ffmlp_available", 1},
         {"ffmlp_bwd_variant", -1},     // -1 auto / 1: multi-pipeline backward (one MMA-issuer warp, up to 4 tiles in flight), 0: one tile per CTA
+        {"ffmlp_bwd_issuers", 2},      // 2: one issuer warp for the layer products + one for the weight gradients, 1: a single issuer warp
         {"ffmlp_bwd_split", 0},        // 0 auto / 1 / 2: threads sharing one accumulator row in the multi-pipeline backward epilogue
         {"ffmlp_fwd_pipes", 0},        // > 0: cap on the tile pipelines per CTA of the FFMLP forward (tuning)
         {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in

@@ -20,6 +20,7 @@
 //   * input / upstream-gradient tiles are prefetched one tile ahead with cp.async (zero-filled ragged tail).
 #include "common.cuh"
 #include "umma.cuh"
+#include <type_traits>
 
 namespace ngp {
 namespace {
@@ -465,22 +466,42 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
 // ==========================================================================================================
 // The single-tile kernel above serialises, per tile, 2*nl+1 round trips (MMA issue -> commit -> TMEM drain ->
 // st.shared -> barrier); measured on B200 it spends ~200 cycles of SM time per tcgen05.mma against a 32-cycle
-// floor.  Here one CTA per SM keeps NP tiles in flight: warp 0 is the only MMA issuer of the CTA (so the dW
-// accumulators in TMEM can be shared by all pipelines -- one thread's tcgen05.mma stream is ordered), and NP
-// warpgroups of 128 threads each own one tile: they drain the accumulator, apply ReLU / the ReLU mask and hand the
-// operands of the next layer step back through an mbarrier.  Per pipeline: full[p] (128 arrivals: operands in shared
-// memory) -> issuer -> done[p] (tcgen05.commit: accumulator ready).  G_l overwrites H_l in place (each round's
-// commit covers the dW MMA that still reads H_l), which is what makes room for 3-4 tiles in 227 KB.
+// floor.  Here one CTA per SM keeps NP tiles in flight, and NP warpgroups of 128*ns threads each own one tile: they
+// drain the accumulator, apply ReLU / the ReLU mask and hand the operands of the next layer step back through an
+// mbarrier.  Per pipeline: full[p] (operands in shared memory) -> issuer -> done[p] (tcgen05.commit: accumulator
+// ready).  G_l overwrites H_l in place (the commits of a round cover the dW MMA that still reads H_l), which is what
+// makes room for 3-4 tiles in 227 KB.
+// Two issuer warps (benchmarks/umma_issue_bench.cu, handshake_bench.cu: one thread cannot issue tcgen05.mma faster
+// than one per ~64-74 cycles whatever N is, while the pipe takes 48 cycles at N=64 and 40 at N<=32; and every
+// hand-off costs the issuer ~250 cycles of polling): warp 0 issues the layer products (H_l, dH_l) of all pipelines,
+// warp 1 the weight-gradient products.  The dW accumulators in TMEM are shared by all pipelines and touched by
+// warp 1's elected lane only -- one thread's tcgen05.mma stream is ordered.  Each issuer has its own full/done
+// barrier pair per pipeline; the tile's threads wait for both before they overwrite an operand.
+#ifdef NGP_FFMLP_TRACE
+// developer build only (benchmarks/ffmlp_trace.py): CTA 0 logs (clock, tag) pairs of its issuers and of the first warp of each pipeline
+__device__ unsigned long long g_tr[8][1024];
+__device__ unsigned g_trn[8];
+#define NGP_TR(slot, tag)                                                                   \
+    do {                                                                                    \
+        if (blockIdx.x == 0 && (threadIdx.x & 31u) == 0 && tr_n < 1024) {                   \
+            g_tr[slot][tr_n] = ((unsigned long long)clock64() << 12) | (unsigned long long)((tag) & 0xfffu); \
+            g_trn[slot] = ++tr_n;  /* stores only: a load of the counter would put ~700 cycles into the timeline */ \
+        }                                                                                   \
+    } while (0)
+#else
+#define NGP_TR(slot, tag) do { } while (0)
+#endif
+
 template <typename WT, int HID>
-__global__ void __launch_bounds__(32 + 128 * 6) k_ffmlp_bwd_mp(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
+__global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                                __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                                int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
-                                                               uint32_t np, uint32_t ns, uint32_t accw, const int *__restrict__ limit) {
+                                                               uint32_t np, uint32_t ns, uint32_t accw, int dual, const int *__restrict__ limit) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
-    __shared__ __align__(8) uint64_t s_full[4];
-    __shared__ __align__(8) uint64_t s_done[4];
+    __shared__ __align__(8) uint64_t s_full[4], s_done[4];    // layer products (single-issuer mode: everything)
+    __shared__ __align__(8) uint64_t s_full2[4], s_done2[4];  // weight-gradient products (two-issuer mode)
     constexpr int STEP = HID >= 32 ? 32 : 16;  // accumulator columns drained per tcgen05.ld
     const uint32_t cw = m.hid / ns;            // columns of a row owned by one of the ns threads that share it
     const uint32_t Beff = eff_batch(m.B, limit);
@@ -506,6 +527,8 @@ __global__ void __launch_bounds__(32 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     if (tid < np) {
         mbar_init(&s_full[tid], 4 * ns);
         mbar_init(&s_done[tid], 1);
+        mbar_init(&s_full2[tid], 4 * ns);
+        mbar_init(&s_done2[tid], 1);
     }
     if (tid == 0) mbar_init_fence();
     fence_proxy_async();
@@ -514,109 +537,169 @@ __global__ void __launch_bounds__(32 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     fence_after_sync();
     const uint32_t tmem = s_tmem;
     const uint32_t stride = gridDim.x * np;
+#ifdef NGP_FFMLP_TRACE
+    unsigned tr_n = 0;
+    bool tr_hit = true;
+#endif
 
-    if (warp == 0) {
-        // ---- the MMA issuer ----
-        uint32_t left[4], rnd[4], ph[4], active = 0, started = 0;
+    // ---- an MMA issuer.  ROLE 0: every product; 1: layer products only; 2: weight-gradient products only ----
+    auto issuer = [&](auto role_c) {
+        constexpr int ROLE = decltype(role_c)::value;
+        uint64_t *fullb = ROLE == 2 ? s_full2 : s_full, *doneb = ROLE == 2 ? s_done2 : s_done;
+        const uint32_t r0 = ROLE == 2 ? m.nl : 0u, r1 = 2 * m.nl + 1;  // rounds of a tile this issuer takes part in
+        uint32_t left[4], rnd[4], phbits = 0, alive = 0, started = 0;
         for (uint32_t p = 0; p < 4; ++p) {
             const uint32_t t0 = blockIdx.x * np + p;
             left[p] = (p < np && t0 < ntiles) ? (ntiles - t0 + stride - 1) / stride : 0u;
-            rnd[p] = 0; ph[p] = 0;
-            active += left[p] ? 1u : 0u;
+            rnd[p] = r0;
+            if (left[p]) alive |= 1u << p;
         }
-        while (active) {
-#pragma unroll
-            for (uint32_t p = 0; p < 4; ++p) {
-                // warp-uniform on purpose (vote): the descriptors below must stay in uniform registers, or every
-                // tcgen05.mma pays a register->uniform-register broadcast loop (measured: ~250 instead of ~64 cycles/MMA)
-                const bool go = p < np && left[p] && mbar_test(&s_full[p], ph[p]);
-                if (!__any_sync(0xffffffffu, go)) continue;
-                ph[p] ^= 1u;
-                fence_after_sync();
-                {
-                    uint8_t *sx = smem + m.wbytes + p * per_pipe, *sgo = sx + goff, *sh = sx + hoff;
-                    const uint32_t acc = tmem + p * accw, rr = rnd[p];
-                    if (rr == 0) {
-                        if (lane == 0) issue_fwd(acc, sx, sw + m.soff[0], m.hid, m.in);
-                    } else if (rr < m.nl) {
-                        if (lane == 0) issue_fwd(acc, sh + (rr - 1) * abytes, sw + m.soff[rr], m.hid, m.hid);
-                    } else if (rr == m.nl) {  // dH_{nl-1} = dY W_last ; dW_last += dY^T H_{nl-1}
-                        if (lane == 0) {
-                            issue_bwd_dx(acc, sgo, sw + m.soff[m.nl], m.hid, m.out);
-                            issue_dw(tmem + dwc[m.nl], sgo, sh + (m.nl - 1) * abytes, m.out, m.hid, (started >> m.nl) & 1u);
-                        }
-                        started |= 1u << m.nl;
-                    } else {
-                        const uint32_t l = 2 * m.nl - rr;  // G_l sits where H_l was
-                        uint8_t *g = sh + l * abytes;
-                        if (lane == 0) {
-                            if (l > 0) {
-                                issue_bwd_dx(acc, g, sw + m.soff[l], m.hid, m.hid);
-                                issue_dw(tmem + dwc[l], g, sh + (l - 1) * abytes, m.hid, m.hid, (started >> l) & 1u);
-                            } else {
-                                if (calc_dx) issue_bwd_dx(acc, g, sw + m.soff[0], m.in, m.hid);
-                                issue_dw(tmem + dwc[0], g, sx, m.hid, m.in, started & 1u);
-                            }
-                        }
-                        started |= 1u << l;
+        while (alive) {
+            // one poll for all pipelines: lane p tests full[p].  The ballot keeps everything below warp-uniform on
+            // purpose: the descriptors must stay in uniform registers, or every tcgen05.mma pays a register ->
+            // uniform-register broadcast loop (measured: ~250 instead of ~64 cycles/MMA)
+            const uint32_t pl = lane & 3u;
+#ifdef NGP_FFMLP_TRACE
+            if (tr_hit) NGP_TR(ROLE == 2 ? 1 : 0, 0xA00u);
+            tr_hit = false;
+#endif
+            const bool ready = lane < 4u && ((alive >> pl) & 1u) && mbar_test(&fullb[pl], (phbits >> pl) & 1u);
+            uint32_t rdy = __ballot_sync(0xffffffffu, ready);
+            if (rdy == 0u) continue;
+            phbits ^= rdy;
+#ifdef NGP_FFMLP_TRACE
+            tr_hit = true;
+            NGP_TR(ROLE == 2 ? 1 : 0, 0xB00u | rdy);
+#endif
+            fence_after_sync();
+            NGP_TR(ROLE == 2 ? 1 : 0, 0x100u | rdy);
+            // p stays a run-time (uniform) value: one copy of the issue code instead of four keeps the issuer's
+            // working set in the instruction cache (the unrolled version was ~200 KB of SASS and paid ~500 cycles
+            // of instruction fetch per round)
+            while (rdy) {
+                const uint32_t p = (uint32_t)__ffs((int)rdy) - 1u;
+                rdy &= rdy - 1u;
+                const uint32_t rr = p == 0 ? rnd[0] : p == 1 ? rnd[1] : p == 2 ? rnd[2] : rnd[3];
+                uint8_t *sx = smem + m.wbytes + p * per_pipe, *sgo = sx + goff, *sh = sx + hoff;
+                const uint32_t acc = tmem + p * accw;
+                const bool leader = elect_one();
+                if (rr == 0) {
+                    if (ROLE != 2 && leader) issue_fwd(acc, sx, sw + m.soff[0], m.hid, m.in);
+                } else if (rr < m.nl) {
+                    if (ROLE != 2 && leader) issue_fwd(acc, sh + (rr - 1) * abytes, sw + m.soff[rr], m.hid, m.hid);
+                } else if (rr == m.nl) {  // dH_{nl-1} = dY W_last ; dW_last += dY^T H_{nl-1}
+                    if (leader) {
+                        if (ROLE != 2) issue_bwd_dx(acc, sgo, sw + m.soff[m.nl], m.hid, m.out);
+                        if (ROLE != 1) issue_dw(tmem + dwc[m.nl], sgo, sh + (m.nl - 1) * abytes, m.out, m.hid, (started >> m.nl) & 1u);
                     }
-                    if (lane == 0) mma_commit(&s_done[p]);
+                    started |= 1u << m.nl;
+                } else {
+                    const uint32_t l = 2 * m.nl - rr;  // G_l sits where H_l was
+                    uint8_t *g = sh + l * abytes;
+                    if (leader) {
+                        if (l > 0) {
+                            if (ROLE != 2) issue_bwd_dx(acc, g, sw + m.soff[l], m.hid, m.hid);
+                            if (ROLE != 1) issue_dw(tmem + dwc[l], g, sh + (l - 1) * abytes, m.hid, m.hid, (started >> l) & 1u);
+                        } else {
+                            if (ROLE != 2 && calc_dx) issue_bwd_dx(acc, g, sw + m.soff[0], m.in, m.hid);
+                            if (ROLE != 1) issue_dw(tmem + dwc[0], g, sx, m.hid, m.in, started & 1u);
+                        }
+                    }
+                    started |= 1u << l;
                 }
-                __syncwarp();
-                if (++rnd[p] == 2 * m.nl + 1) {
-                    rnd[p] = 0;
-                    if (--left[p] == 0) --active;
+                NGP_TR(ROLE == 2 ? 1 : 0, 0xC00u | (p << 4) | rr);
+                if (leader) mma_commit(&doneb[p]);
+                NGP_TR(ROLE == 2 ? 1 : 0, 0x200u | (p << 4) | rr);
+                const bool wrap = rr + 1u == r1;
+                bool last = false;
+#pragma unroll
+                for (uint32_t q = 0; q < 4; ++q) {
+                    if (q == p) {
+                        rnd[q] = wrap ? r0 : rr + 1u;
+                        if (wrap) last = --left[q] == 0u;
+                    }
                 }
+                if (last) alive &= ~(1u << p);
             }
+            __syncwarp();
         }
+    };
+
+    if (warp == 0) {
+        if (dual) issuer(std::integral_constant<int, 1>{});
+        else issuer(std::integral_constant<int, 0>{});
+    } else if (warp == 1) {
+        if (dual) issuer(std::integral_constant<int, 2>{});
     } else {
         // ---- tile pipelines ----
         // pipeline p = 4*ns consecutive warps; warp w drains TMEM lanes 32*(w%4).. (hardware rule) = tile rows, and the
         // column group cg = (warp within pipeline) / 4 of width cw, so one row is handled by ns threads in parallel
-        const uint32_t wpp = 4u * ns, p = (warp - 1) / wpp, wp = (warp - 1) - p * wpp, cg = wp >> 2, q = warp & 3u;
+        const uint32_t wpp = 4u * ns, p = (warp - 2) / wpp, wp = (warp - 2) - p * wpp, cg = wp >> 2, q = warp & 3u;
         const uint32_t row = q * 32u + lane, ptid = wp * 32u + lane, nth = 128u * ns;
         if (p < np) {
             uint8_t *sx = smem + m.wbytes + p * per_pipe, *sh = sx + hoff;
             const uint32_t trow = tmem + p * accw + ((q * 32u) << 16);
-            uint32_t phase = 0;
+            uint32_t phase = 0, phase2 = 0;
             for (uint32_t tile = blockIdx.x * np + p; tile < ntiles; tile += stride) {
                 load_rows_async(sx, x, tile * kTileRows, Beff, m.in, ptid, nth);
                 if (packed) load_rows_async(sx, grad, tile * kTileRows, Beff, m.out, ptid, nth, m.in >> 3);
                 else load_rows_async(sx + xbytes, grad, tile * kTileRows, Beff, m.out, ptid, nth);
+                if (wp == 0) NGP_TR(2 + p, 0x300u);
                 cp_async_commit();
                 cp_async_wait<0>();
                 fence_proxy_async();
                 __syncwarp();
-                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
-                for (uint32_t l = 0; l < m.nl; ++l) {  // forward recompute: H_l = ReLU(W_l H_{l-1})
+                if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                if (wp == 0) NGP_TR(2 + p, 0x301u);
+                for (uint32_t l = 0; l < m.nl; ++l) {    // forward recompute: H_l = ReLU(W_l H_{l-1})
                     mbar_wait(&s_done[p], phase);
                     phase ^= 1u;
                     fence_after_sync();
+                    if (wp == 0) NGP_TR(2 + p, 0x400u | l);
                     for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0);
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                    if (lane == 0) {
+                        mbar_arrive(&s_full[p]);
+                        if (dual && l + 1 == m.nl) mbar_arrive(&s_full2[p]);  // dW_last reads dY and H_{nl-1}
+                    }
+                    if (wp == 0) NGP_TR(2 + p, 0x500u | l);
                 }
                 for (int l = (int)m.nl - 1; l >= 0; --l) {  // G_l = dH_l * (H_l > 0), in place
                     mbar_wait(&s_done[p], phase);
                     phase ^= 1u;
+                    if (dual) {  // the dW product of the previous round still read H_l
+                        mbar_wait(&s_done2[p], phase2);
+                        phase2 ^= 1u;
+                    }
                     fence_after_sync();
+                    if (wp == 0) NGP_TR(2 + p, 0x600u | (uint32_t)l);
                     uint8_t *h = sh + (uint32_t)l * abytes;
                     for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_mask_to_tile<STEP>(trow, h, h, row, c0);
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                    if (lane == 0) {
+                        mbar_arrive(&s_full[p]);
+                        if (dual) mbar_arrive(&s_full2[p]);
+                    }
+                    if (wp == 0) NGP_TR(2 + p, 0x700u | (uint32_t)l);
                 }
                 mbar_wait(&s_done[p], phase);
                 phase ^= 1u;
                 fence_after_sync();
+                if (wp == 0) NGP_TR(2 + p, 0x800u);
                 if (calc_dx) {
                     const uint32_t grow = tile * kTileRows + row;
                     for (uint32_t c0 = cg * 16u; c0 < m.in; c0 += ns * 16u)
                         epi_to_global(trow, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < Beff);
                 }
+                if (dual) {  // dW_0 reads G_0 and X: both are overwritten by the next tile
+                    mbar_wait(&s_done2[p], phase2);
+                    phase2 ^= 1u;
+                }
+                if (wp == 0) NGP_TR(2 + p, 0x900u);
                 fence_before_sync();
             }
         }
@@ -626,8 +709,8 @@ __global__ void __launch_bounds__(32 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     fence_after_sync();
 
     // ---- flush the CTA's dW accumulators: TMEM lane = output row of the matrix; pipeline index = column group ----
-    if (warp > 0 && blockIdx.x * np < ntiles) {
-        const uint32_t grp = (warp - 1) >> 2, ngrp = np * ns, q = warp & 3u, row = q * 32u + lane;
+    if (warp > 1 && blockIdx.x * np < ntiles) {
+        const uint32_t grp = (warp - 2) >> 2, ngrp = np * ns, q = warp & 3u, row = q * 32u + lane;
         if (grp < ngrp) {
             const uint32_t trow = tmem + ((q * 32u) << 16);
             for (uint32_t i = 0; i <= m.nl; ++i) {
@@ -825,7 +908,7 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (m.wbytes + 2048 < kMaxSmem) np = (uint32_t)((kMaxSmem - 2048 - m.wbytes) / per_pipe);  // 2 KB: static shared + alignment
         if (dwcols < 512) { if (np > (512 - dwcols) / accw) np = (512 - dwcols) / accw; } else np = 0;
         if (np > 4) np = 4;
-        // ns threads share a row's epilogue (latency); 32 + 128 * np * ns <= 800 threads keeps 80 registers per thread
+        // ns threads share a row's epilogue (latency); 64 + 128 * np * ns <= 832 threads keeps 72 registers per thread
         uint32_t ns = hidden_dim >= 64 ? 2u : 1u;
         const int ns_opt = get_option("ffmlp_bwd_split", 0);
         if (ns_opt == 1 || ns_opt == 2) ns = (uint32_t)ns_opt;
@@ -837,6 +920,7 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (np > ntiles) np = ntiles;
         if (variant != 0 && (np >= 2 || (variant == 1 && np >= 1))) {
             const size_t smem_mp = m.wbytes + np * per_pipe;
+            const int dual = get_option("ffmlp_bwd_issuers", 2) != 1;
             const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
             uint32_t grid_mp = div_round_up(ntiles, np);
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();
@@ -845,8 +929,8 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         rc = set_smem(k_ffmlp_bwd_mp<WT_, HID_>, smem_mp);                                                                   \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd_mp", st);                                                                                      \
-        k_ffmlp_bwd_mp<WT_, HID_><<<grid_mp, 32 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, batch_limit());   \
+        k_ffmlp_bwd_mp<WT_, HID_><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit());   \
     }
 #define NGP_BWDMP_HID(WT_)                                         \
     switch (hidden_dim) {                                          \
@@ -885,3 +969,13 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
 }
 
 }  // extern "C"
+
+#ifdef NGP_FFMLP_TRACE
+extern "C" __attribute__((visibility("default"))) int ngp_ffmlp_trace_dump(unsigned long long *events, unsigned *counts, int reset) {
+    cudaDeviceSynchronize();
+    if (events) cudaMemcpyFromSymbol(events, ngp::g_tr, sizeof(unsigned long long) * 8 * 1024);
+    if (counts) cudaMemcpyFromSymbol(counts, ngp::g_trn, sizeof(unsigned) * 8);
+    if (reset) { unsigned z[8] = {0, 0, 0, 0, 0, 0, 0, 0}; cudaMemcpyToSymbol(ngp::g_trn, z, sizeof(z)); }
+    return 0;
+}
+#endif

@@ -135,6 +135,19 @@ __device__ __forceinline__ void mma_commit(uint64_t *mbar) {
 __device__ __forceinline__ void mbar_init(uint64_t *mbar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(mbar)), "r"(count) : "memory");
 }
+// one lane of a converged warp (elect.sync).  Branching on this instead of `lane == 0` lets the compiler keep the
+// tcgen05 instructions of the region in the uniform datapath without an ELECT/BRA waterfall around each of them.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t *mbar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(mbar)) : "memory");
 }

@@ -11,7 +11,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libngp_b200.so")
+LIB_PATH = os.environ.get("NGP_B200_LIB") or os.path.join(_HERE, "lib", "libngp_b200.so")  # override: developer builds (benchmarks/)
 
 DTYPE_F32, DTYPE_F16, DTYPE_F64 = 0, 1, 2
 LAYOUT_LBC, LAYOUT_BLC = 0, 1
