@@ -213,7 +213,7 @@ class HashGridWorkload:
         name = max(grid, key=lambda k: grid[k][1])
         cnt, ms = grid[name]
         share = 1.0
-        if not name.endswith("_lg4"):  # the split variants: shared-memory levels vs L2 levels
+        if not (name.endswith("_lg4") or name.endswith("_v3")):  # the split variants: shared-memory levels vs L2 levels
             ns = self.n_smem_levels(prof)
             share = (ns if name.endswith("_smem") else self.L - ns) / self.L
         alg = self.B * (12 + 9 * self.L * self.C * 4) * share
@@ -677,6 +677,7 @@ def main():
     ap.add_argument("--pretrain", type=int, default=1024, help="nerf_train: untimed optimisation steps before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="nerf_train: launch the step eagerly instead of replaying CUDA graphs")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=INT", help="ngp_set_option before setup (kernel A/B tests; development only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -693,6 +694,9 @@ def main():
     dev = torch.device("cuda", local)
     import ngp_abi as abi
     peaks = load_peaks()
+    for kv in args.opt:
+        k, v = kv.split("=")
+        abi.set_option(k, int(v))
     wl.setup(dev, rank, world)
     flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 

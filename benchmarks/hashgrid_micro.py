@@ -62,27 +62,31 @@ def main():
         emb = ((torch.rand_like(enc.embeddings) - 0.5) * 2).to(dtype)
         a_fwd = B * (4 * D + 8 * L * C * s + L * C * s)
         a_bwd = B * (L * C * s + 4 * D + 8 * L * C * s) + emb.numel() * s
-        for layout, ltag in ((0, "LBC"), (1, "BLC")):
+        for layout, ltag in ((1, "BLC"),):
             out = torch.empty(L * B * C, device=dev, dtype=dtype)
             g = torch.randn(L * B * C, device=dev).to(dtype)
             ge = torch.zeros_like(emb)
-            for fv, sm in ((0, 0), (-1, 0), (-1, 1)):
-                abi.set_option("hashgrid_fwd_variant", fv)
-                abi.set_option("hashgrid_smem_levels", sm)
+            DEF = dict(hashgrid_fwd_variant=-1, hashgrid_bwd_variant=-1, hashgrid_v3_minb_fwd=-1, hashgrid_v3_minb_bwd=-1, hashgrid_v3_mix_fwd=0, hashgrid_v3_mix_bwd=1, hashgrid_bwd_red4=0, hashgrid_bwd_warp_agg=1)
+
+            def setopts(**kw):
+                for k_, v_ in {**DEF, **kw}.items():
+                    abi.set_option(k_, v_)
+            for nm, kw in (("lg4", dict(hashgrid_fwd_variant=2)), ("v3_mix0", {}), ("v3_mix1", dict(hashgrid_v3_mix_fwd=1)),
+                           ("v3_mix0_occ4", dict(hashgrid_v3_minb_fwd=4)), ("v3_mix0_occ6", dict(hashgrid_v3_minb_fwd=6))):
+                setopts(**kw)
                 med, mn = time_fn(lambda: be.grid_encode_forward(x, emb, offsets, out, B, D, C, L, S, H, None, 0, False, 0, layout=layout), flush=flush)
-                res[f"fwd_{tag}_{ltag}_v{fv}_smem{sm}"] = dict(us=med, us_min=mn, gbs=a_fwd / med / 1e3)
-            for bv, sm, agg in ((0, 0, 0), (-1, 0, 0), (-1, 0, 1), (-1, 1, 1)):
-                abi.set_option("hashgrid_bwd_variant", bv)
-                abi.set_option("hashgrid_smem_levels", sm)
-                abi.set_option("hashgrid_bwd_warp_agg", agg)
+                res[f"fwd_{tag}_{nm}"] = dict(us=med, us_min=mn, gbs=a_fwd / med / 1e3)
+            for nm, kw in (("lg4", dict(hashgrid_bwd_variant=2)), ("v3_mix0_red4_0", dict(hashgrid_v3_mix_bwd=0, hashgrid_bwd_red4=0)),
+                           ("v3_mix0_red4_1", dict(hashgrid_v3_mix_bwd=0, hashgrid_bwd_red4=1)), ("v3_mix1_red4_0", {}), ("v3_mix1_red4_1", dict(hashgrid_bwd_red4=1)),
+                           ("v3_mix1_red4_0_occ6", dict(hashgrid_v3_minb_bwd=6)), ("v3_mix1_red4_0_noagg", dict(hashgrid_bwd_warp_agg=0))):
+                setopts(**kw)
 
                 def bwd():
                     ge.zero_()
                     be.grid_encode_backward(g, x, emb, offsets, ge, B, D, C, L, S, H, None, None, 0, False, 0, layout=layout)
                 med, mn = time_fn(bwd, flush=flush)
-                res[f"bwd_{tag}_{ltag}_v{bv}_smem{sm}_agg{agg}"] = dict(us=med, us_min=mn, gbs=a_bwd / med / 1e3)
-            abi.set_option("hashgrid_fwd_variant", -1); abi.set_option("hashgrid_bwd_variant", -1)
-            abi.set_option("hashgrid_smem_levels", 1); abi.set_option("hashgrid_bwd_warp_agg", 1)
+                res[f"bwd_{tag}_{nm}"] = dict(us=med, us_min=mn, gbs=a_bwd / med / 1e3)
+            setopts()
         if args.ref:
             from oracle import ref_ext
             ref = ref_ext.load("_gridencoder")

@@ -24,8 +24,13 @@ void set_error(const char *fmt, ...) {
 static std::mutex g_opt_mu;
 static std::map<std::string, int> &options() {
     static std::map<std::string, int> o = {
-        {"hashgrid_fwd_variant", -1},  // -1 auto, 0 generic, 1 paired-gather (point,level) threads, 2 sector-gather (point, 4 levels) threads
+        {"hashgrid_fwd_variant", -1},  // -1 auto, 0 generic, 1 paired-gather (point,level) threads, 2 sector-gather (point, 4 levels) threads, 3 = 2 with per-level-kind index code
         {"hashgrid_bwd_variant", -1},  // -1 auto, 0 generic atomics, 1 paired + warp-aggregated (+ smem levels), 2 (point, 4 levels) threads
+        {"hashgrid_v3_minb_fwd", -1},  // v3 forward: resident blocks per SM the register allocation targets (4 or 6; -1 = by dtype)
+        {"hashgrid_v3_minb_bwd", -1},  // v3 backward: same
+        {"hashgrid_v3_mix_fwd", 0},    // v3 forward: warps of one block work on different level groups (1) or whole blocks do (0)
+        {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
+        {"hashgrid_bwd_red4", 0},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours (faster on random points, slower on ray-ordered samples)
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)

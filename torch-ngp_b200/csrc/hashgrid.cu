@@ -346,4 +346,5 @@ __global__ void __launch_bounds__(256) k_grad_tv(const T *__restrict__ inputs, c
 }  // namespace ngp
 
 #include "hashgrid_fast.cuh"
+#include "hashgrid_v3.cuh"
 #include "hashgrid_host.cuh"

@@ -95,7 +95,21 @@ template <typename T>
 int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *offsets_host, T *out, uint32_t B, uint32_t L,
              float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     const int variant = get_option("hashgrid_fwd_variant", -1);
-    if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
+    if ((variant == -1 || variant == 3) && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
+        const uint32_t ng = L / 4;
+        const bool mix = get_option("hashgrid_v3_mix_fwd", 0) && (ng == 1 || ng == 2 || ng == 4 || ng == 8);
+        const dim3 gr = mix ? dim3(div_round_up(B, 256u / ng), 1, 1) : dim3(div_round_up(B, 256u), ng, 1);
+        const int minb = get_option("hashgrid_v3_minb_fwd", -1);
+        const bool occ6 = minb < 0 ? sizeof(T) == 2 : minb >= 6;  // fp16 groups are 4 registers, fp32 groups 8: 40 registers spill the latter
+        NGP_PROF("k_grid_fwd_v3", st);
+#define NGP_FWD_V3(MINB, MIX) k_grid_fwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit())
+        if (mix) { if (occ6) NGP_FWD_V3(6, true); else NGP_FWD_V3(4, true); }
+        else { if (occ6) NGP_FWD_V3(6, false); else NGP_FWD_V3(4, false); }
+#undef NGP_FWD_V3
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
+    if (variant == 2 && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
         { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
         return NGP_OK;
@@ -128,7 +142,23 @@ template <typename T>
 int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *offsets_host, T *g_emb, uint32_t B, uint32_t L,
              float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     const int variant = get_option("hashgrid_bwd_variant", -1);
-    if ((variant == -1 || variant == 2) && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
+    if ((variant == -1 || variant == 3) && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
+        const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
+        const uint32_t ng = L / 4;
+        const bool mix = get_option("hashgrid_v3_mix_bwd", 1) && (ng == 1 || ng == 2 || ng == 4 || ng == 8);
+        const dim3 gr = mix ? dim3(div_round_up(B, 256u / ng), 1, 1) : dim3(div_round_up(B, 256u), ng, 1);
+        const int minb = get_option("hashgrid_v3_minb_bwd", -1);
+        const bool occ6 = minb < 0 ? false : minb >= 6;
+        const int red4 = get_option("hashgrid_bwd_red4", 0);
+        NGP_PROF("k_grid_bwd_v3", st);
+#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, batch_limit())
+        if (mix) { if (occ6) NGP_BWD_V3(6, true); else NGP_BWD_V3(4, true); }
+        else { if (occ6) NGP_BWD_V3(6, false); else NGP_BWD_V3(4, false); }
+#undef NGP_BWD_V3
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
+    if (variant == 2 && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
         { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, batch_limit()); }
         NGP_CHECK_LAUNCH();
