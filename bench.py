@@ -278,9 +278,12 @@ class NerfTrainWorkload:
         import nerf
         from nerf import synthetic
         self.torch, self.dev, self.world = torch, dev, world
+        self._overlap = not self.args.no_overlap
         torch.manual_seed(1000 + rank)  # ray jitter and density-grid probes; fp16 atomics still make runs differ in the last bits
         self.N = self.args.rays or (4096 if world == 1 else (1 << 18) // world)
-        self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=self.N, device=dev, world_size=world, seed=0, use_graph=not self.args.no_graph)
+        self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=self.N, device=dev, world_size=world, seed=0, use_graph=not self.args.no_graph,
+                                       overlap_optimizer=not self.args.no_overlap)
+        tr.adam_blocks_per_sm = self.args.adam_blocks
         n_batches = 16
         views = max(16, n_batches * self.N // 4096)
         o, d, gt = synthetic.make_pool(views, n_batches * self.N // views, dev, seed=1000 + rank)
@@ -306,7 +309,8 @@ class NerfTrainWorkload:
              "l2": "flushed between steps (256 MiB memset outside the per-step events)", "pretrain_steps": self.args.pretrain}
         if tr is not None:
             c.update({"rays_per_gpu": self.N, "global_rays": self.N * world, "samples_per_ray": round(tr.mean_count / self.N, 2),
-                      "samples_per_step_per_gpu": tr.mean_count, "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph), "density_grid_update": f"every {tr.update_interval} steps, inside the timed region",
+                      "samples_per_step_per_gpu": tr.mean_count, "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph),
+                      "optimizer_overlap": "optimizer(n-1) runs beside march(n) on a second stream, inside step n's timed region" if self._overlap else "none", "density_grid_update": f"every {tr.update_interval} steps, inside the timed region",
                       "last_loss": tr.loss()})
         return c
 
@@ -328,6 +332,9 @@ class NerfTrainWorkload:
         """per-launch CUDA events cannot be recorded inside a graph replay: the profile pass runs the same launches eagerly."""
         self._saved = getattr(self, "_saved", self.tr.use_graph)
         self.tr.use_graph = False if on else self._saved
+        if on:  # per-kernel durations are taken with the kernels one after the other
+            self.tr.flush()
+        self.tr.overlap_optimizer = False if on else self._overlap
 
     def launches_per_step(self):
         """Kernels of this library in one step (graph replays do not pass through the host-side counter)."""
@@ -562,6 +569,9 @@ class SDFWorkload:
     def profile_mode(self, on):
         self._saved = getattr(self, "_saved", self.tr.use_graph)
         self.tr.use_graph = False if on else self._saved
+        if on:  # per-kernel durations are taken with the kernels one after the other
+            self.tr.flush()
+        self.tr.overlap_optimizer = False if on else self._overlap
 
     def launches_per_step(self):
         import ngp_abi as abi
@@ -677,6 +687,8 @@ def main():
     ap.add_argument("--pretrain", type=int, default=1024, help="nerf_train: untimed optimisation steps before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="nerf_train: launch the step eagerly instead of replaying CUDA graphs")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--adam-blocks", type=int, default=5, help="nerf_train: k_adam blocks per SM while it runs beside the marcher")
+    ap.add_argument("--no-overlap", action="store_true", help="nerf_train: optimizer(n) strictly before march(n+1) (default: side by side on two streams)")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=INT", help="ngp_set_option before setup (kernel A/B tests; development only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

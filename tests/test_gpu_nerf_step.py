@@ -142,6 +142,31 @@ def test_graph_and_eager_steps_agree():
     assert _rel(outs[0][1], outs[1][1]) < 2e-2
 
 
+@pytest.mark.parametrize("graph", [False, True])
+def test_overlapped_optimizer_is_the_same_training(graph):
+    """overlap_optimizer defers Adam(n) to run beside march(n+1): after flush() the state is that of the sequential trainer."""
+    outs = []
+    for overlap in (False, True):
+        torch.manual_seed(0)
+        tr = _make(num_rays=1024, graph=graph, perturb=False, update_interval=0, overlap_optimizer=overlap)
+        torch.manual_seed(1)
+        tr.update_extra_state()
+        losses = []
+        for _ in range(6):
+            tr.next_pool_batch()
+            tr.train_step()
+            losses.append(tr.loss())
+        if overlap:
+            assert int(tr.state[0].view(torch.int32)) == 5, "one optimizer step must still be pending"
+        tr.flush()
+        torch.cuda.synchronize()
+        assert int(tr.state[0].view(torch.int32)) == 6
+        outs.append((losses, tr.sigma_w.clone(), tr.embeddings.clone(), tr.table16.clone()))
+    assert np.allclose(outs[0][0], outs[1][0], rtol=1e-3, atol=1e-6), (outs[0][0], outs[1][0])
+    assert _rel(outs[0][1], outs[1][1]) < 2e-2  # fp16 atomics: not bit-exact run to run (see test above)
+    assert torch.equal(outs[1][3], outs[1][2].half())
+
+
 def test_step_matches_cpu_oracle_step():
     """Whole step (march -> encode -> MLPs -> composite -> loss -> backward -> Adam) against oracle/nerf_step_ref.py."""
     from oracle import cpu_ref, nerf_step_ref as R

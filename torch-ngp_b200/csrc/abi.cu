@@ -31,6 +31,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_v3_mix_fwd", 0},    // v3 forward: warps of one block work on different level groups (1) or whole blocks do (0)
         {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
         {"hashgrid_bwd_red4", 0},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours (faster on random points, slower on ray-ordered samples)
+        {"adam_blocks_per_sm", 0},     // k_adam grid cap (0 = one block per 1024 parameters); NGPTrainer sets it when the optimizer shares the SMs with the marcher
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
         {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)

@@ -232,35 +232,37 @@ __global__ void __launch_bounds__(256) k_found_inf(const uint4 *__restrict__ g16
 __global__ void __launch_bounds__(256) k_adam(float4 *__restrict__ p, float4 *__restrict__ m, float4 *__restrict__ v, uint2 *__restrict__ g16,
                                               float4 *__restrict__ g32, uint2 *__restrict__ shadow, size_t n16_4, size_t n32_4,
                                               const float *__restrict__ st, float beta1, float beta2, float eps, float grad_div, float wd32) {
-    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i >= n16_4 + n32_4) return;
     const bool skip = __float_as_int(st[ST_FOUND_INF]) != 0;
-    float g[4];
-    if (i < n16_4) {
-        const uint2 u = g16[i];
-        const float2 a = unh2(u.x), b = unh2(u.y);
-        g[0] = a.x; g[1] = a.y; g[2] = b.x; g[3] = b.y;
-        if (u.x | u.y) g16[i] = make_uint2(0u, 0u);
-    } else {
-        const float4 t = g32[i - n16_4];
-        g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
-        g32[i - n16_4] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    if (skip) return;
     const float inv = 1.0f / (st[ST_SCALE] * grad_div);
     const float lr = st[ST_LR], bc1 = st[ST_BC1], rbc2 = rsqrtf(st[ST_BC2]);
-    float4 pp = p[i], mm = m[i], vv = v[i];
-    float *pf = &pp.x, *mf = &mm.x, *vf = &vv.x;
-    const float wd = i < n16_4 ? 0.f : wd32;  // torch.optim.Adam weight_decay (L2 term added to the gradient), MLP group only
+    // grid-stride: the launch may be capped to a few blocks per SM so that the kernel shares the SMs with the ray marcher
+    // of the next step (NGPTrainer overlap_optimizer); it is HBM-bound and saturates the memory system well below full occupancy
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16_4 + n32_4; i += (size_t)gridDim.x * blockDim.x) {
+        float g[4];
+        if (i < n16_4) {
+            const uint2 u = g16[i];
+            const float2 a = unh2(u.x), b = unh2(u.y);
+            g[0] = a.x; g[1] = a.y; g[2] = b.x; g[3] = b.y;
+            if (u.x | u.y) g16[i] = make_uint2(0u, 0u);
+        } else {
+            const float4 t = g32[i - n16_4];
+            g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+            g32[i - n16_4] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (skip) continue;
+        float4 pp = p[i], mm = m[i], vv = v[i];
+        float *pf = &pp.x, *mf = &mm.x, *vf = &vv.x;
+        const float wd = i < n16_4 ? 0.f : wd32;  // torch.optim.Adam weight_decay (L2 term added to the gradient), MLP group only
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float gk = g[k] * inv + wd * pf[k];
-        mf[k] = beta1 * mf[k] + (1.0f - beta1) * gk;
-        vf[k] = beta2 * vf[k] + (1.0f - beta2) * gk * gk;
-        pf[k] -= (lr / bc1) * mf[k] / (sqrtf(vf[k]) * rbc2 + eps);
+        for (int k = 0; k < 4; ++k) {
+            const float gk = g[k] * inv + wd * pf[k];
+            mf[k] = beta1 * mf[k] + (1.0f - beta1) * gk;
+            vf[k] = beta2 * vf[k] + (1.0f - beta2) * gk * gk;
+            pf[k] -= (lr / bc1) * mf[k] / (sqrtf(vf[k]) * rbc2 + eps);
+        }
+        p[i] = pp; m[i] = mm; v[i] = vv;
+        if (i < n16_4) shadow[i] = make_uint2(h2(pp.x, pp.y), h2(pp.z, pp.w));
     }
-    p[i] = pp; m[i] = mm; v[i] = vv;
-    if (i < n16_4) shadow[i] = make_uint2(h2(pp.x, pp.y), h2(pp.z, pp.w));
 }
 
 // fp32 -> fp16 shadow (initialisation / checkpoint load)
@@ -425,7 +427,10 @@ int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, f
     if (n16 + n32 == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n4 = (n16 + n32) / 4;
-    { NGP_PROF("k_adam", st); k_adam<<<(uint32_t)((n4 + 255) / 256), 256, 0, st>>>((float4 *)params, (float4 *)exp_avg, (float4 *)exp_avg_sq, (uint2 *)g16, (float4 *)g32,
+    uint32_t grid = (uint32_t)((n4 + 255) / 256);
+    const int per_sm = get_option("adam_blocks_per_sm", 0);
+    if (per_sm > 0 && grid > (uint32_t)(per_sm * sm_count())) grid = (uint32_t)(per_sm * sm_count());
+    { NGP_PROF("k_adam", st); k_adam<<<grid, 256, 0, st>>>((float4 *)params, (float4 *)exp_avg, (float4 *)exp_avg_sq, (uint2 *)g16, (float4 *)g32,
                                                            (uint2 *)shadow16, n16 / 4, n32 / 4, state, beta1, beta2, eps, grad_div, weight_decay32); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;

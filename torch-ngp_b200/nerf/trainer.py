@@ -37,8 +37,18 @@ class NGPTrainer:
     def __init__(self, bound=1.0, num_rays=4096, device="cuda", lr=1e-2, grid_size=128, density_thresh=10.0, density_scale=1.0,
                  min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=128.0,
                  growth_interval=2000, decay_steps=30000, world_size=1, seed=0, use_graph=True, update_interval=16,
-                 num_levels=16, log2_hashmap_size=19, base_resolution=16):
+                 num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False):
+        """overlap_optimizer: defer the optimizer of step n to the start of step n+1 and run it on a second stream next to
+        the ray marching of step n+1 (the marcher reads rays and the occupancy bitfield, never the parameters; Adam is
+        HBM-bound, the marcher instruction-bound).  Same arithmetic in the same order; the parameters a caller reads
+        between two steps lag one update until flush() -- loss(), update_extra_state(), density() and render() flush or
+        read around it themselves."""
         self.dev = torch.device(device)
+        self.overlap_optimizer = bool(overlap_optimizer)
+        self._pending = False
+        self._side = None
+        self._g_steady = None
+        self.adam_blocks_per_sm = 5  # grid cap of k_adam while it shares the SMs with the marcher
         self.bound, self.N = float(bound), int(num_rays)
         self.cascade = 1 + math.ceil(math.log2(bound))
         self.H = grid_size
@@ -155,10 +165,10 @@ class NGPTrainer:
         _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s))
 
     # ---- one training step as a fixed launch sequence ---------------------------------------------------------
-    def _forward_backward(self):
+    def _march(self):
+        """Phase A of a step: rays -> samples.  Touches neither the parameters nor the optimizer state."""
         s, N, M, lib = abi.stream(), self.N, self.M, abi.lib
         counter = self.step_counter[0]  # one slot: sample placement starts at counter[0], so it is cleared every step
-        lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s)
         counter.zero_()
         if self.perturb:
             self.noises.uniform_()
@@ -169,6 +179,12 @@ class NGPTrainer:
                                      self.dirs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), counter.data_ptr(), self.noises.data_ptr(),
                                      self.march_ws.data_ptr(), self.march_ws.numel(), s))
         self.count_sum.add_(counter[:1])  # running sample count since the last density-grid update (-> mean_count)
+
+    def _samples(self):
+        """Phase B: network forward, compositing, loss, backward on the samples of phase A."""
+        s, lib = abi.stream(), abi.lib
+        counter = self.step_counter[0]
+        lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s)
         # everything per-sample below runs on min(M, counter[0]) rows, read on the device: no host sync, no padded work
         lib.ngp_set_batch_limit(counter.data_ptr())
         try:
@@ -204,6 +220,7 @@ class NGPTrainer:
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
         _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
+        abi.set_option("adam_blocks_per_sm", self.adam_blocks_per_sm if self.overlap_optimizer else 0)
         _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
                               self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world), 0.0, s))
         _ck(lib.ngp_step_end(self.state.data_ptr(), s))
@@ -212,11 +229,52 @@ class NGPTrainer:
         from .parallel import allreduce_gradients
         allreduce_gradients(self.g16, self.g32)
 
+    def _forward_backward(self):
+        self._march()
+        self._samples()
+
     def _step_eager(self):
         self._forward_backward()
         if self.world > 1:
             self._allreduce()
         self._optimizer_step()
+
+    # ---- deferred optimizer (overlap_optimizer=True) -----------------------------------------------------------------
+    def _run(self, what):
+        """one phase, as a graph replay when captured"""
+        if self.use_graph and self._graph:
+            {"march": self._g_a, "samples": self._g_b, "opt": self._g_opt}[what].replay()
+        else:
+            {"march": self._march, "samples": self._samples, "opt": self._optimizer_step}[what]()
+
+    def flush(self):
+        """Apply the deferred optimizer step, if any, on the current stream."""
+        if self._pending:
+            if self.world > 1:
+                self._allreduce()
+            self._run("opt")
+            self._pending = False
+
+    def _step_overlapped(self):
+        main = torch.cuda.current_stream()
+        if self._pending and self.use_graph and self._graph and self._g_steady is not None:
+            self._g_steady.replay()
+            return
+        if self._pending:
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            self._side.wait_stream(main)  # the gradients of the previous step
+            self._run("march")          # submitted first: its blocks take their share of every SM before Adam's do
+            with torch.cuda.stream(self._side):
+                if self.world > 1:
+                    self._allreduce()
+                self._run("opt")
+            self._pending = False
+            main.wait_stream(self._side)
+        else:
+            self._run("march")
+        self._run("samples")
+        self._pending = True
 
     def _capture(self):
         """Warm up eagerly on a side stream (lazy kernel attributes, NCCL communicators), then capture the launch sequence.
@@ -230,6 +288,26 @@ class NGPTrainer:
         self._g_fb = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._g_fb):
             self._forward_backward()
+        if self.overlap_optimizer:  # the same launches as two graphs, so the optimizer can run beside the first
+            self._g_a = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._g_a):
+                self._march()
+            self._g_b = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._g_b):
+                self._samples()
+            self._g_steady = None
+            if self.world == 1:  # one graph for the steady state: {optimizer(n-1) | march(n)} -> samples(n); one launch per step
+                if self._side is None:
+                    self._side = torch.cuda.Stream()
+                self._g_steady = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._g_steady):
+                    cur = torch.cuda.current_stream()
+                    self._side.wait_stream(cur)
+                    self._march()
+                    with torch.cuda.stream(self._side):
+                        self._optimizer_step()
+                    cur.wait_stream(self._side)
+                    self._samples()
         self._g_opt = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._g_opt):
             self._optimizer_step()
@@ -245,22 +323,25 @@ class NGPTrainer:
             self.gt.copy_(gt, non_blocking=True)
         if self.update_interval > 0 and self.global_step % self.update_interval == 0:
             self.update_extra_state()
-        if self.use_graph:
-            if self._graph is None:
-                self._capture()
-            else:
-                self._g_fb.replay()
-                if self.world > 1:
-                    self._allreduce()
-                self._g_opt.replay()
+        if self.use_graph and self._graph is None:
+            self.flush()
+            self._capture()
+        elif self.overlap_optimizer:
+            self._step_overlapped()
+        elif self.use_graph:
+            self._g_fb.replay()
+            if self.world > 1:
+                self._allreduce()
+            self._g_opt.replay()
         else:
             self._step_eager()
         self.local_step += 1
         self.global_step += 1
 
     def loss(self):
-        """Loss of the last finished step (device -> host read)."""
-        return float(self.state[_ST_LAST_LOSS].item())
+        """Loss of the last finished step (device -> host read).  With a deferred optimizer step pending, the value is
+        still in the accumulator slot (k_step_end has not copied it yet): read it there instead of forcing the update."""
+        return float(self.state[_ST_LOSS if self._pending else _ST_LAST_LOSS].item())
 
     # ---- synthetic ray pool (device resident inputs for the kernel-side benchmark) ----------------------------
     def set_pool(self, rays_o, rays_d, gt):
@@ -280,6 +361,7 @@ class NGPTrainer:
     @torch.no_grad()
     def density(self, xyz):
         """sigma(x) * density_scale through the encoder + sigma net in inference mode; xyz [n,3] in [-bound, bound]."""
+        self.flush()
         n = xyz.shape[0]
         out = torch.empty(n, device=self.dev)
         chunk = 1 << 21
@@ -296,6 +378,7 @@ class NGPTrainer:
 
     @torch.no_grad()
     def update_extra_state(self, decay=0.95):
+        self.flush()
         H, dev = self.H, self.dev
         tmp = -torch.ones_like(self.density_grid)
         if self.iter_density < 16:  # full sweep
@@ -351,6 +434,7 @@ class NGPTrainer:
         The loop of the reference: march up to n_step samples for every ray still alive, shade them, composite in place,
         drop the finished rays -- here on buffers allocated once per call, with the alive list compacted on the device
         (raymarching.compact_alive) and one 4-byte read of the alive count per iteration to size the next launch."""
+        self.flush()
         lib, s, dev = abi.lib, abi.stream(), self.dev
         rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
         N = rays_o.shape[0]
