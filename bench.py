@@ -332,9 +332,10 @@ class NerfTrainWorkload:
         """per-launch CUDA events cannot be recorded inside a graph replay: the profile pass runs the same launches eagerly."""
         self._saved = getattr(self, "_saved", self.tr.use_graph)
         self.tr.use_graph = False if on else self._saved
-        if on:  # per-kernel durations are taken with the kernels one after the other
-            self.tr.flush()
-        self.tr.overlap_optimizer = False if on else self._overlap
+        if hasattr(self.tr, "flush"):
+            if on:  # per-kernel durations are taken with the kernels one after the other
+                self.tr.flush()
+            self.tr.overlap_optimizer = False if on else self._overlap
 
     def launches_per_step(self):
         """Kernels of this library in one step (graph replays do not pass through the host-side counter)."""
@@ -569,9 +570,10 @@ class SDFWorkload:
     def profile_mode(self, on):
         self._saved = getattr(self, "_saved", self.tr.use_graph)
         self.tr.use_graph = False if on else self._saved
-        if on:  # per-kernel durations are taken with the kernels one after the other
-            self.tr.flush()
-        self.tr.overlap_optimizer = False if on else self._overlap
+        if hasattr(self.tr, "flush"):
+            if on:  # per-kernel durations are taken with the kernels one after the other
+                self.tr.flush()
+            self.tr.overlap_optimizer = False if on else self._overlap
 
     def launches_per_step(self):
         import ngp_abi as abi

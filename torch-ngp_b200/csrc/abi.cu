@@ -30,7 +30,8 @@ static std::map<std::string, int> &options() {
         {"hashgrid_v3_minb_bwd", -1},  // v3 backward: same
         {"hashgrid_v3_mix_fwd", 0},    // v3 forward: warps of one block work on different level groups (1) or whole blocks do (0)
         {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
-        {"hashgrid_bwd_red4", 0},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours (faster on random points, slower on ray-ordered samples)
+        {"hashgrid_bwd_red4", 2},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours: 0 never, 1 always, 2 when the lanes of a warp do not share groups (random points)
+        {"ffmlp_ablate", 0},           // timing experiments only (results are wrong): 1 skip the weight-gradient MMAs, 2 skip the layer MMAs, 3 both
         {"adam_blocks_per_sm", 0},     // k_adam grid cap (0 = one block per 1024 parameters); NGPTrainer sets it when the optimizer shares the SMs with the marcher
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
@@ -40,7 +41,7 @@ static std::map<std::string, int> &options() {
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
         {"ffmlp_available", 1},
         {"ffmlp_bwd_variant", -1},     // -1 auto / 1: multi-pipeline backward (one MMA-issuer warp, up to 4 tiles in flight), 0: one tile per CTA
-        {"ffmlp_bwd_issuers", 2},      // 2: one issuer warp for the layer products + one for the weight gradients, 1: a single issuer warp
+        {"ffmlp_bwd_issuers", 3},      // 3: every pipeline issues its own layer products, warp 1 the weight gradients; 2: warp 0 / warp 1; 1: a single issuer warp
         {"ffmlp_bwd_split", 0},        // 0 auto / 1 / 2: threads sharing one accumulator row in the multi-pipeline backward epilogue
         {"ffmlp_fwd_pipes", 0},        // > 0: cap on the tile pipelines per CTA of the FFMLP forward (tuning)
         {"profile_events", 0},         // 1: bracket every kernel launch with CUDA events (ngp_profile_collect)        // read-only in spirit: 1 once the tcgen05 FFMLP kernels are linked in

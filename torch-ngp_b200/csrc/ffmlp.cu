@@ -537,6 +537,14 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     fence_after_sync();
     const uint32_t tmem = s_tmem;
     const uint32_t stride = gridDim.x * np;
+    const bool abl_dw = (dual >> 4) & 1, abl_mm = (dual >> 5) & 1;  // timing ablations (option ffmlp_ablate): wrong results
+    // self-issue: every pipeline issues its own layer products (one elected thread of its first warp, after a named
+    // barrier over the pipeline's threads) instead of handing them to warp 0.  The central issuer's control code
+    // (poll, bookkeeping, ~1.2k cycles per service, three pipelines served in turn) was the critical path of the
+    // kernel: with every MMA removed it still ran at 74 % of its full time (benchmarks/ffmlp_trace.py).  Weight
+    // gradients stay with warp 1: their TMEM accumulators are shared by the pipelines and one thread's MMA stream is ordered.
+    const bool selfi = (dual >> 1) & 1;
+    dual &= 1;
 #ifdef NGP_FFMLP_TRACE
     unsigned tr_n = 0;
     bool tr_hit = true;
@@ -584,13 +592,13 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                 const uint32_t acc = tmem + p * accw;
                 const bool leader = elect_one();
                 if (rr == 0) {
-                    if (ROLE != 2 && leader) issue_fwd(acc, sx, sw + m.soff[0], m.hid, m.in);
+                    if (ROLE != 2 && leader && !abl_mm) issue_fwd(acc, sx, sw + m.soff[0], m.hid, m.in);
                 } else if (rr < m.nl) {
-                    if (ROLE != 2 && leader) issue_fwd(acc, sh + (rr - 1) * abytes, sw + m.soff[rr], m.hid, m.hid);
+                    if (ROLE != 2 && leader && !abl_mm) issue_fwd(acc, sh + (rr - 1) * abytes, sw + m.soff[rr], m.hid, m.hid);
                 } else if (rr == m.nl) {  // dH_{nl-1} = dY W_last ; dW_last += dY^T H_{nl-1}
                     if (leader) {
-                        if (ROLE != 2) issue_bwd_dx(acc, sgo, sw + m.soff[m.nl], m.hid, m.out);
-                        if (ROLE != 1) issue_dw(tmem + dwc[m.nl], sgo, sh + (m.nl - 1) * abytes, m.out, m.hid, (started >> m.nl) & 1u);
+                        if (ROLE != 2 && !abl_mm) issue_bwd_dx(acc, sgo, sw + m.soff[m.nl], m.hid, m.out);
+                        if (ROLE != 1 && !abl_dw) issue_dw(tmem + dwc[m.nl], sgo, sh + (m.nl - 1) * abytes, m.out, m.hid, (started >> m.nl) & 1u);
                     }
                     started |= 1u << m.nl;
                 } else {
@@ -598,11 +606,11 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     uint8_t *g = sh + l * abytes;
                     if (leader) {
                         if (l > 0) {
-                            if (ROLE != 2) issue_bwd_dx(acc, g, sw + m.soff[l], m.hid, m.hid);
-                            if (ROLE != 1) issue_dw(tmem + dwc[l], g, sh + (l - 1) * abytes, m.hid, m.hid, (started >> l) & 1u);
+                            if (ROLE != 2 && !abl_mm) issue_bwd_dx(acc, g, sw + m.soff[l], m.hid, m.hid);
+                            if (ROLE != 1 && !abl_dw) issue_dw(tmem + dwc[l], g, sh + (l - 1) * abytes, m.hid, m.hid, (started >> l) & 1u);
                         } else {
-                            if (ROLE != 2 && calc_dx) issue_bwd_dx(acc, g, sw + m.soff[0], m.in, m.hid);
-                            if (ROLE != 1) issue_dw(tmem + dwc[0], g, sx, m.hid, m.in, started & 1u);
+                            if (ROLE != 2 && calc_dx && !abl_mm) issue_bwd_dx(acc, g, sw + m.soff[0], m.in, m.hid);
+                            if (ROLE != 1 && !abl_dw) issue_dw(tmem + dwc[0], g, sx, m.hid, m.in, started & 1u);
                         }
                     }
                     started |= 1u << l;
@@ -626,7 +634,8 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     };
 
     if (warp == 0) {
-        if (dual) issuer(std::integral_constant<int, 1>{});
+        if (selfi) { /* layer products are issued by the pipelines */ }
+        else if (dual) issuer(std::integral_constant<int, 1>{});
         else issuer(std::integral_constant<int, 0>{});
     } else if (warp == 1) {
         if (dual) issuer(std::integral_constant<int, 2>{});
@@ -640,6 +649,31 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
             uint8_t *sx = smem + m.wbytes + p * per_pipe, *sh = sx + hoff;
             const uint32_t trow = tmem + p * accw + ((q * 32u) << 16);
             uint32_t phase = 0, phase2 = 0;
+            // round rr of this pipeline's tile: operands are in shared memory (every writer has fenced), accumulator drained
+            auto self_issue = [&](uint32_t rr) {
+                asm volatile("bar.sync %0, %1;" ::"r"(1u + p), "r"(nth) : "memory");
+                if (wp != 0) return;
+                fence_after_sync();
+                // REDUX puts the pipeline index into a uniform register: everything derived from it (descriptors, TMEM
+                // address) stays on the uniform datapath the tcgen05 instructions read from
+                const uint32_t pu = __reduce_max_sync(0xffffffffu, p), ru = __reduce_max_sync(0xffffffffu, rr);
+                uint8_t *ux = smem + m.wbytes + pu * per_pipe, *ugo = ux + goff, *uh = ux + hoff;
+                const uint32_t acc = tmem + pu * accw;
+                if (elect_one()) {
+                    if (!abl_mm) {
+                        if (ru == 0) issue_fwd(acc, ux, sw + m.soff[0], m.hid, m.in);
+                        else if (ru < m.nl) issue_fwd(acc, uh + (ru - 1) * abytes, sw + m.soff[ru], m.hid, m.hid);
+                        else if (ru == m.nl) issue_bwd_dx(acc, ugo, sw + m.soff[m.nl], m.hid, m.out);
+                        else {
+                            const uint32_t l = 2 * m.nl - ru;
+                            if (l > 0) issue_bwd_dx(acc, uh + l * abytes, sw + m.soff[l], m.hid, m.hid);
+                            else if (calc_dx) issue_bwd_dx(acc, uh, sw + m.soff[0], m.in, m.hid);
+                        }
+                    }
+                    mma_commit(&s_done[pu]);
+                }
+                __syncwarp();
+            };
             for (uint32_t tile = blockIdx.x * np + p; tile < ntiles; tile += stride) {
                 load_rows_async(sx, x, tile * kTileRows, Beff, m.in, ptid, nth);
                 if (packed) load_rows_async(sx, grad, tile * kTileRows, Beff, m.out, ptid, nth, m.in >> 3);
@@ -649,7 +683,8 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                 cp_async_wait<0>();
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
+                if (selfi) self_issue(0u);
+                else if (lane == 0) mbar_arrive(&s_full[p]);  // one arrival per warp
                 if (wp == 0) NGP_TR(2 + p, 0x301u);
                 for (uint32_t l = 0; l < m.nl; ++l) {    // forward recompute: H_l = ReLU(W_l H_{l-1})
                     mbar_wait(&s_done[p], phase);
@@ -661,9 +696,10 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     fence_before_sync();
                     __syncwarp();
                     if (lane == 0) {
-                        mbar_arrive(&s_full[p]);
+                        if (!selfi) mbar_arrive(&s_full[p]);
                         if (dual && l + 1 == m.nl) mbar_arrive(&s_full2[p]);  // dW_last reads dY and H_{nl-1}
                     }
+                    if (selfi) self_issue(l + 1u);
                     if (wp == 0) NGP_TR(2 + p, 0x500u | l);
                 }
                 for (int l = (int)m.nl - 1; l >= 0; --l) {  // G_l = dH_l * (H_l > 0), in place
@@ -681,9 +717,10 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     fence_before_sync();
                     __syncwarp();
                     if (lane == 0) {
-                        mbar_arrive(&s_full[p]);
+                        if (!selfi) mbar_arrive(&s_full[p]);
                         if (dual) mbar_arrive(&s_full2[p]);
                     }
+                    if (selfi) self_issue(2u * m.nl - (uint32_t)l);
                     if (wp == 0) NGP_TR(2 + p, 0x700u | (uint32_t)l);
                 }
                 mbar_wait(&s_done[p], phase);
@@ -920,7 +957,8 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (np > ntiles) np = ntiles;
         if (variant != 0 && (np >= 2 || (variant == 1 && np >= 1))) {
             const size_t smem_mp = m.wbytes + np * per_pipe;
-            const int dual = get_option("ffmlp_bwd_issuers", 2) != 1;
+            const int nis = get_option("ffmlp_bwd_issuers", 3);  // 1 one central issuer, 2 two (layer products / weight gradients), 3 pipelines issue their own layer products
+            const int dual = (nis != 1 ? 1 : 0) | (nis >= 3 ? 2 : 0) | (get_option("ffmlp_ablate", 0) << 4);
             const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
             uint32_t grid_mp = div_round_up(ntiles, np);
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();

@@ -149,7 +149,7 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         const dim3 gr = mix ? dim3(div_round_up(B, 256u / ng), 1, 1) : dim3(div_round_up(B, 256u), ng, 1);
         const int minb = get_option("hashgrid_v3_minb_bwd", -1);
         const bool occ6 = minb < 0 ? false : minb >= 6;
-        const int red4 = get_option("hashgrid_bwd_red4", 0);
+        const int red4 = get_option("hashgrid_bwd_red4", 2);
         NGP_PROF("k_grid_bwd_v3", st);
 #define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, batch_limit())
         if (mix) { if (occ6) NGP_BWD_V3(6, true); else NGP_BWD_V3(4, true); }
