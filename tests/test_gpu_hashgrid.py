@@ -108,7 +108,7 @@ def test_torch_gradcheck_fp64_reference_config():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
 @pytest.mark.parametrize("layout", [0, 1])
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 def test_fast_path_equals_generic(oracle, dtype, layout, variant):
     """D=3,C=2 fast kernels (paired accesses, shared-memory coarse levels) vs the generic kernels."""
     abi = _abi()
@@ -147,6 +147,54 @@ def test_fast_path_equals_generic(oracle, dtype, layout, variant):
                 assert torch.allclose(ge[hashed].float(), ge_ref[hashed].float(), rtol=2e-2, atol=2e-2)
         abi.set_option("hashgrid_bwd_warp_agg", 1)
         abi.set_option("hashgrid_bwd_variant", -1)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+@pytest.mark.parametrize("gridtype", [0, 1])
+def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
+    """Every switch of the per-level-kind kernels (warp-mixed level groups, occupancy target, 16 B group reductions,
+    zero-gradient skip) and its general-index fallback (tiled grids: levels that wrap) against the generic kernels;
+    random and ray-ordered points, a block of exactly zero upstream gradients."""
+    abi = _abi()
+    offsets, pls = oracle.make_offsets(desired_resolution=2048)
+    ot = torch.from_numpy(offsets).to(DEV)
+    B = 20000
+    torch.manual_seed(3)
+    x = torch.rand(B, 3, device=DEV)
+    n_rays = 64
+    o = torch.rand(n_rays, 1, 3, device=DEV) * 0.5 + 0.25
+    d = torch.nn.functional.normalize(torch.randn(n_rays, 1, 3, device=DEV), dim=-1)
+    t = torch.arange(128, device=DEV).view(1, 128, 1) * (3.4641 / 2048)
+    x[: n_rays * 128] = (o + d * t).clamp(0, 1).reshape(-1, 3)  # coherent part: runs of equal cells
+    x[-3:] = torch.tensor([[-0.1, 0.2, 0.3], [0, 0, 0], [1, 1, 1]], device=DEV)
+    emb = ((torch.rand(int(offsets[-1]), 2, device=DEV) - 0.5) * 2).to(dtype)
+    g = torch.randn(B, 32, device=DEV).to(dtype)
+    g[100:400] = 0  # zero-gradient lanes are skipped
+    keys = ("hashgrid_fwd_variant", "hashgrid_bwd_variant", "hashgrid_v3_mix_fwd", "hashgrid_v3_mix_bwd", "hashgrid_v3_minb_fwd",
+            "hashgrid_v3_minb_bwd", "hashgrid_bwd_red4")
+    defaults = dict(zip(keys, (-1, -1, 0, 1, -1, -1, 2)))
+
+    def setopts(**kw):
+        for k, v in {**defaults, **kw}.items():
+            abi.set_option(k, v)
+    try:
+        setopts(hashgrid_fwd_variant=0, hashgrid_bwd_variant=0)
+        ref, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
+        ge_ref, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)
+        for kw in (dict(), dict(hashgrid_v3_mix_fwd=1, hashgrid_v3_mix_bwd=0), dict(hashgrid_v3_minb_fwd=4, hashgrid_v3_minb_bwd=6),
+                   dict(hashgrid_v3_minb_fwd=6, hashgrid_bwd_red4=0), dict(hashgrid_bwd_red4=1)):
+            setopts(hashgrid_fwd_variant=3, hashgrid_bwd_variant=3, **kw)
+            out, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
+            ge, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)
+            if dtype == torch.float32:
+                assert torch.equal(out, ref), kw
+                assert torch.allclose(ge, ge_ref, rtol=1e-4, atol=1e-4), kw
+            else:
+                assert torch.allclose(out.float(), ref.float(), rtol=2e-3, atol=2e-3), kw
+                hashed = slice(int(offsets[6]), None)  # coarse levels: fp16 atomic order noise of the generic path
+                assert torch.allclose(ge[hashed].float(), ge_ref[hashed].float(), rtol=2e-2, atol=2e-2), kw
+    finally:
+        setopts()
 
 
 def test_warp_aggregated_backward_coherent_points(oracle):
