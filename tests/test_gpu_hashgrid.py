@@ -158,7 +158,7 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
     abi = _abi()
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
     ot = torch.from_numpy(offsets).to(DEV)
-    B = 20000
+    B = 40000  # > 32768: the shared-memory coarse levels of hashgrid_bwd_smem_coarse are exercised
     torch.manual_seed(3)
     x = torch.rand(B, 3, device=DEV)
     n_rays = 64
@@ -171,8 +171,8 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
     g = torch.randn(B, 32, device=DEV).to(dtype)
     g[100:400] = 0  # zero-gradient lanes are skipped
     keys = ("hashgrid_fwd_variant", "hashgrid_bwd_variant", "hashgrid_v3_mix_fwd", "hashgrid_v3_mix_bwd", "hashgrid_v3_minb_fwd",
-            "hashgrid_v3_minb_bwd", "hashgrid_bwd_red4")
-    defaults = dict(zip(keys, (-1, -1, 0, 1, -1, -1, 2)))
+            "hashgrid_v3_minb_bwd", "hashgrid_bwd_red4", "hashgrid_bwd_smem_coarse")
+    defaults = dict(zip(keys, (-1, -1, 0, 1, -1, -1, 2, 0)))
 
     def setopts(**kw):
         for k, v in {**defaults, **kw}.items():
@@ -182,7 +182,7 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
         ref, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
         ge_ref, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)
         for kw in (dict(), dict(hashgrid_v3_mix_fwd=1, hashgrid_v3_mix_bwd=0), dict(hashgrid_v3_minb_fwd=4, hashgrid_v3_minb_bwd=6),
-                   dict(hashgrid_v3_minb_fwd=6, hashgrid_bwd_red4=0), dict(hashgrid_bwd_red4=1)):
+                   dict(hashgrid_v3_minb_fwd=6, hashgrid_bwd_red4=0), dict(hashgrid_bwd_red4=1), dict(hashgrid_bwd_smem_coarse=1)):
             setopts(hashgrid_fwd_variant=3, hashgrid_bwd_variant=3, **kw)
             out, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
             ge, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)

@@ -150,8 +150,32 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         const int minb = get_option("hashgrid_v3_minb_bwd", -1);
         const bool occ6 = minb < 0 ? false : minb >= 6;
         const int red4 = get_option("hashgrid_bwd_red4", 2);
+        // Unordered points (hashgrid_bwd_smem_coarse = 1; the SDF step, configs[0]): every point lands in one of a few
+        // thousand coarse cells and the L2 atomic unit serialises same-address reductions.  The levels that fit are
+        // accumulated in shared memory instead (fp32, one flush per block).  Ray-ordered samples keep them in the warp
+        // reduction (runs of equal cells collapse before they reach L2).
+        uint32_t skip = 0;
+        if (get_option("hashgrid_bwd_smem_coarse", 0)) {
+            size_t smem = 0;
+            const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(float), &smem);
+            if (ns > 0) {
+                static bool attr_done = false;
+                if (!attr_done) {
+                    NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
+                    attr_done = true;
+                }
+                const uint32_t per_sm = smem <= 100 * 1024 ? 2 : 1;
+                uint32_t nb = (uint32_t)sm_count() * per_sm / ns;
+                nb = nb < 1 ? 1 : nb;
+                const uint32_t need = div_round_up(B, 1024u);
+                nb = nb > need ? need : nb;
+                { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
+                NGP_CHECK_LAUNCH();
+                skip = ns;
+            }
+        }
         NGP_PROF("k_grid_bwd_v3", st);
-#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, batch_limit())
+#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, batch_limit())
         if (mix) { if (occ6) NGP_BWD_V3(6, true); else NGP_BWD_V3(4, true); }
         else { if (occ6) NGP_BWD_V3(6, false); else NGP_BWD_V3(4, false); }
 #undef NGP_BWD_V3

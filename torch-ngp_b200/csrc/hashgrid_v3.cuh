@@ -276,7 +276,7 @@ template <typename T, int MINB, bool MIX>
 __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                      const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
-                                                     int layout, int warp_agg, int red4, const int *__restrict__ limit) {
+                                                     int layout, int warp_agg, int red4, uint32_t skip, const int *__restrict__ limit) {
     B = eff_batch(B, limit);
     uint32_t b, l0;
     map_thread<MIX>(L, b, l0);
@@ -301,6 +301,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
+        if (l0 + k < skip) continue;  // coarse levels accumulated in shared memory by k_grid_bwd_d3c2_smem
         const lv3_t lv = my_lv[k];
         T *tab = grad_grid + (size_t)lv.offset * 2;
         // A zero upstream gradient adds nothing: drop the lane for this level.  In NeRF training every sample behind

@@ -68,9 +68,14 @@ class SDFTrainer:
                              self.state[_ST_LOSS:].data_ptr(), s))
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, None, B, 32, 16, self.hid, self.nl, 0, 6, 1,
                                    None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
-        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
-                                         self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
-                                         None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+        # unordered surface samples: a few thousand coarse cells take every point -> those levels go through shared memory
+        abi.set_option("hashgrid_bwd_smem_coarse", 1)
+        try:
+            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
+                                             self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
+                                             None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+        finally:
+            abi.set_option("hashgrid_bwd_smem_coarse", 0)
 
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
