@@ -442,7 +442,7 @@ class RenderWorkload:
         import torch
         import nerf
         from nerf import synthetic
-        from nerf.parallel import row_band
+        from nerf.parallel import row_stripes
         self.torch, self.dev = torch, dev
         torch.manual_seed(7)
         self.tr = tr = nerf.NGPTrainer(bound=1.0, num_rays=4096, device=dev, seed=0, use_graph=True)
@@ -451,11 +451,11 @@ class RenderWorkload:
         for _ in range(self.args.pretrain):
             tr.next_pool_batch()
             tr.train_step()
-        self.band = row_band(self.Hh, rank, world)
-        self.frames = [synthetic.frame_rays(self.W, self.Hh, dev, pose_index=i * 7, rows=self.band) for i in range(4)]
+        self.rows = row_stripes(self.Hh, rank, world, stripe=8)  # interleaved 8-row stripes: every rank gets its share of the object
+        self.frames = [synthetic.frame_rays(self.W, self.Hh, dev, pose_index=i * 7, rows=self.rows.numpy()) for i in range(4)]
         self.frames_host = [(o.cpu().pin_memory(), d.cpu().pin_memory()) for o, d in self.frames]
         self.i = 0
-        self.units_per_step = (self.band[1] - self.band[0]) * self.W
+        self.units_per_step = int(self.rows.numel()) * self.W
         self.h2d_bytes = self.units_per_step * 6 * 4
         self.d2h_bytes = self.units_per_step * 4 * 4
         self.T = tr.T
@@ -464,16 +464,20 @@ class RenderWorkload:
 
     def config(self, world):
         c = {"workload": f"inference render {self.W}x{self.Hh} frames, march_rays/composite_rays from a 128^3 bitfield + network_ff shading (configs[3])",
-             "parallelism": f"{world} row bands, no collective", "l2": "flushed between steps (256 MiB memset outside the per-step events)",
+             "parallelism": f"rows dealt to {world} rank(s) in interleaved 8-row stripes, no collective", "l2": "flushed between steps (256 MiB memset outside the per-step events)",
              "pretrain_steps": self.args.pretrain}
         if hasattr(self, "tr"):
-            c.update({"rows_per_gpu": self.band[1] - self.band[0], "loop_iterations": getattr(self.tr, "last_render_iters", None)})
+            c.update({"rows_per_gpu": int(self.rows.numel()), "loop_iterations": getattr(self.tr, "last_render_iters", None)})
         return c
 
     def step_device(self):
         o, d = self.frames[self.i % 4]
         self.i += 1
-        self.tr.render(o, d)
+        self.tr.render(o, d, use_graph=getattr(self, "_graph_ok", True))
+
+    def profile_mode(self, on):
+        """per-launch CUDA events cannot be recorded inside a graph capture / replay: the profile pass runs the loop eagerly"""
+        self._graph_ok = not on
 
     def step_e2e(self):
         o, d = self.frames_host[self.i % 4]

@@ -71,6 +71,16 @@ def test_data_parallel_step_equals_global_batch_step(tmp_path):
     assert got["bands"] == [(0, 540), (540, 1080)]
 
 
+def test_row_stripes_cover_the_frame():
+    import torch
+    from nerf.parallel import row_stripes
+    for h, w, st in [(1080, 8, 8), (1080, 7, 16), (5, 8, 8), (720, 1, 8), (1081, 4, 3)]:
+        parts = [row_stripes(h, r, w, st) for r in range(w)]
+        allr = torch.cat(parts)
+        assert allr.numel() == h and torch.equal(torch.sort(allr).values, torch.arange(h))
+        assert max(p.numel() for p in parts) - min(p.numel() for p in parts) <= st
+
+
 def test_row_bands_cover_the_frame():
     from nerf.parallel import row_band, rays_per_rank
     for h, w in ((1080, 8), (1080, 7), (5, 8), (800, 1)):

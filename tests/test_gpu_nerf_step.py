@@ -283,3 +283,22 @@ def test_inference_render_matches_training_quadrature_and_band_sharding():
         r0, r1 = row_band(H, r, 2)
         parts.append(tr.render(ro[r0 * W:r1 * W], rd[r0 * W:r1 * W])[0])
     assert torch.allclose(torch.cat(parts), img, atol=1e-5)
+    # interleaved stripes == whole frame
+    from nerf.parallel import row_stripes
+    out = torch.empty_like(img)
+    for r in range(3):
+        rows = row_stripes(H, r, 3, stripe=4).cuda()
+        idx = (rows[:, None] * W + torch.arange(W, device="cuda")[None, :]).reshape(-1)
+        out[idx] = tr.render(ro[idx], rd[idx])[0]
+    assert torch.allclose(out, img, atol=2e-3)
+    # The loop schedule (how often the alive count is read back, how many samples per ray an iteration takes) changes
+    # where a ray's march is cut and resumed from the compositor's running t, i.e. sample positions in their last bits
+    # (the reference's own result depends on its n_alive-driven n_step in the same way): every schedule must agree with
+    # the reference's to the tolerance of the fp16 network, not bit for bit.
+    img1, depth1 = tr.render(ro, rd, sync_every=1, use_graph=False, n_step_range=(1, 8))   # the reference's schedule
+    ref_iters = tr.last_render_iters
+    for kw in (dict(sync_every=8), dict(sync_every=2, n_step_range=(3, 17)), dict(use_graph=False), dict(sync_every=4, n_step_range=(1, 8))):
+        a, b = tr.render(ro, rd, **kw)
+        assert (a - img1).abs().max() < 2e-3 and (b - depth1).abs().max() < 2e-3, (kw, float((a - img1).abs().max()), float((b - depth1).abs().max()))
+    tr.render(ro, rd)
+    assert tr.last_render_iters < ref_iters

@@ -4,7 +4,9 @@ Training (BASELINE.json configs[2]): data-parallel over rays.  Every rank marche
 full replica of the parameters; the only exchange is the gradient all-reduce -- one call for the fp16 hash-table
 gradient (T*C halves) and one for the fp32 MLP gradients -- after which every rank runs the same fused Adam with
 grad_div = world_size (sum of per-rank means / world = mean over the global batch).
-Inference (configs[3]): image rows are split into contiguous bands, one per rank, no collective.
+Inference (configs[3]): image rows are split over the ranks, no collective: contiguous bands (row_band) or interleaved
+stripes (row_stripes) -- stripes balance the load, since the rows that cross the object cost ~10x the rows of empty sky
+(measured on 8 B200: bands 3.6x one GPU, stripes see BASELINE.md).
 """
 import torch
 
@@ -23,6 +25,13 @@ def row_band(height, rank, world):
     base, extra = divmod(height, world)
     r0 = rank * base + min(rank, extra)
     return r0, r0 + base + (1 if rank < extra else 0)
+
+
+def row_stripes(height, rank, world, stripe=8):
+    """Row indices (ascending int64 tensor) that rank renders: stripes of `stripe` rows dealt round-robin to the ranks.
+    Disjoint over the ranks and covering [0, height)."""
+    rows = torch.arange(height, dtype=torch.int64)
+    return rows[(rows // stripe) % world == rank]
 
 
 def rays_per_rank(global_rays, world):

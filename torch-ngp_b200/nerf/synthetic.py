@@ -50,7 +50,8 @@ def random_rays(n_views, rays_per_view, device, seed=0, radius=1.6, fovy_deg=50.
 
 
 def frame_rays(W, H, device, pose_index=0, n_poses=120, radius=1.6, fovy_deg=50.0, rows=None):
-    """All rays of one orbit frame, row-major; rows=(r0, r1) selects a band (tile sharding across ranks)."""
+    """All rays of one orbit frame, row-major; rows=(r0, r1) selects a band, rows=<1-D index tensor / array> the listed
+    rows (tile sharding across ranks: nerf/parallel.py row_band / row_stripes)."""
     ang = 2 * math.pi * pose_index / n_poses
     eye = np.array([radius * math.cos(ang) * 0.9, radius * 0.3, radius * math.sin(ang) * 0.9])
     fwd = -eye / np.linalg.norm(eye)
@@ -58,8 +59,13 @@ def frame_rays(W, H, device, pose_index=0, n_poses=120, radius=1.6, fovy_deg=50.
     right /= np.linalg.norm(right)
     upv = np.cross(right, fwd)
     focal = H / (2 * math.tan(math.radians(fovy_deg) / 2))
-    r0, r1 = (0, H) if rows is None else rows
-    jj, ii = np.meshgrid(np.arange(r0, r1), np.arange(W), indexing="ij")
+    if rows is None:
+        row_idx = np.arange(0, H)
+    elif isinstance(rows, tuple):
+        row_idx = np.arange(rows[0], rows[1])
+    else:
+        row_idx = np.asarray(rows, dtype=np.int64)
+    jj, ii = np.meshgrid(row_idx, np.arange(W), indexing="ij")
     xs = (ii.ravel() + 0.5 - W / 2) / focal
     ys = (jj.ravel() + 0.5 - H / 2) / focal
     d = xs[:, None] * right + (-ys)[:, None] * upv + fwd

@@ -428,60 +428,139 @@ class NGPTrainer:
         return float(self.mean_sum.item()) / self.density_grid.numel()
 
     # ---- inference rendering (nerf/renderer.py:346-431, the `not self.training` branch of run_cuda) ----------------
+    def _render_state(self, N, rows):
+        """Buffers of the render loop for N rays and at most `rows` samples per iteration, allocated once and kept (a frame
+        sequence renders the same N again and again), plus the CUDA graphs of its iteration groups."""
+        cache = self.__dict__.setdefault("_rcache", {})
+        rs = cache.get((N, rows))
+        if rs is not None:
+            return rs
+        if len(cache) >= 4:
+            cache.pop(next(iter(cache)))
+        dev, lib = self.dev, abi.lib
+        f32, f16 = dict(dtype=torch.float32, device=dev), dict(dtype=torch.half, device=dev)
+        cap = rows + 128  # n_alive * n_step <= rows by construction
+        rs = dict(
+            rays_o=torch.empty(N, 3, **f32), rays_d=torch.empty(N, 3, **f32), nears=torch.empty(N, **f32), fars=torch.empty(N, **f32),
+            ws=torch.empty(N, **f32), depth=torch.empty(N, **f32), image=torch.empty(N, 3, **f32), rays_t=torch.empty(N, **f32),
+            alive=[torch.empty(N, dtype=torch.int32, device=dev), torch.empty(N, dtype=torch.int32, device=dev)],
+            iota=torch.arange(N, dtype=torch.int32, device=dev), n_dev=torch.zeros(1, dtype=torch.int32, device=dev),
+            rows_dev=torch.zeros(1, dtype=torch.int32, device=dev),
+            xyzs=torch.zeros(cap, 3, **f32), dirs=torch.zeros(cap, 3, **f32), deltas=torch.zeros(cap, 2, **f32), x01=torch.empty(cap, 3, **f32),
+            enc=torch.empty(cap, 32, **f16), h=torch.empty(cap, 16, **f16), cin=torch.empty(cap, 32, **f16), c=torch.empty(cap, 16, **f16),
+            sigmas=torch.empty(cap, **f32), rgbs=torch.empty(cap, 3, **f32),
+            cws=torch.empty(max(1 << 16, lib.ngp_compact_alive_workspace_bytes(N)), dtype=torch.uint8, device=dev),
+            noises=torch.zeros(N, **f32), zeros_n=torch.zeros(N, **f32), graphs={}, table=None)
+        cache[(N, rows)] = rs
+        return rs
+
+    def _render_iteration(self, rs, n_alive, n_step, cur, noises, T_thresh):
+        """One loop iteration (renderer.py:380-417) for at most n_alive rays (the kernels clamp to the device count)."""
+        lib, s = abi.lib, abi.stream()
+        M = n_alive * n_step
+        n_dev = rs["n_dev"]
+        rs["deltas"][:M].zero_()  # a zero delta ends a ray's samples in composite_rays (the reference allocates zeroed buffers every iteration)
+        torch.mul(n_dev, n_step, out=rs["rows_dev"])  # sample rows really in use: bounds the shading kernels on the device
+        _ck(lib.ngp_march_rays(n_alive, n_dev.data_ptr(), n_step, rs["alive"][cur].data_ptr(), rs["rays_t"].data_ptr(), rs["rays_o"].data_ptr(),
+                               rs["rays_d"].data_ptr(), self.bound, self.dt_gamma, self.max_steps, self.cascade, self.H,
+                               self.density_bitfield.data_ptr(), rs["nears"].data_ptr(), rs["fars"].data_ptr(), rs["xyzs"].data_ptr(),
+                               rs["dirs"].data_ptr(), rs["deltas"].data_ptr(), noises.data_ptr(), s))
+        lib.ngp_set_batch_limit(rs["rows_dev"].data_ptr())
+        try:  # shade the samples (inference kernels: no activations kept)
+            _ck(lib.ngp_nerf_x01(rs["xyzs"].data_ptr(), self.bound, rs["x01"].data_ptr(), M, s))
+            _ck(lib.ngp_grid_encode_forward(rs["x01"].data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                            rs["enc"].data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                            abi.LAYOUT_BLC, s))
+            _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s))
+            _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s))
+            _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s))
+            _ck(lib.ngp_nerf_rgb_forward(rs["c"].data_ptr(), rs["rgbs"].data_ptr(), M, s))
+        finally:
+            lib.ngp_set_batch_limit(None)
+        _ck(lib.ngp_composite_rays(n_alive, n_dev.data_ptr(), n_step, T_thresh, rs["alive"][cur].data_ptr(), rs["rays_t"].data_ptr(),
+                                   rs["sigmas"].data_ptr(), rs["rgbs"].data_ptr(), rs["deltas"].data_ptr(), rs["ws"].data_ptr(), rs["depth"].data_ptr(),
+                                   rs["image"].data_ptr(), s))
+        _ck(lib.ngp_compact_alive(rs["alive"][cur].data_ptr(), n_alive, n_dev.data_ptr(), rs["alive"][cur ^ 1].data_ptr(), n_dev.data_ptr(),
+                                  rs["cws"].data_ptr(), rs["cws"].numel(), s))
+
     @torch.no_grad()
-    def render(self, rays_o, rays_d, perturb=False, T_thresh=1e-4, max_iters=None):
-        """Image [N,3], depth [N] for the given rays (one row band of a frame per rank when sharded, nerf/parallel.py).
+    def render(self, rays_o, rays_d, perturb=False, T_thresh=1e-4, max_iters=None, sync_every=4, use_graph=True, n_step_range=(2, 64)):
+        """Image [N,3], depth [N] for the given rays (the rows of a frame one rank owns when sharded, nerf/parallel.py).
         The loop of the reference: march up to n_step samples for every ray still alive, shade them, composite in place,
-        drop the finished rays -- here on buffers allocated once per call, with the alive list compacted on the device
-        (raymarching.compact_alive) and one 4-byte read of the alive count per iteration to size the next launch."""
+        drop the finished rays -- on buffers kept per ray count, with the alive list compacted on the device
+        (raymarching.compact_alive).  The alive count is read back only every `sync_every` iterations: in between, the
+        launches are sized by an upper bound of the count (it never grows) and the kernels clamp to the count on the
+        device (n_alive_dev / ngp_set_batch_limit), so the host does not wait on the GPU 200 times per frame.  With
+        use_graph the bound is rounded up a 2^(1/8) ladder and each group of `sync_every` iterations with the same
+        (bound, n_step) is one CUDA graph, captured on first use and replayed for every later frame of the same size.
+        A different cut of a ray's samples into iterations moves the points where the march resumes from the compositor's
+        running t, i.e. sample positions in their last bits -- as the reference's own n_alive-driven n_step does; images of
+        different schedules agree to the tolerance of the fp16 network (tests: 2e-3), each op stays bit-exact.
+        n_step_range: the reference marches n_step = clamp(N // n_alive, 1, 8) samples per ray and iteration, which makes
+        >= 128 iterations for a ray that crosses the whole box and ~200 per frame, each a dozen launches whose fixed cost
+        dominates once few rays are left.  (lo, hi) = (2, 64) with room for lo * N samples cuts that to a few dozen
+        iterations; the only cost is the < n_step samples a ray computes past its own end.
+        sync_every=1, use_graph=False, n_step_range=(1, 8) is the reference's schedule."""
         self.flush()
         lib, s, dev = abi.lib, abi.stream(), self.dev
         rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
         N = rays_o.shape[0]
-        f32 = dict(dtype=torch.float32, device=dev)
-        nears, fars = torch.empty(N, **f32), torch.empty(N, **f32)
-        _ck(lib.ngp_near_far_from_aabb(rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(), N, self.min_near, nears.data_ptr(), fars.data_ptr(), s))
-        ws, depth, image = torch.zeros(N, **f32), torch.zeros(N, **f32), torch.zeros(N, 3, **f32)
-        alive = [torch.arange(N, dtype=torch.int32, device=dev), torch.empty(N, dtype=torch.int32, device=dev)]
-        n_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-        rays_t = nears.clone()
-        cap = N * 8 + 128  # n_alive * n_step <= N by construction (n_step = min(N // n_alive, 8)) except n_step = 1: <= N
-        cap = max(cap, N + 128)
-        xyzs, dirs, deltas = torch.zeros(cap, 3, **f32), torch.zeros(cap, 3, **f32), torch.zeros(cap, 2, **f32)
-        x01 = torch.empty(cap, 3, **f32)
-        f16 = dict(dtype=torch.half, device=dev)
-        enc, h, cin, c = torch.empty(cap, 32, **f16), torch.empty(cap, 16, **f16), torch.empty(cap, 32, **f16), torch.empty(cap, 16, **f16)
-        sigmas, rgbs = torch.empty(cap, **f32), torch.empty(cap, 3, **f32)
-        cws = torch.empty(max(1 << 16, lib.ngp_compact_alive_workspace_bytes(N)), dtype=torch.uint8, device=dev)
-        noises = torch.rand(N, **f32) if perturb else torch.zeros(N, **f32)
-        zeros_n = torch.zeros(N, **f32)
-        n_alive, step, cur, it = N, 0, 0, 0
+        lo, hi = max(1, int(n_step_range[0])), max(1, int(n_step_range[1]))
+        rows = lo * N
+        rs = self._render_state(N, rows)
+        if rs["table"] is not self.table16 or rs.get("M_train") != self.M:  # graphs hold the parameter pointers of their capture
+            rs["graphs"].clear()
+            rs["table"], rs["M_train"] = self.table16, self.M
+        rs["rays_o"].copy_(rays_o, non_blocking=True)
+        rs["rays_d"].copy_(rays_d, non_blocking=True)
+        nears, fars = rs["nears"], rs["fars"]
+        _ck(lib.ngp_near_far_from_aabb(rs["rays_o"].data_ptr(), rs["rays_d"].data_ptr(), self.aabb.data_ptr(), N, self.min_near, nears.data_ptr(),
+                                       fars.data_ptr(), s))
+        rs["ws"].zero_(); rs["depth"].zero_(); rs["image"].zero_()
+        rs["alive"][0].copy_(rs["iota"])
+        rs["n_dev"].fill_(N)
+        rs["rays_t"].copy_(nears)
+        if perturb:
+            rs["noises"].uniform_()
+        else:
+            rs["noises"].zero_()
+        sync_every = max(1, int(sync_every))
+        group = sync_every if sync_every % 2 == 0 else 1  # a graph must end on the alive buffer it started on
+        n_alive, step, cur, it = N, 0, 0, 0  # n_alive: the host's view of the count (possibly stale, never too small)
         while step < self.max_steps and n_alive > 0:
-            n_step = max(min(N // n_alive, 8), 1)
-            M = n_alive * n_step
-            deltas[:M].zero_()  # a zero delta ends a ray's samples in composite_rays (the reference allocates zeroed buffers every iteration)
-            _ck(lib.ngp_march_rays(n_alive, None, n_step, alive[cur].data_ptr(), rays_t.data_ptr(), rays_o.data_ptr(), rays_d.data_ptr(), self.bound,
-                                   self.dt_gamma, self.max_steps, self.cascade, self.H, self.density_bitfield.data_ptr(), nears.data_ptr(),
-                                   fars.data_ptr(), xyzs.data_ptr(), dirs.data_ptr(), deltas.data_ptr(), (noises if step == 0 else zeros_n).data_ptr(), s))
-            # shade M samples (inference kernels: no activations kept)
-            _ck(lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
-            _ck(lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                            enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                            abi.LAYOUT_BLC, s))
-            _ck(lib.ngp_ffmlp_inference(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, h.data_ptr(), s))
-            _ck(lib.ngp_nerf_mid_forward(h.data_ptr(), dirs.data_ptr(), self.density_scale, sigmas.data_ptr(), cin.data_ptr(), M, s))
-            _ck(lib.ngp_ffmlp_inference(cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, c.data_ptr(), s))
-            _ck(lib.ngp_nerf_rgb_forward(c.data_ptr(), rgbs.data_ptr(), M, s))
-            _ck(lib.ngp_composite_rays(n_alive, None, n_step, T_thresh, alive[cur].data_ptr(), rays_t.data_ptr(), sigmas.data_ptr(), rgbs.data_ptr(),
-                                       deltas.data_ptr(), ws.data_ptr(), depth.data_ptr(), image.data_ptr(), s))
-            _ck(lib.ngp_compact_alive(alive[cur].data_ptr(), n_alive, None, alive[cur ^ 1].data_ptr(), n_dev.data_ptr(), cws.data_ptr(), cws.numel(), s))
-            cur ^= 1
-            n_alive = int(n_dev.item())
-            step += n_step
-            it += 1
+            n_step = max(min(rows // n_alive, hi), lo)
+            left = (self.max_steps - step + n_step - 1) // n_step  # iterations the reference's loop bound still allows
+            if max_iters is not None:
+                left = min(left, max_iters - it)
+            if use_graph and it > 0 and group > 1 and left >= group:
+                key = (n_alive, n_step, cur, float(T_thresh))
+                g = rs["graphs"].get(key)
+                if g is None:
+                    side = torch.cuda.Stream()
+                    side.wait_stream(torch.cuda.current_stream())
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=side):
+                        for k in range(group):
+                            self._render_iteration(rs, n_alive, n_step, cur ^ (k & 1), rs["zeros_n"], T_thresh)
+                    torch.cuda.current_stream().wait_stream(side)
+                    rs["graphs"][key] = g
+                g.replay()
+                done = group
+            else:
+                self._render_iteration(rs, n_alive, n_step, cur, rs["noises"] if step == 0 else rs["zeros_n"], T_thresh)
+                cur ^= 1
+                done = 1
+            step += n_step * done
+            it += done
+            if it % sync_every == 0 or done > 1:
+                actual = int(rs["n_dev"].item())
+                n_alive = actual
+                if use_graph and actual > 0:  # round up a 2^(1/8) ladder so that (bound, n_step) repeats from frame to frame
+                    j = int(math.floor(8 * math.log2(N / actual) + 1e-9)) if actual < N else 0  # largest j with N * 2^(-j/8) >= actual
+                    n_alive = max(actual, min(N, int(math.ceil(N * 2 ** (-j / 8)))))
             if max_iters is not None and it >= max_iters:
                 break
-        image = image + (1 - ws).unsqueeze(-1) * self.bg_color
-        depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+        image = rs["image"] + (1 - rs["ws"]).unsqueeze(-1) * self.bg_color
+        depth = torch.clamp(rs["depth"] - nears, min=0) / (fars - nears)
         self.last_render_iters = it
         return image, depth
