@@ -68,6 +68,13 @@ NGP_API long long ngp_launch_count(void);
 NGP_API int ngp_set_batch_limit(const int32_t *count_dev);
 NGP_API int ngp_profile_collect(char *buf, size_t buf_bytes);
 
+/* Input range of ngp_grid_encode_forward / _backward.  While bound > 0 (process-wide, like the batch limit), `inputs`
+ * are positions in [-bound, bound]^3 and the kernels apply the module's own mapping (x + bound) / (2 bound)
+ * (gridencoder/grid.py:807) as they load them -- one pass over the samples less for a caller that owns its buffers
+ * (NGPTrainer).  D = 3, C = 2 fast kernels only: any other configuration returns NGP_EUNSUPPORTED while it is set.
+ * bound <= 0 restores the default (inputs already in [0, 1]). */
+NGP_API int ngp_set_input_bound(float bound);
+
 /* ---------------------------------------------------------------------------------------------
  * gridencoder  (replaces gridencoder.h:12-15)
  * ------------------------------------------------------------------------------------------- */

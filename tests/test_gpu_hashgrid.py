@@ -197,6 +197,40 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
         setopts()
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+def test_input_bound_is_the_module_mapping(oracle, dtype):
+    """ngp_set_input_bound(b): the kernels map [-b, b] -> [0, 1] as they load the points, bit for bit the
+    (x + b) / (2 b) of GridEncoder.forward (grid.py:807); unsupported configurations refuse loudly."""
+    abi = _abi()
+    offsets, pls = oracle.make_offsets(desired_resolution=2048)
+    ot = torch.from_numpy(offsets).to(DEV)
+    B, bound = 50000, 2.0
+    torch.manual_seed(5)
+    x = (torch.rand(B, 3, device=DEV) * 2 - 1) * bound * 1.01  # a few points outside
+    x01 = (x + bound) / (2 * bound)
+    emb = ((torch.rand(int(offsets[-1]), 2, device=DEV) - 0.5) * 2).to(dtype)
+    g = torch.randn(B, 32, device=DEV).to(dtype)
+    ref, _ = _run_fwd(x01, emb, ot, pls, 16, layout=1)
+    for coarse in (0, 1):
+        abi.set_option("hashgrid_bwd_smem_coarse", coarse)
+        ge_ref, _ = _run_bwd(g, x01, emb, ot, pls, 16, layout=1)
+        abi.lib.ngp_set_input_bound(bound)
+        try:
+            out, _ = _run_fwd(x, emb, ot, pls, 16, layout=1)
+            ge, _ = _run_bwd(g, x, emb, ot, pls, 16, layout=1)
+            with pytest.raises(RuntimeError):  # generic kernels (no host offsets / D != 3) do not take the mapping
+                _run_fwd(x[:, :2].contiguous(), emb, ot, pls, 16, layout=1)
+        finally:
+            abi.lib.ngp_set_input_bound(0.0)
+            abi.set_option("hashgrid_bwd_smem_coarse", 0)
+        assert torch.equal(out, ref)
+        if dtype == torch.float32:
+            assert torch.allclose(ge, ge_ref, rtol=1e-4, atol=1e-4)
+        else:
+            hashed = slice(int(offsets[6]), None)
+            assert torch.allclose(ge[hashed].float(), ge_ref[hashed].float(), rtol=2e-2, atol=2e-2)
+
+
 def test_warp_aggregated_backward_coherent_points(oracle):
     """Samples marching along rays: many warps sit in one coarse cell -> the shuffle-reduced path."""
     offsets, pls = oracle.make_offsets(desired_resolution=2048)

@@ -90,6 +90,9 @@ prof_scope::~prof_scope() {
 static std::atomic<const int *> g_batch_limit{nullptr};
 const int *batch_limit() { return g_batch_limit.load(std::memory_order_acquire); }
 void set_batch_limit(const int *p) { g_batch_limit.store(p, std::memory_order_release); }
+static std::atomic<float> g_input_bound{0.0f};
+float input_bound() { return g_input_bound.load(std::memory_order_acquire); }
+void set_input_bound(float b) { g_input_bound.store(b, std::memory_order_release); }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -124,6 +127,11 @@ int ngp_set_option(const char *key, int value) {
 }
 
 long long ngp_launch_count(void) { return ngp::g_launches.load(); }
+
+int ngp_set_input_bound(float bound) {
+    ngp::set_input_bound(bound > 0.f ? bound : 0.f);
+    return NGP_OK;
+}
 
 int ngp_set_batch_limit(const int32_t *count_dev) {
     ngp::set_batch_limit(reinterpret_cast<const int *>(count_dev));

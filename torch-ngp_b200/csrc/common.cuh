@@ -14,6 +14,8 @@ int get_option(const char *key, int dflt);
 int sm_count();  // SMs of the current device (148 on B200), cached
 const int *batch_limit();  // device pointer set by ngp_set_batch_limit (process-wide), or nullptr
 void set_batch_limit(const int *p);
+float input_bound();  // ngp_set_input_bound (process-wide): > 0 -> the grid kernels map inputs from [-bound, bound] to [0, 1] themselves
+void set_input_bound(float b);
 
 // Effective batch of a per-sample kernel: min(B, *limit * mult) when a device-side limit is set.  The launch is
 // still sized for B; blocks past the limit exit at once.  `limit` was written by an earlier kernel on the stream.

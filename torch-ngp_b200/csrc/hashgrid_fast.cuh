@@ -103,14 +103,18 @@ template <> struct entry_io<__half> {
     }
 };
 
+// (x + bound) / (2 bound): gridencoder/grid.py:807, the arithmetic of k_nerf_x01 (IEEE division, no contraction)
+__device__ __forceinline__ float to_unit(float x, float bound) { return __fdiv_rn(__fadd_rn(x, bound), __fmul_rn(2.0f, bound)); }
+
 // position of one point inside one level (reference :146-156); returns false when out of [0,1]^3
 struct loc3_t {
     uint32_t p0, p1, p2;   // base cell
     float f0, f1, f2;      // (smooth-stepped) fractions
 };
 __device__ __forceinline__ bool locate3(const float *__restrict__ inputs, uint32_t b, float scale, bool align_corners,
-                                        uint32_t interp, loc3_t &o) {
-    const float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
+                                        uint32_t interp, loc3_t &o, float in_bound = 0.f) {
+    float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
+    if (in_bound > 0.f) { x0 = to_unit(x0, in_bound); x1 = to_unit(x1, in_bound); x2 = to_unit(x2, in_bound); }
     if (x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1) return false;
     const float off = align_corners ? 0.0f : 0.5f;
     float q0 = x0 * scale + off, q1 = x1 * scale + off, q2 = x2 * scale + off;
@@ -320,7 +324,8 @@ template <typename T>
 __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                              const int *__restrict__ offsets, T *__restrict__ grad_grid,
                                                              uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
-                                                             bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+                                                             bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit,
+                                                             float in_bound = 0.f) {
     B = eff_batch(B, limit);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *acc = reinterpret_cast<float *>(smem_raw);
@@ -332,7 +337,7 @@ __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict
     __syncthreads();
     for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
         loc3_t o;
-        if (!locate3(inputs, b, lv.scale, align_corners, interp, o)) continue;
+        if (!locate3(inputs, b, lv.scale, align_corners, interp, o, in_bound)) continue;
         const float2 gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2));
         rows3_t r;
         make_rows3(g, o, r);

@@ -102,13 +102,14 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
         const int minb = get_option("hashgrid_v3_minb_fwd", -1);
         const bool occ6 = minb < 0 ? sizeof(T) == 2 : minb >= 6;  // fp16 groups are 4 registers, fp32 groups 8: 40 registers spill the latter
         NGP_PROF("k_grid_fwd_v3", st);
-#define NGP_FWD_V3(MINB, MIX) k_grid_fwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit())
+#define NGP_FWD_V3(MINB, MIX) k_grid_fwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, input_bound(), batch_limit())
         if (mix) { if (occ6) NGP_FWD_V3(6, true); else NGP_FWD_V3(4, true); }
         else { if (occ6) NGP_FWD_V3(6, false); else NGP_FWD_V3(4, false); }
 #undef NGP_FWD_V3
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
+    if (input_bound() > 0.f) { set_error("grid_encode_forward: ngp_set_input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
     if (variant == 2 && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
         { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
@@ -169,19 +170,20 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
                 nb = nb < 1 ? 1 : nb;
                 const uint32_t need = div_round_up(B, 1024u);
                 nb = nb > need ? need : nb;
-                { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
+                { NGP_PROF("k_grid_bwd_d3c2_smem", st); k_grid_bwd_d3c2_smem<T><<<dim3(nb, ns, 1), 1024, smem, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, batch_limit(), input_bound()); }
                 NGP_CHECK_LAUNCH();
                 skip = ns;
             }
         }
         NGP_PROF("k_grid_bwd_v3", st);
-#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, batch_limit())
+#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit())
         if (mix) { if (occ6) NGP_BWD_V3(6, true); else NGP_BWD_V3(4, true); }
         else { if (occ6) NGP_BWD_V3(6, false); else NGP_BWD_V3(4, false); }
 #undef NGP_BWD_V3
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
+    if (input_bound() > 0.f) { set_error("grid_encode_backward: ngp_set_input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
     if (variant == 2 && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
         { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, batch_limit()); }
@@ -249,6 +251,10 @@ int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const i
     const bool ac = align_corners != 0;
     const int variant = get_option("hashgrid_fwd_variant", -1);
     const bool fast = D == 3 && C == 2 && !dy_dx && variant != 0 && fast_path_ok(offsets_host, L);
+    if (input_bound() > 0.f && !(fast && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
+        set_error("grid_encode_forward: ngp_set_input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
+        return NGP_EUNSUPPORTED;
+    }
     switch (dtype) {
         case NGP_DTYPE_F32:
             if (fast) return fwd_d3c2<float>(inputs, (const float *)embeddings, offsets, offsets_host, (float *)outputs, B, L, S, H, gridtype, ac, interp, layout, st);
@@ -278,6 +284,10 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
     const bool ac = align_corners != 0;
     const int variant = get_option("hashgrid_bwd_variant", -1);
     const bool fast = D == 3 && C == 2 && variant != 0 && fast_path_ok(offsets_host, L);
+    if (input_bound() > 0.f && !(fast && !dy_dx && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
+        set_error("grid_encode_backward: ngp_set_input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
+        return NGP_EUNSUPPORTED;
+    }
     int rc;
     switch (dtype) {
         case NGP_DTYPE_F32:

@@ -198,14 +198,15 @@ template <typename T, int MINB, bool MIX>
 __global__ void __launch_bounds__(256, MINB) k_grid_fwd_v3(const float *__restrict__ inputs, const T *__restrict__ grid,
                                                      const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
-                                                     int layout, const int *__restrict__ limit) {
+                                                     int layout, float in_bound, const int *__restrict__ limit) {
     B = eff_batch(B, limit);
     uint32_t b, l0;
     map_thread<MIX>(L, b, l0);
     __shared__ lv3_t s_lv[MIX ? 32 : 4];
     const lv3_t *my_lv = block_levels<MIX>(s_lv, offsets, L, l0, S, H, gridtype, align_corners);
     if (b >= B) return;
-    const float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
+    float x0 = inputs[3 * (size_t)b], x1 = inputs[3 * (size_t)b + 1], x2 = inputs[3 * (size_t)b + 2];
+    if (in_bound > 0.f) { x0 = to_unit(x0, in_bound); x1 = to_unit(x1, in_bound); x2 = to_unit(x2, in_bound); }
     const bool oob = (x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
     const float off = align_corners ? 0.0f : 0.5f;
     float2 res[4];
@@ -276,7 +277,7 @@ template <typename T, int MINB, bool MIX>
 __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                      const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
-                                                     int layout, int warp_agg, int red4, uint32_t skip, const int *__restrict__ limit) {
+                                                     int layout, int warp_agg, int red4, uint32_t skip, float in_bound, const int *__restrict__ limit) {
     B = eff_batch(B, limit);
     uint32_t b, l0;
     map_thread<MIX>(L, b, l0);
@@ -284,6 +285,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
     const lv3_t *my_lv = block_levels<MIX>(s_lv, offsets, L, l0, S, H, gridtype, align_corners);
     float x0 = 0.f, x1 = 0.f, x2 = 0.f;
     if (b < B) { x0 = inputs[3 * (size_t)b]; x1 = inputs[3 * (size_t)b + 1]; x2 = inputs[3 * (size_t)b + 2]; }
+    if (in_bound > 0.f) { x0 = to_unit(x0, in_bound); x1 = to_unit(x1, in_bound); x2 = to_unit(x2, in_bound); }
     const bool inside = (b < B) && !(x0 < 0 || x0 > 1 || x1 < 0 || x1 > 1 || x2 < 0 || x2 > 1);
     if (__ballot_sync(0xffffffffu, inside) == 0) return;
     const float off = align_corners ? 0.0f : 0.5f;

@@ -59,10 +59,14 @@ class SDFTrainer:
     def _forward_backward(self):
         s, lib, B = abi.stream(), abi.lib, self.B
         _ck(lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s))
-        _ck(lib.ngp_nerf_x01(self.points.data_ptr(), 1.0, self.x01.data_ptr(), B, s))  # encoder(x, bound=1): (x + 1) / 2
-        _ck(lib.ngp_grid_encode_forward(self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                        self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                        abi.LAYOUT_BLC, s))
+        # encoder(x, bound=1): (x + 1) / 2, applied by the grid kernels as they load the points (ngp_set_input_bound)
+        lib.ngp_set_input_bound(1.0)
+        try:
+            _ck(lib.ngp_grid_encode_forward(self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                            self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                            abi.LAYOUT_BLC, s))
+        finally:
+            lib.ngp_set_input_bound(0.0)
         _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s))
         _ck(lib.ngp_sdf_loss(self.h.data_ptr(), self.sdfs.data_ptr(), B, self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(),
                              self.state[_ST_LOSS:].data_ptr(), s))
@@ -70,11 +74,13 @@ class SDFTrainer:
                                    None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
         # unordered surface samples: a few thousand coarse cells take every point -> those levels go through shared memory
         abi.set_option("hashgrid_bwd_smem_coarse", 1)
+        lib.ngp_set_input_bound(1.0)
         try:
-            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
+            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
                                              self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
                                              None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
         finally:
+            lib.ngp_set_input_bound(0.0)
             abi.set_option("hashgrid_bwd_smem_coarse", 0)
 
     def _optimizer_step(self):

@@ -68,6 +68,8 @@ class NGPTrainer:
         self.offsets_host = np.ascontiguousarray(enc.offsets.numpy().astype(np.int32))
         self.T = int(enc.offsets[-1])
         self.enc_dim = self.L * self.C
+        # the per-level-kind kernels (L % 4 == 0, level slices on 8-entry boundaries) can map [-bound, bound] -> [0, 1] themselves
+        self.fuse_x01 = self.L % 4 == 0 and bool((self.offsets_host % 8 == 0).all())
         assert self.enc_dim == 32, "the network_ff topology expects a 32-wide encoding"
         sig = _ffmlp.FFMLP(32, 16, 64, 2)
         col = _ffmlp.FFMLP(32, 3, 64, 3)
@@ -141,11 +143,22 @@ class NGPTrainer:
 
     # ---- network pieces on raw buffers (shared by the step, the density query and the renderer) -----------
     def _encode(self, xyzs, x01, enc, M):
+        """xyzs in [-bound, bound] -> hash-grid features.  The (x + bound) / (2 bound) of GridEncoder.forward is applied by
+        the grid kernels as they load the points (ngp_set_input_bound) when the fast kernels serve this table; otherwise
+        through the x01 buffer."""
         s = abi.stream()
-        _ck(abi.lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
-        _ck(abi.lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                            enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                            abi.LAYOUT_BLC, s))
+        if self.fuse_x01:
+            src = xyzs
+            abi.lib.ngp_set_input_bound(self.bound)
+        else:
+            src = x01
+            _ck(abi.lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
+        try:
+            _ck(abi.lib.ngp_grid_encode_forward(src.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                                enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                                abi.LAYOUT_BLC, s))
+        finally:
+            abi.lib.ngp_set_input_bound(0.0)
 
     def _sigma_forward(self, enc, h, M, inference):
         fn = abi.lib.ngp_ffmlp_inference if inference else abi.lib.ngp_ffmlp_forward
@@ -213,9 +226,14 @@ class NGPTrainer:
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 2, 0, 6, 1,
                                    None, self.g_enc.data_ptr(), self.g_sig.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
         # table gradient: g16 was cleared by the previous optimizer step (k_adam consumes and zeroes it)
-        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
-                                         self.offsets_host.ctypes.data, self.g16.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None,
-                                         None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+        if self.fuse_x01:
+            lib.ngp_set_input_bound(self.bound)
+        try:
+            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), (self.xyzs if self.fuse_x01 else self.x01).data_ptr(), self.table16.data_ptr(),
+                                             self.offsets.data_ptr(), self.offsets_host.ctypes.data, self.g16.data_ptr(), M, 3, self.C, self.L, self.S,
+                                             self.base_resolution, None, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
+        finally:
+            lib.ngp_set_input_bound(0.0)
 
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
@@ -467,10 +485,7 @@ class NGPTrainer:
                                rs["dirs"].data_ptr(), rs["deltas"].data_ptr(), noises.data_ptr(), s))
         lib.ngp_set_batch_limit(rs["rows_dev"].data_ptr())
         try:  # shade the samples (inference kernels: no activations kept)
-            _ck(lib.ngp_nerf_x01(rs["xyzs"].data_ptr(), self.bound, rs["x01"].data_ptr(), M, s))
-            _ck(lib.ngp_grid_encode_forward(rs["x01"].data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                            rs["enc"].data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                            abi.LAYOUT_BLC, s))
+            self._encode(rs["xyzs"], rs["x01"], rs["enc"], M)
             _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s))
             _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s))
             _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s))

@@ -28,6 +28,7 @@ SIGNATURES = {
     "ngp_launch_count": (ctypes.c_longlong, []),
     "ngp_set_batch_limit": (_int, [_vp]),
     "ngp_profile_collect": (_int, [ctypes.c_char_p, _sz]),
+    "ngp_set_input_bound": (_int, [_f32]),
     "ngp_grid_encode_forward": (_int, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _u32, _int, _u32, _int, _int, _vp]),
     "ngp_grid_encode_backward": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _vp, _u32, _int, _u32, _int, _int, _vp]),
     "ngp_grad_total_variation": (_int, [_vp, _vp, _vp, _vp, _f32, _u32, _u32, _u32, _u32, _f32, _u32, _u32, _int, _int, _vp]),
