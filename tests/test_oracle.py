@@ -289,3 +289,33 @@ def test_sh_encode_orthonormal(oracle):
     y = oracle.sh_encode(d, 4)
     gram = 4 * np.pi * (y.T @ y) / d.shape[0]  # Monte-Carlo <Y_i, Y_j> over the sphere
     assert np.allclose(gram, np.eye(16), atol=0.03)
+
+
+def test_constant_step_t_sequence_closed_form():
+    """Host-side mirror of chunk_ts_const (csrc/raymarch_warp.cuh): inside one binade and away from rounding ties the
+    reference's chain t <- fl(t + d) advances by the same multiple of ulp(t) every step, so t_i = t_base + i * inc exactly.
+    The kernel takes that shortcut only under the guard reproduced here; everywhere it does, the values must be the chain's."""
+    f = np.float32
+    rng = np.random.default_rng(0)
+    used = 0
+    for trial in range(20000):
+        tb = f(rng.uniform(0.01, 8.0)) if trial % 3 else f(2.0 ** rng.integers(-5, 3) * (1 + rng.uniform(0, 0.02) * (rng.integers(0, 2) * 2 - 1)))
+        d = f(rng.choice([3.4641016 / 1024, 2 * 3.4641016 / 1024, 0.001, 0.0078125, rng.uniform(1e-4, 0.05)]))
+        t1 = f(tb + d)
+        inc = f(t1 - tb)
+        t32 = f(np.float64(32) * np.float64(inc) + np.float64(tb))
+        eb = int(tb.view(np.uint32)) & 0x7f800000
+        if eb < (24 << 23) or eb >= 0x7f800000:
+            continue
+        u = np.uint32(eb - (23 << 23)).view(np.float32)
+        err = f(d - inc)
+        ok = tb > 0 and (int(t32.view(np.uint32)) & 0x7f800000) == eb and inc > 0 and d >= f(4) * u and f(abs(err) * f(2)) != u
+        if not ok:
+            continue
+        used += 1
+        run = tb
+        for i in range(32):
+            assert run == f(np.float64(i) * np.float64(inc) + np.float64(tb)), (tb, d, i)
+            run = f(run + d)
+        assert run == t32, (tb, d)
+    assert used > 5000

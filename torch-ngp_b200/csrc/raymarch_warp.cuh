@@ -41,6 +41,36 @@ __device__ __forceinline__ bool test_point(const ray_t &r, const march_consts_t 
     return occ;
 }
 
+// 32 consecutive t values of a constant-step march (dt_gamma == 0): tl = t_base advanced `lane` times by t <- fl(t + d),
+// run = t_base advanced 32 times.  The reference's sequence is a chain of rounded additions, but while the chain stays
+// inside one binade every t is a multiple of u = ulp(t_base), so t + d rounds by the same multiple of u at every step
+// (unless t + d is an exact tie, where round-to-even alternates): t_i = t_base + i * inc EXACTLY, inc = fl(t_base + d) -
+// t_base, and the fma below is exact because its result is representable.  The whole chunk is then two instructions
+// instead of 32 dependent additions and 32 selects.  Binade crossings (a handful per ray), ties and degenerate steps take
+// the sequential path.  `ok` depends on t_base and d only: warp-uniform.
+__device__ __forceinline__ void chunk_ts_const(float t_base, float d, uint32_t lane, float &tl, float &run) {
+    const float t1 = __fadd_rn(t_base, d);
+    const float inc = __fsub_rn(t1, t_base);           // exact when t1 is in t_base's binade (implied by the t32 test)
+    const float t32 = __fmaf_rn(32.0f, inc, t_base);
+    const uint32_t eb = __float_as_uint(t_base) & 0x7f800000u;
+    const float u = __uint_as_float(eb - (23u << 23));  // ulp of the binade (eb >= 24 checked below)
+    const float err = __fsub_rn(d, inc);                // rounding error of t_base + d (Sterbenz: inc within a factor 2 of d)
+    const bool ok = t_base > 0.0f && eb >= (24u << 23) && eb < 0x7f800000u && (__float_as_uint(t32) & 0x7f800000u) == eb &&
+                    inc > 0.0f && d >= 4.0f * u && __fmul_rn(fabsf(err), 2.0f) != u;
+    if (ok) {
+        tl = __fmaf_rn((float)lane, inc, t_base);
+        run = t32;
+        return;
+    }
+    tl = t_base;
+    run = t_base;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        if (i == (int)lane) tl = run;
+        run = __fadd_rn(run, d);
+    }
+}
+
 __device__ __forceinline__ uint32_t mask_from(uint32_t pos) { return pos >= 32 ? 0u : (0xffffffffu << pos); }
 __device__ __forceinline__ uint32_t mask_below(uint32_t pos) { return pos >= 32 ? 0xffffffffu : ((1u << pos) - 1u); }
 
@@ -64,11 +94,7 @@ __device__ __forceinline__ uint32_t march_ray_warp(const ray_t &r, const march_c
         // t of this lane's point = t_base advanced `lane` times; `run` ends as the next chunk's base
         float tl = t_base, run = t_base;
         if (const_dt) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                if (i == (int)lane) tl = run;
-                run = __fadd_rn(run, dt0);
-            }
+            chunk_ts_const(t_base, dt0, lane, tl, run);
         } else {
 #pragma unroll 8
             for (int i = 0; i < 32; ++i) {
@@ -152,11 +178,7 @@ __device__ __forceinline__ void replay_ray_warp(const ray_t &r, const march_cons
     for (uint32_t ch = 0; ch < nchunks; ++ch) {
         float tl = t_base, run = t_base;
         if (const_dt) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                if (i == (int)lane) tl = run;
-                run = __fadd_rn(run, dt0);
-            }
+            chunk_ts_const(t_base, dt0, lane, tl, run);
         } else {
 #pragma unroll 8
             for (int i = 0; i < 32; ++i) {
