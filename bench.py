@@ -144,6 +144,7 @@ class HashGridWorkload:
     Device step = forward + grad-table clear + backward through gridencoder._backend (C ABI).
     Algorithmic bytes: fwd 1,164 B/pt, bwd 1,164 B/pt + T*C*4 B table clear."""
     name = "hashgrid"
+    l2_flush = True  # the 47 MB table and the 2^18-point buffers would sit in the 126 MB L2 from step to step
     metric = "hash-encode Mpts/s fwd+bwd"
     unit = "Mpts/s"
     dtype = "f32"
@@ -155,7 +156,7 @@ class HashGridWorkload:
 
     def config(self, world):
         return {"workload": "GridEncoder fwd+bwd, 2^18 random points in [-1,1]^3 per GPU, L=16 F=2 log2_hashmap=19 fp32 (configs[0])",
-                "points_per_gpu": self.B, "table_entries": int(self.T), "l2": "flushed between steps (256 MiB memset outside the per-step events)",
+                "points_per_gpu": self.B, "table_entries": int(self.T), "l2": getattr(self, "l2_note", ""),
                 "parallelism": f"dp{world} (independent points, no collective)"}
 
     def setup(self, dev, rank, world):
@@ -265,6 +266,7 @@ class NerfTrainWorkload:
     The model is pre-trained for `--pretrain` steps before the warm-up so that the occupancy grid (and with it the
     samples per ray) is that of a scene in training, not of the random initialisation."""
     name = "nerf_train"
+    l2_flush = False  # a step streams ~470 MB (parameters + Adam moments 147 MB, fp16 table and gradient 49 MB, ~270 MB of sample buffers) > 126 MB L2
     metric = "train rays/s"
     unit = "rays/s"
     dtype = "f16"
@@ -306,7 +308,7 @@ class NerfTrainWorkload:
                                                                 "2^18 rays/step global, data-parallel (configs[2])" if not self.args.rays else
                                                                 f"{self.args.rays} rays per GPU per step")),
              "parallelism": f"dp{world}" + (" (NCCL all-reduce of fp16 table + fp32 MLP gradients)" if world > 1 else ""),
-             "l2": "flushed between steps (256 MiB memset outside the per-step events)", "pretrain_steps": self.args.pretrain}
+             "l2": getattr(self, "l2_note", ""), "pretrain_steps": self.args.pretrain}
         if tr is not None:
             c.update({"rays_per_gpu": self.N, "global_rays": self.N * world, "samples_per_ray": round(tr.mean_count / self.N, 2),
                       "samples_per_step_per_gpu": tr.mean_count, "sample_capacity": tr.M, "cuda_graph": bool(tr.use_graph),
@@ -427,8 +429,9 @@ class NerfTrainWorkload:
 class RenderWorkload:
     """1920x1080 frames of the synthetic scene from a 128^3 density bitfield: march_rays / composite_rays loop with the
     network_ff model (briefly pre-trained so that the occupancy grid is that of a scene).  Each rank renders one
-    contiguous band of rows (nerf/parallel.py::row_band), no collective; a step is one frame (one band per rank)."""
+    share of the rows (nerf/parallel.py::row_stripes), no collective; a step is one frame (one share per rank)."""
     name = "render"
+    l2_flush = False  # a frame streams ~100 GB through the sample buffers (~160 M samples x ~600 B)
     metric = "render Mrays/s"
     unit = "Mrays/s"
     dtype = "f16"
@@ -464,7 +467,7 @@ class RenderWorkload:
 
     def config(self, world):
         c = {"workload": f"inference render {self.W}x{self.Hh} frames, march_rays/composite_rays from a 128^3 bitfield + network_ff shading (configs[3])",
-             "parallelism": f"rows dealt to {world} rank(s) in interleaved 8-row stripes, no collective", "l2": "flushed between steps (256 MiB memset outside the per-step events)",
+             "parallelism": f"rows dealt to {world} rank(s) in interleaved 8-row stripes, no collective", "l2": getattr(self, "l2_note", ""),
              "pretrain_steps": self.args.pretrain}
         if hasattr(self, "tr"):
             c.update({"rows_per_gpu": int(self.rows.numel()), "loop_iterations": getattr(self.tr, "last_render_iters", None)})
@@ -529,6 +532,7 @@ class SDFWorkload:
     """main_sdf --fp16 --ff on an analytic torus: 2^20 points per GPU per step (surface / near-surface / uniform samples),
     hash grid 16x2 T=2^19 -> FFMLP 32->64x3->1, mape loss, GradScaler + Adam; data-parallel over points with N>1."""
     name = "sdf"
+    l2_flush = False  # 2^20 points x ~330 B of sample buffers + 196 MB of parameters, moments and gradients > 126 MB L2
     metric = "sdf train Mpts/s"
     unit = "Mpts/s"
     dtype = "f16"
@@ -555,7 +559,7 @@ class SDFWorkload:
     def config(self, world):
         c = {"workload": "main_sdf --fp16 --ff training step, analytic torus SDF, 2^20 points/batch per GPU (configs[4])",
              "parallelism": f"dp{world}" + (" (NCCL all-reduce of table + MLP gradients)" if world > 1 else ""),
-             "l2": "flushed between steps (256 MiB memset outside the per-step events)", "points_per_gpu": self.B}
+             "l2": getattr(self, "l2_note", ""), "points_per_gpu": self.B}
         if hasattr(self, "tr"):
             c["last_loss"] = self.tr.loss()
         return c
@@ -693,6 +697,7 @@ def main():
     ap.add_argument("--pretrain", type=int, default=1024, help="nerf_train: untimed optimisation steps before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="nerf_train: launch the step eagerly instead of replaying CUDA graphs")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--flush", action="store_true", help="flush L2 between steps even for the workloads whose per-step data exceeds L2")
     ap.add_argument("--adam-blocks", type=int, default=5, help="nerf_train: k_adam blocks per SM while it runs beside the marcher")
     ap.add_argument("--no-overlap", action="store_true", help="nerf_train: optimizer(n) strictly before march(n+1) (default: side by side on two streams)")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=INT", help="ngp_set_option before setup (kernel A/B tests; development only)")
@@ -716,7 +721,10 @@ def main():
         k, v = kv.split("=")
         abi.set_option(k, int(v))
     wl.setup(dev, rank, world)
-    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    do_flush = (getattr(wl, "l2_flush", True) or args.flush) and not args.no_flush
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if do_flush else None
+    wl.l2_note = ("flushed between steps (256 MiB memset outside the per-step events)" if do_flush else
+                  "not flushed: the data one step streams (see workload) is several times the 126 MB L2")
 
     for _ in range(args.warmup):
         wl.step_device()
