@@ -106,6 +106,12 @@ NGP_API int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, con
 NGP_API int ngp_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uint32_t N, float *coords, void *stream);
 NGP_API int ngp_morton3D(const int *coords, uint32_t N, int *indices, void *stream);
 NGP_API int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *stream);
+/* NeRFRenderer.mark_untrained_grid (nerf/renderer.py:433-496; the reference's 5-deep Python loop over cell blocks,
+ * cascades and camera batches) as one kernel.  poses [B,4,4] f32 camera-to-world (device), intrinsics fx fy cx cy;
+ * density_grid [C, H^3] in Morton order: cells whose centre no camera sees (frustum widened by one cell) become -1.
+ * count_out [C, H^3] i32 or NULL: the per-cell camera count of the reference's `count` tensor. */
+NGP_API int ngp_mark_untrained_grid(const float *poses, uint32_t B, double fx, double fy, double cx, double cy, float bound, uint32_t C,
+                            uint32_t H, float *density_grid, int *count_out, void *stream);
 /* N = number of output BYTES = C*H^3/8 (raymarching.cu:292) */
 NGP_API int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream);
 

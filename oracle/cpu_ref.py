@@ -185,6 +185,37 @@ def morton3D_invert(indices):
     return out
 
 
+def mark_untrained_grid(poses, intrinsic, bound, cascade, H):
+    """count[C, H^3] (Morton order) of the cameras that see each cell -- numpy restatement of
+    NeRFRenderer.mark_untrained_grid (nerf/renderer.py:433-496) without its blocking loops, float32 with one rounding per
+    torch op; the camera-space product is summed ((c0 R0j + c1 R1j) + c2 R2j).  Cells with count 0 are the ones the
+    reference sets to -1 (:493)."""
+    f = np.float32
+    poses = _c(poses, np.float32).reshape(-1, 4, 4)
+    fx, fy, cx, cy = [float(v) for v in intrinsic]
+    r = np.arange(H, dtype=np.int32)
+    xx, yy, zz = np.meshgrid(r, r, r, indexing="ij")
+    coords = np.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], -1).astype(np.int32)  # :460
+    indices = morton3D(coords).astype(np.int64)                                                # :461
+    world = (f(2) * coords.astype(np.float32) / f(H - 1) - f(1)).astype(np.float32)            # :462
+    count = np.zeros((cascade, H ** 3), np.int32)
+    kx, ky = f(cx / fx), f(cy / fy)
+    for cas in range(cascade):
+        b = min(2 ** cas, bound)                                                               # :466
+        hgs = b / H                                                                            # :467
+        cw = (world * f(b - hgs)).astype(np.float32)                                           # :469
+        margin = f(hgs * 2)
+        acc = np.zeros(H ** 3, np.int32)
+        for P in poses:                                                                        # :473-486, one camera at a time
+            d = (cw - P[:3, 3][None, :]).astype(np.float32)
+            cam = [((d[:, 0] * P[0, j]).astype(np.float32) + (d[:, 1] * P[1, j]).astype(np.float32)).astype(np.float32) for j in range(3)]
+            cam = [(cam[j] + (d[:, 2] * P[2, j]).astype(np.float32)).astype(np.float32) for j in range(3)]
+            m = (cam[2] > 0) & (np.abs(cam[0]) < (kx * cam[2]).astype(np.float32) + margin) & (np.abs(cam[1]) < (ky * cam[2]).astype(np.float32) + margin)
+            acc += m.astype(np.int32)
+        count[cas, indices] = acc                                                              # :489
+    return count
+
+
 def packbits(grid, thresh):
     grid = _c(grid, np.float32)
     N = grid.size // 8

@@ -240,3 +240,34 @@ def test_march_rays_train_step_cap_and_full_occupancy(oracle, scene, variant, ma
     assert np.array_equal(rays.cpu().numpy(), ref[3])
     assert np.array_equal(xyzs.cpu().numpy(), ref[0])
     assert np.array_equal(deltas.cpu().numpy(), ref[2])
+
+
+def test_mark_untrained_grid_matches_oracle_and_stays_unoccupied():
+    """ngp_mark_untrained_grid (one kernel) against the numpy restatement of nerf/renderer.py:433-496: per-cell camera
+    counts bit-exact, unseen cells -1; a density-grid update afterwards never turns them on (renderer.py:565-566)."""
+    import raymarching
+    from oracle import cpu_ref
+    from test_oracle import _orbit_poses
+    cpu_ref.build()
+    H, C, bound = 32, 2, 2.0
+    poses = _orbit_poses(70)  # > 64: two shared-memory batches of cameras
+    intr = (55.0, 50.0, 20.0, 16.0)
+    grid = torch.rand(C, H ** 3, device="cuda")
+    before = grid.clone()
+    count = raymarching.mark_untrained_grid(poses, intr, grid, bound, return_count=True)
+    ref = cpu_ref.mark_untrained_grid(poses, intr, bound, C, H)
+    assert np.array_equal(count.cpu().numpy(), ref)
+    unseen = torch.from_numpy(ref == 0).cuda()
+    assert 0 < int(unseen.sum()) < unseen.numel()
+    assert torch.equal(grid[unseen], torch.full_like(grid[unseen], -1)) and torch.equal(grid[~unseen], before[~unseen])
+    # the trainer's update keeps them out of the bitfield
+    import nerf
+    tr = nerf.NGPTrainer(bound=1.0, num_rays=256, use_graph=False, log2_hashmap_size=15)
+    n_marked = tr.mark_untrained_grid(_orbit_poses(6), (300.0, 300.0, 64.0, 64.0))
+    assert 0 < n_marked < tr.density_grid.numel()
+    marked = tr.density_grid < 0
+    tr.update_extra_state()
+    assert torch.equal(tr.density_grid < 0, marked)
+    bits = tr.density_bitfield.cpu().numpy()
+    occ = np.unpackbits(bits, bitorder="little").astype(bool)
+    assert not occ[marked.view(-1).cpu().numpy()].any()

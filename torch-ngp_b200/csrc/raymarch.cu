@@ -185,6 +185,49 @@ __global__ void __launch_bounds__(256) k_morton3D_invert(const int *__restrict__
     coords[3 * (size_t)n + 2] = (int)compact_bits((uint32_t)(ind >> 2));
 }
 
+// mark_untrained_grid (nerf/renderer.py:433-496) as one kernel instead of a 5-deep Python loop over cell blocks, cascades
+// and camera batches: one thread per cell (c, Morton index n) walks the camera list (staged 64 poses at a time in shared
+// memory) and counts the cameras whose frustum, widened by one cell, contains the cell centre; cells no camera sees are
+// set to -1 in the density grid (they never become occupied: update_extra_state only touches cells >= 0).
+// Arithmetic = the torch expressions of the reference, one rounding per op (no contraction); the 3x3 product is summed
+// ((c0 R0j + c1 R1j) + c2 R2j).  poses: [B,4,4] row-major camera-to-world.
+__global__ void __launch_bounds__(256) k_mark_untrained(const float *__restrict__ poses, uint32_t B, float kx, float ky, float bound, uint32_t C,
+                                                        uint32_t H, float *__restrict__ grid, int *__restrict__ count_out) {
+    __shared__ float s_pose[64][12];
+    const uint32_t H3 = H * H * H;
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x, cas = blockIdx.y;
+    const float bound_c = fminf(scalbnf(1.0f, (int)cas), bound);
+    const double hgs_d = (double)bound_c / (double)H;
+    const float scale = (float)((double)bound_c - hgs_d), margin = (float)(hgs_d * 2.0);
+    float w[3];
+    {
+        const uint32_t c[3] = {compact_bits(n), compact_bits(n >> 1), compact_bits(n >> 2)};
+#pragma unroll
+        for (int d = 0; d < 3; ++d) w[d] = __fmul_rn(__fsub_rn(__fdiv_rn(__fmul_rn(2.0f, (float)c[d]), (float)(H - 1)), 1.0f), scale);
+    }
+    int count = 0;
+    for (uint32_t b0 = 0; b0 < B; b0 += 64) {
+        const uint32_t nb = min(64u, B - b0);
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nb * 12; i += blockDim.x) s_pose[i / 12][i % 12] = poses[(size_t)(b0 + i / 12) * 16 + i % 12];
+        __syncthreads();
+        for (uint32_t b = 0; b < nb; ++b) {
+            const float *P = s_pose[b];  // rows 0..2 of the 4x4: P[4 i + j] = R[i][j], P[4 i + 3] = t[i]
+            const float d0 = __fsub_rn(w[0], P[3]), d1 = __fsub_rn(w[1], P[7]), d2 = __fsub_rn(w[2], P[11]);
+            float cam[3];
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                cam[j] = __fadd_rn(__fadd_rn(__fmul_rn(d0, P[j]), __fmul_rn(d1, P[4 + j])), __fmul_rn(d2, P[8 + j]));
+            const bool in = cam[2] > 0.0f && fabsf(cam[0]) < __fadd_rn(__fmul_rn(kx, cam[2]), margin) &&
+                            fabsf(cam[1]) < __fadd_rn(__fmul_rn(ky, cam[2]), margin);
+            count += in ? 1 : 0;
+        }
+    }
+    if (n >= H3) return;
+    if (count_out) count_out[(size_t)cas * H3 + n] = count;
+    if (count == 0) grid[(size_t)cas * H3 + n] = -1.0f;
+}
+
 // one thread packs 32 cells (128 B in, 4 B out): 8x float4 loads, one 32-bit store.
 // N4 = number of whole 4-byte groups; the (< 4) trailing bytes go through k_packbits_tail.
 __global__ void __launch_bounds__(256) k_packbits32(const float4 *__restrict__ grid4, uint32_t N4, float thresh,

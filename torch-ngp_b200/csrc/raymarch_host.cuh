@@ -54,6 +54,18 @@ int ngp_morton3D_invert(const int *indices, uint32_t N, int *coords, void *strea
     return NGP_OK;
 }
 
+int ngp_mark_untrained_grid(const float *poses, uint32_t B, double fx, double fy, double cx, double cy, float bound, uint32_t C, uint32_t H,
+                            float *density_grid, int *count_out, void *stream) {
+    using namespace ngp;
+    NGP_CHECK_ARG(density_grid && (B == 0 || poses), "mark_untrained_grid: null pointer argument");
+    NGP_CHECK_ARG(C >= 1 && H >= 2 && H <= 1024 && fx != 0.0 && fy != 0.0, "mark_untrained_grid: bad cascade / grid size / focal length");
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t H3 = H * H * H;
+    { NGP_PROF("k_mark_untrained", st); k_mark_untrained<<<dim3(div_round_up(H3, 256u), C, 1), 256, 0, st>>>(poses, B, (float)(cx / fx), (float)(cy / fy), bound, C, H, density_grid, count_out); }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
 int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream) {
     using namespace ngp;
     if (N == 0) return NGP_OK;

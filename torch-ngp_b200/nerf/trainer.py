@@ -442,6 +442,14 @@ class NGPTrainer:
         self.count_sum.zero_()
         self.local_step = 0
 
+    @torch.no_grad()
+    def mark_untrained_grid(self, poses, intrinsic):
+        """nerf/renderer.py:433-496: cells outside every training camera's frustum are set to -1 and stay unoccupied.
+        Returns the number of cells marked (the figure the reference prints)."""
+        self.flush()
+        count = _raymarching.mark_untrained_grid(poses, intrinsic, self.density_grid, self.bound, return_count=True)
+        return int((count == 0).sum().item())
+
     def mean_density(self):
         return float(self.mean_sum.item()) / self.density_grid.numel()
 

@@ -36,6 +36,7 @@ SIGNATURES = {
     "ngp_sph_from_ray": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
     "ngp_morton3D": (_int, [_vp, _u32, _vp, _vp]),
     "ngp_morton3D_invert": (_int, [_vp, _u32, _vp, _vp]),
+    "ngp_mark_untrained_grid": (_int, [_vp, _u32, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double, _f32, _u32, _u32, _vp, _vp, _vp]),
     "ngp_packbits": (_int, [_vp, _u32, _f32, _vp, _vp]),
     "ngp_march_rays_train_workspace_bytes": (_sz, [_u32]),
     "ngp_march_rays_train_workspace_bytes_ex": (_sz, [_u32, _f32, _u32]),

@@ -50,6 +50,16 @@ def morton3D_invert(indices, N, coords):
     abi.check(abi.lib.ngp_morton3D_invert(indices.data_ptr(), N, coords.data_ptr(), abi.stream()))
 
 
+def mark_untrained_grid(poses, fx, fy, cx, cy, bound, C, H, density_grid, count=None):
+    B = poses.shape[0]
+    abi.check_tensor(poses, "poses", _f32, "a float", 16 * B)
+    abi.check_tensor(density_grid, "density_grid", _f32, "a float", C * H * H * H)
+    if count is not None:
+        abi.check_tensor(count, "count", torch.int32, "an int", C * H * H * H)
+    abi.check(abi.lib.ngp_mark_untrained_grid(poses.data_ptr(), B, float(fx), float(fy), float(cx), float(cy), float(bound), C, H,
+                                              density_grid.data_ptr(), abi.ptr(count), abi.stream()))
+
+
 def packbits(grid, N, density_thresh, bitfield):
     abi.check_tensor(grid, "grid", _f32, "a float", 8 * N)
     abi.check_tensor(bitfield, "bitfield", _u8, "a uint8", N)

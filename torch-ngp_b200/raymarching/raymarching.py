@@ -217,6 +217,23 @@ class _composite_rays(Function):
 composite_rays = _composite_rays.apply
 
 
+def mark_untrained_grid(poses, intrinsic, density_grid, bound, return_count=False):
+    """NeRFRenderer.mark_untrained_grid (nerf/renderer.py:433-496) on a density grid [cascade, H^3] (Morton order), in
+    place: cells no training camera sees become -1.  poses [B,4,4] camera-to-world (tensor or ndarray), intrinsic
+    (fx, fy, cx, cy).  One kernel instead of the reference's loops over 64^3 cell blocks x cascades x 64-camera batches."""
+    import numpy as np
+    if isinstance(poses, np.ndarray):
+        poses = torch.from_numpy(poses)
+    poses = poses.to(density_grid.device, torch.float32).contiguous()
+    C, H3 = density_grid.shape
+    H = round(H3 ** (1.0 / 3.0))
+    assert H * H * H == H3, "density_grid must be [cascade, H^3]"
+    fx, fy, cx, cy = [float(v) for v in intrinsic]
+    count = torch.empty(C, H3, dtype=torch.int32, device=density_grid.device) if return_count else None
+    _backend.mark_untrained_grid(poses, fx, fy, cx, cy, bound, C, H, density_grid, count)
+    return count
+
+
 def compact_alive(rays_alive, n_alive=None):
     """Device-side `rays_alive[rays_alive >= 0]` (nerf/renderer.py:416) without a boolean-mask sync.
     -> (compacted ids in a same-sized buffer, device int32[1] count)."""
