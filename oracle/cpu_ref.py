@@ -300,16 +300,41 @@ def ffmlp_split_weights(weights, input_dim, output_dim_padded, hidden_dim, num_l
     return ws
 
 
+_K_ACT = 10.0  # ffmlp/src/utils.h:41
+
+
+def ffmlp_activation(act, x):
+    """hidden activation by the reference's code (ffmlp.cu:22-32, utils.h:425-470)"""
+    if act == 0: return np.maximum(x, 0)
+    if act == 1: return np.exp(x)
+    if act == 2: return np.sin(x)
+    if act == 3: return 1.0 / (1.0 + np.exp(-x))
+    if act == 4: return 0.5 * (x * _K_ACT + np.sqrt((x * _K_ACT) ** 2 + 4)) / _K_ACT
+    if act == 5: return np.log(np.exp(x * _K_ACT) + 1.0) / _K_ACT
+    return x
+
+
+def ffmlp_activation_backward(act, y):
+    """d act / d pre-activation from the stored post-activation y (utils.h:538-580)"""
+    if act == 0: return (y > 0).astype(y.dtype)
+    if act == 1: return y
+    if act == 3: return y * (1.0 - y)
+    if act == 4: return (y * _K_ACT) ** 2 / ((y * _K_ACT) ** 2 + 1.0)
+    if act == 5: return 1.0 - np.exp(-y * _K_ACT)
+    if act == 6: return np.ones_like(y)
+    raise ValueError("Sine has no backward from post-activations (utils.h:552-556)")
+
+
 def ffmlp_forward(inputs, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype=np.float64,
-                  round_activations_fp16=False):
-    """-> (outputs [B,out_pad], [post-activation of every hidden layer]).  ReLU hidden, linear output."""
+                  round_activations_fp16=False, activation=0):
+    """-> (outputs [B,out_pad], [post-activation of every hidden layer]).  Hidden activation by code (default ReLU), linear output."""
     x = np.asarray(inputs, dtype=dtype)
     acts = []
     ws = ffmlp_split_weights(np.asarray(weights, dtype=dtype), input_dim, output_dim_padded, hidden_dim, num_layers)
     for i, w in enumerate(ws):
         x = x @ w.T
         if i != num_layers:
-            x = np.maximum(x, 0)
+            x = ffmlp_activation(activation, x)
             if round_activations_fp16:
                 x = x.astype(np.float16).astype(dtype)
             acts.append(x)
@@ -317,14 +342,14 @@ def ffmlp_forward(inputs, weights, input_dim, output_dim_padded, hidden_dim, num
 
 
 def ffmlp_backward(grad, inputs, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype=np.float64,
-                   round_activations_fp16=False):
+                   round_activations_fp16=False, activation=0):
     """-> (grad_inputs [B,in], grad_weights flat), matching ffmlp.cu:749-895's results.
     round_activations_fp16: the saved activations (and so the ReLU masks, ffmlp.cu:105-108) are the fp16-rounded ones,
     as both the reference and the tcgen05 kernels store them -- a pre-activation within rounding distance of zero
     otherwise flips a mask and changes that unit's whole gradient contribution."""
     x = np.asarray(inputs, dtype=dtype)
     ws = ffmlp_split_weights(np.asarray(weights, dtype=dtype), input_dim, output_dim_padded, hidden_dim, num_layers)
-    _, acts = ffmlp_forward(x, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype, round_activations_fp16)
+    _, acts = ffmlp_forward(x, weights, input_dim, output_dim_padded, hidden_dim, num_layers, dtype, round_activations_fp16, activation)
     g = np.asarray(grad, dtype=dtype)
     gws = [None] * len(ws)
     for i in range(num_layers, -1, -1):
@@ -332,7 +357,7 @@ def ffmlp_backward(grad, inputs, weights, input_dim, output_dim_padded, hidden_d
         gws[i] = g.T @ a_prev
         g = g @ ws[i]
         if i > 0:
-            g = g * (acts[i - 1] > 0)
+            g = g * ffmlp_activation_backward(activation, acts[i - 1])
     return g, np.concatenate([w.reshape(-1) for w in gws])
 
 

@@ -211,6 +211,46 @@ def test_vs_reference_extension():
     assert rel(gw.float().cpu().numpy(), gw_ref.float().cpu().numpy()) < 5e-2
 
 
+ACTS = {"relu": 0, "exponential": 1, "sine": 2, "sigmoid": 3, "squareplus": 4, "softplus": 5, "none": 6}
+
+
+@pytest.mark.parametrize("name", list(ACTS))
+@pytest.mark.parametrize("cfg", [(32, 16, 64, 2), (16, 16, 32, 3)])
+def test_hidden_activations_vs_twin(oracle, name, cfg, bwd_variant):
+    """The reference's hidden activations (ffmlp.py:89-96, utils.h:425-580): forward on the fp32 accumulator, backward from
+    the stored post-activation.  Through the kernels and through the module (autograd)."""
+    import ffmlp
+    be = _be()
+    act = ACTS[name]
+    in_dim, out_dim, hid, nl = cfg
+    B = 700
+    torch.manual_seed(11)
+    x = (torch.randn(B, in_dim, device=DEV) * 0.3).half()
+    g = (torch.randn(B, out_dim, device=DEV) * 0.5).half()
+    w = _weights(in_dim, out_dim, hid, nl, seed=4) * (0.5 if name == "exponential" else 1.0)
+    w16 = w.half().float().cpu().numpy().astype(np.float64)
+    y = torch.empty(B, out_dim, device=DEV, dtype=torch.half)
+    be.ffmlp_forward(x, w, B, in_dim, out_dim, hid, nl, act, 6, None, y)
+    ref, _ = oracle.ffmlp_forward(x.float().cpu().numpy(), w16, in_dim, out_dim, hid, nl, round_activations_fp16=True, activation=act)
+    assert np.abs(y.float().cpu().numpy() - ref).max() / np.abs(ref).max() < 2e-3, name
+    if name == "sine":
+        return
+    gx, gw = torch.empty_like(x), torch.empty(w.numel(), device=DEV)
+    be.ffmlp_backward(g, x, w, None, B, in_dim, out_dim, hid, nl, act, 6, True, None, gx, gw)
+    gx_ref, gw_ref = oracle.ffmlp_backward(g.float().cpu().numpy(), x.float().cpu().numpy(), w16, in_dim, out_dim, hid, nl,
+                                            round_activations_fp16=True, activation=act)
+    ex = np.abs(gx.float().cpu().numpy() - gx_ref).max() / np.abs(gx_ref).max()
+    ew = np.abs(gw.cpu().numpy() - gw_ref).max() / np.abs(gw_ref).max()
+    assert ex < 1e-2 and ew < 1e-2, (name, ex, ew)
+    # module level: FFMLP(activation=name) trains through autograd
+    net = ffmlp.FFMLP(in_dim, 3, hid, nl, activation=name).to(DEV)
+    with torch.no_grad():
+        net.weights.mul_(0.3)  # the default U(+-sqrt(3/hidden)) init overflows fp16 through stacked exponentials
+    out = net(x)
+    out.float().square().mean().backward()
+    assert out.shape == (B, 3) and torch.isfinite(net.weights.grad).all() and net.weights.grad.abs().max() > 0
+
+
 def test_error_behaviour():
     be = _be()
     x = torch.zeros(128, 32, device=DEV, dtype=torch.half)
@@ -222,7 +262,9 @@ def test_error_behaviour():
         be.ffmlp_forward(x.cpu(), w, 128, 32, 16, 64, 2, 0, 6, None, y)
     with pytest.raises(RuntimeError, match="half"):
         be.ffmlp_forward(x.float(), w, 128, 32, 16, 64, 2, 0, 6, None, y)
-    with pytest.raises(RuntimeError, match="ReLU"):
-        be.ffmlp_forward(x, w, 128, 32, 16, 64, 2, 2, 6, None, y)
+    with pytest.raises(RuntimeError, match="activation must be one of"):
+        be.ffmlp_forward(x, w, 128, 32, 16, 64, 2, 9, 6, None, y)
+    with pytest.raises(RuntimeError, match="Sine activation has no backward"):
+        be.ffmlp_backward(y, x, w, None, 128, 32, 16, 64, 2, 2, 6, True, None, torch.empty_like(x), torch.empty_like(w))
     # empty batch is a no-op
     be.ffmlp_forward(x[:0], w, 0, 32, 16, 64, 2, 0, 6, None, y[:0])

@@ -38,9 +38,11 @@ struct mlp_t {
     // weight matrix m (0..nl): rows[m] x K[m], flat offset woff[m] (elements), smem offset soff[m] (bytes)
     uint32_t rows[kMaxLayers + 1], K[kMaxLayers + 1], woff[kMaxLayers + 1], soff[kMaxLayers + 1];
     uint32_t wbytes, nweights;
+    uint32_t act;  // hidden activation, the reference's codes (ffmlp.cu:22-32): 0 ReLU 1 Exponential 2 Sine 3 Sigmoid 4 Squareplus 5 Softplus 6 None
 };
 
 inline void make_mlp(mlp_t &m, uint32_t B, uint32_t in, uint32_t out, uint32_t hid, uint32_t nl) {
+    m.act = 0;
     m.B = B; m.in = in; m.out = out; m.hid = hid; m.nl = nl;
     uint32_t w = 0, s = 0;
     for (uint32_t i = 0; i <= nl; ++i) {
@@ -110,9 +112,52 @@ __device__ __forceinline__ uint32_t relu2(float a, float b) {
     const __half2 h = __hmax2(__floats2half2_rn(a, b), __float2half2_rn(0.f));
     return *reinterpret_cast<const uint32_t *>(&h);
 }
-// acc[row, col0 .. col0+CW) -> ReLU -> fp16 -> swizzled tile(s)
+// The reference's other hidden activations (utils.h:425-470 forward, :538-580 backward from the stored POST-activation),
+// evaluated on the fp32 accumulator; K_ACT = 10 (utils.h:41).  `act` is uniform over the launch.
+constexpr float kKAct = 10.0f;
+__device__ __forceinline__ float act_fwd(uint32_t act, float x) {
+    switch (act) {
+        case 1: return expf(x);
+        case 2: return sinf(x);
+        case 3: return 1.0f / (1.0f + expf(-x));
+        case 4: { const float k = x * kKAct; return 0.5f * (k + sqrtf(k * k + 4.0f)) / kKAct; }
+        case 5: return logf(expf(x * kKAct) + 1.0f) / kKAct;
+        case 6: return x;
+        default: return fmaxf(x, 0.0f);
+    }
+}
+// d act / d pre-activation as a function of the post-activation y (what the tile holds)
+__device__ __forceinline__ float act_bwd_from_out(uint32_t act, float y) {
+    switch (act) {
+        case 1: return y;
+        case 3: return y * (1.0f - y);
+        case 4: { const float k = y * kKAct; return k * k / (k * k + 1.0f); }
+        case 5: return 1.0f - expf(-y * kKAct);
+        case 6: return 1.0f;
+        default: return y > 0.0f ? 1.0f : 0.0f;  // ReLU (Sine is rejected on the host: its derivative needs the pre-activation)
+    }
+}
+
+// acc[row, col0 .. col0+CW) -> activation (ReLU: fast path) -> fp16 -> swizzled tile(s)
+// generic activation: out of line, so that the ReLU kernels keep their register allocation and code size
 template <int CW>
-__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0) {
+__device__ __noinline__ void epi_act_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0, uint32_t act) {
+    float v[CW];
+    tmem_ldN<CW>(taddr + col0, v);
+    uint8_t *t = tiles + (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
+    const uint32_t c8 = (col0 & 63u) >> 3;
+#pragma unroll
+    for (int j = 0; j < CW; ++j) v[j] = act_fwd(act, v[j]);
+#pragma unroll
+    for (int j = 0; j < CW; j += 8) {
+        uint4 u;
+        u.x = pack2(v[j], v[j + 1]); u.y = pack2(v[j + 2], v[j + 3]); u.z = pack2(v[j + 4], v[j + 5]); u.w = pack2(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4 *>(t + (((c8 + (j >> 3)) ^ (row & 7u)) << 4)) = u;
+    }
+}
+template <int CW>
+__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0, uint32_t act = 0u) {
+    if (act != 0u) { epi_act_to_tile<CW>(taddr, tiles, row, col0, act); return; }
     float v[CW];
     tmem_ldN<CW>(taddr + col0, v);
     uint8_t *t = tiles + (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
@@ -131,8 +176,30 @@ __device__ __forceinline__ uint32_t mask2(float a, float b, uint32_t h2) {
     return g & ((h2 & 0xFFFFu ? 0xFFFFu : 0u) | (h2 & 0xFFFF0000u ? 0xFFFF0000u : 0u));
 }
 // acc[row, col0 .. col0+CW) * (act[row, :] > 0) -> fp16 -> swizzled tile(s)   (ReLU backward from the saved activation)
+__device__ __forceinline__ uint32_t dact2(uint32_t act, float a, float b, uint32_t h2) {
+    const float2 y = __half22float2(*reinterpret_cast<const __half2 *>(&h2));
+    return pack2(a * act_bwd_from_out(act, y.x), b * act_bwd_from_out(act, y.y));
+}
 template <int CW>
-__device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t col0) {
+__device__ __noinline__ void epi_dact_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t col0, uint32_t act) {
+    float v[CW];
+    tmem_ldN<CW>(taddr + col0, v);
+    const uint32_t base = (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
+    const uint32_t c8 = (col0 & 63u) >> 3;
+#pragma unroll
+    for (int j = 0; j < CW; j += 8) {
+        const uint32_t o = base + (((c8 + (j >> 3)) ^ (row & 7u)) << 4);
+        const uint4 a = *reinterpret_cast<const uint4 *>(act_tiles + o);
+        uint4 u;
+        u.x = dact2(act, v[j], v[j + 1], a.x); u.y = dact2(act, v[j + 2], v[j + 3], a.y);
+        u.z = dact2(act, v[j + 4], v[j + 5], a.z); u.w = dact2(act, v[j + 6], v[j + 7], a.w);
+        *reinterpret_cast<uint4 *>(tiles + o) = u;
+    }
+}
+template <int CW>
+__device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t col0,
+                                                 uint32_t act = 0u) {
+    if (act != 0u) { epi_dact_to_tile<CW>(taddr, act_tiles, tiles, row, col0, act); return; }
     float v[CW];
     tmem_ldN<CW>(taddr + col0, v);
     const uint32_t base = (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
@@ -209,7 +276,7 @@ __device__ __forceinline__ void pipe_sync(uint32_t id) { asm volatile("bar.sync 
 // weights: measured on B200 a layer step is latency bound (each tcgen05.mma of this size takes ~80-100 cycles to
 // ISSUE, the accumulator round trip another ~600), so throughput comes from tiles in flight, not from a
 // faster single chain.  Pipeline p: rows = its tile, TMEM columns [p*accw, (p+1)*accw), mbarrier p, named barrier 1+p.
-template <typename WT, int HID>
+template <typename WT, int HID, bool GACT>
 __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
                                                     const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, uint32_t accw,
                                                     const int *__restrict__ limit) {
@@ -256,7 +323,7 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
             fence_after_sync();
             constexpr int CW = HID < 32 ? HID : 32;  // 1024 threads per CTA: <= 64 registers, drain 32 columns at a time
 #pragma unroll
-            for (int c0 = 0; c0 < HID; c0 += CW) epi_relu_to_tile<CW>(trow, sa, row, c0);
+            for (int c0 = 0; c0 < HID; c0 += CW) epi_relu_to_tile<CW>(trow, sa, row, c0, GACT ? m.act : 0u);
             fence_proxy_async();
             fence_before_sync();
             pipe_sync(bid);
@@ -297,7 +364,7 @@ __host__ __device__ inline void make_bwd_cols(const mlp_t &m, bool calc_dx, bwd_
     c.total = o;
 }
 
-template <typename WT, int HID>
+template <typename WT, int HID, bool GACT>
 __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                    __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                    int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
@@ -373,7 +440,7 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
             mbar_wait(&s_bar, phase);
             phase ^= 1u;
             fence_after_sync();
-            epi_relu_to_tile<CW>(trow + tc.acc, sh + l * abytes, row, cg * CW);
+            epi_relu_to_tile<CW>(trow + tc.acc, sh + l * abytes, row, cg * CW, GACT ? m.act : 0u);
             fence_proxy_async();
             fence_before_sync();
             __syncthreads();
@@ -394,7 +461,7 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
             mbar_wait(&s_bar, phase);
             phase ^= 1u;
             fence_after_sync();
-            epi_mask_to_tile<CW>(trow + tc.acc, sh + (uint32_t)l * abytes, g, row, cg * CW);  // G_l = dH_l * (H_l > 0)
+            epi_mask_to_tile<CW>(trow + tc.acc, sh + (uint32_t)l * abytes, g, row, cg * CW, GACT ? m.act : 0u);  // G_l = dH_l * (H_l > 0)
             fence_proxy_async();
             fence_before_sync();
             __syncthreads();
@@ -492,7 +559,7 @@ __device__ unsigned g_trn[8];
 #define NGP_TR(slot, tag) do { } while (0)
 #endif
 
-template <typename WT, int HID>
+template <typename WT, int HID, bool GACT>
 __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                                __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                                int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
@@ -691,7 +758,7 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     phase ^= 1u;
                     fence_after_sync();
                     if (wp == 0) NGP_TR(2 + p, 0x400u | l);
-                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0);
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0, GACT ? m.act : 0u);
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
@@ -712,7 +779,7 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     fence_after_sync();
                     if (wp == 0) NGP_TR(2 + p, 0x600u | (uint32_t)l);
                     uint8_t *h = sh + (uint32_t)l * abytes;
-                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_mask_to_tile<STEP>(trow, h, h, row, c0);
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_mask_to_tile<STEP>(trow, h, h, row, c0, GACT ? m.act : 0u);
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
@@ -805,8 +872,8 @@ int check_dims(const char *fn, uint32_t in, uint32_t out, uint32_t hid, uint32_t
     NGP_CHECK_ARG(out > 0 && out % 16 == 0 && out <= 128, "%s: (padded) output_dim should be 16 * m, 0 < m <= 8, but got %u", fn, out);
     NGP_CHECK_ARG(nl >= 2 && nl <= kMaxLayers, "%s: num_layers should be in [2, %u], but got %u", fn, kMaxLayers, nl);
     NGP_CHECK_ARG(wdtype == NGP_DTYPE_F16 || wdtype == NGP_DTYPE_F32, "%s: weights must be a half or float tensor", fn);
-    if (act != 0 || out_act != 6) {
-        set_error("%s: only activation=ReLU (0) with output_activation=None (6) is implemented (got %u, %u)", fn, act, out_act);
+    if (act > 6 || out_act != 6) {
+        set_error("%s: activation must be one of the reference's codes 0..6 and output_activation None (6) (got %u, %u)", fn, act, out_act);
         return NGP_EUNSUPPORTED;
     }
     return NGP_OK;
@@ -826,6 +893,7 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     if (rc != NGP_OK) return rc;
     mlp_t m;
     make_mlp(m, B, in, out, hid, nl);
+    m.act = act;
     const size_t per_pipe = ((size_t)ktiles(in) + ktiles(hid)) * kActTileBytes;
     uint32_t accw = hid > out ? hid : out;
     accw = (accw + 31u) & ~31u;
@@ -845,10 +913,11 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     cudaStream_t st = (cudaStream_t)stream;
 #define NGP_FWD_CASE(WT_, HID_)                                                                                              \
     {                                                                                                                        \
-        rc = set_smem(k_ffmlp_fwd<WT_, HID_>, smem);                                                                         \
+        rc = m.act ? set_smem(k_ffmlp_fwd<WT_, HID_, true>, smem) : set_smem(k_ffmlp_fwd<WT_, HID_, false>, smem);               \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_fwd", st);                                                                                         \
-        k_ffmlp_fwd<WT_, HID_><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
+        if (m.act) k_ffmlp_fwd<WT_, HID_, true><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
+        else k_ffmlp_fwd<WT_, HID_, false><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
     }
 #define NGP_FWD_HID(WT_)                                         \
     switch (hid) {                                               \
@@ -905,6 +974,8 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
     cudaStream_t st = (cudaStream_t)stream;
     mlp_t m;
     make_mlp(m, B, input_dim, output_dim, hidden_dim, num_layers);
+    m.act = activation;
+    if (activation == 2) { set_error("%s: the Sine activation has no backward: its derivative needs the pre-activation, which is not kept (the reference's warp_activation_backward leaves it unimplemented too, utils.h:552-556)", fn); return NGP_EUNSUPPORTED; }
     if (B == 0) {  // empty batch: zero gradient
         NGP_CHECK_CUDA(cudaMemsetAsync(grad_weights, 0, (size_t)m.nweights * (grad_weights_dtype == NGP_DTYPE_F32 ? 4 : 2), st));
         return NGP_OK;
@@ -964,10 +1035,12 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();
 #define NGP_BWDMP_CASE(WT_, HID_)                                                                                            \
     {                                                                                                                        \
-        rc = set_smem(k_ffmlp_bwd_mp<WT_, HID_>, smem_mp);                                                                   \
+        rc = m.act ? set_smem(k_ffmlp_bwd_mp<WT_, HID_, true>, smem_mp) : set_smem(k_ffmlp_bwd_mp<WT_, HID_, false>, smem_mp);   \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd_mp", st);                                                                                      \
-        k_ffmlp_bwd_mp<WT_, HID_><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+        if (m.act) k_ffmlp_bwd_mp<WT_, HID_, true><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit());   \
+        else k_ffmlp_bwd_mp<WT_, HID_, false><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
                                                         (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit());   \
     }
 #define NGP_BWDMP_HID(WT_)                                         \
@@ -986,10 +1059,10 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
     }
 #define NGP_BWD_CASE(WT_, HID_)                                                                                              \
     {                                                                                                                        \
-        rc = set_smem(k_ffmlp_bwd<WT_, HID_>, smem);                                                                         \
+        rc = set_smem(k_ffmlp_bwd<WT_, HID_, true>, smem);                                                                         \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd", st);                                                                                         \
-        k_ffmlp_bwd<WT_, HID_><<<grid, 128 * split_of<HID_>::NS, smem, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+        k_ffmlp_bwd<WT_, HID_, true><<<grid, 128 * split_of<HID_>::NS, smem, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
                                                         (float *)workspace, grad_weights, gf32, m, ntiles, cols, calc_grad_inputs, nbuf, batch_limit());   \
     }
 #define NGP_BWD_HID(WT_)                                         \
