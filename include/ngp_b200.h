@@ -190,6 +190,10 @@ NGP_API int ngp_free_splitk(void);
  * lets the caller encode straight into a wider, padded MLP input). */
 NGP_API int ngp_sh_encode_forward(const float *inputs, void *outputs, uint32_t B, uint32_t degree, uint32_t out_stride,
                           int dtype, void *stream);
+/* sh_encode_backward (shencoder.cu:366-383 contracted with the dy_dx of :122-250 in one pass, no dy_dx buffer):
+ * grad [B, grad_stride] f32 (first degree^2 columns used), inputs [B,3] f32 -> grad_inputs [B,3] f32. */
+NGP_API int ngp_sh_encode_backward(const float *grad, const float *inputs, float *grad_inputs, uint32_t B, uint32_t degree,
+                           uint32_t grad_stride, void *stream);
 
 /* Renderer-driver glue (scope table "next" row 1: nerf/renderer.py:257-431 run_cuda, :498-598 update_extra_state;
  * network nerf/network_ff.py:51-74; optimizer step main_nerf.py:194-197 + nerf/utils.py:974-978).  All device

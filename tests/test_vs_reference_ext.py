@@ -267,3 +267,26 @@ def test_sh_encoder_vs_reference():
         out = torch.empty(B, degree ** 2, device=DEV)
         abi.check(abi.lib.ngp_sh_encode_forward(d.data_ptr(), out.data_ptr(), B, degree, degree ** 2, abi.DTYPE_F32, abi.stream()))
         assert torch.allclose(out, out_r, rtol=1e-6, atol=1e-7)
+        # gradients w.r.t. the directions: the reference's dy_dx + kernel_sh_backward vs the fused backward
+        dy_dx = torch.empty(B, degree ** 2 * 3, device=DEV)
+        ref.sh_encode_forward(d, out_r, B, 3, degree, dy_dx)
+        g = torch.randn(B, degree ** 2, device=DEV)
+        gi_r = torch.zeros_like(d)
+        ref.sh_encode_backward(g, d, B, 3, degree, dy_dx, gi_r)
+        gi = torch.empty_like(d)
+        abi.check(abi.lib.ngp_sh_encode_backward(g.data_ptr(), d.data_ptr(), gi.data_ptr(), B, degree, degree ** 2, abi.stream()))
+        assert torch.allclose(gi, gi_r, rtol=1e-5, atol=1e-5), (degree, float((gi - gi_r).abs().max()))
+    # module level: autograd through SHEncoder against autograd through the polynomial written in torch
+    import shencoder
+    dd = d[:512].clone().requires_grad_(True)
+    y = shencoder.SHEncoder(degree=4)(dd)
+    w = torch.randn_like(y)
+    (y * w).sum().backward()
+    x_, y_, z_ = (d[:512, i].clone().requires_grad_(True) for i in range(3))
+    poly = torch.stack([0.3731763325901154 * z_ * (5 * z_ * z_ - 3), 2.8906114426405538 * x_ * y_ * z_, 1.4453057213202769 * z_ * (x_ * x_ - y_ * y_)], -1)
+    (poly * w[:, [12, 10, 14]]).sum().backward()
+    w2 = w.clone(); w2[:, [12, 10, 14]] = 0
+    dd2 = d[:512].clone().requires_grad_(True)
+    (shencoder.SHEncoder(degree=4)(dd2) * w2).sum().backward()
+    part = dd.grad - dd2.grad  # contribution of coefficients 10, 12, 14 alone
+    assert torch.allclose(part, torch.stack([x_.grad, y_.grad, z_.grad], -1), rtol=1e-4, atol=1e-5)
