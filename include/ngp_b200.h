@@ -223,6 +223,11 @@ NGP_API int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t 
 NGP_API int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
                   const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream);
 NGP_API int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream);
+/* get_rays (nerf/utils.py:52-136) after the pixel indices are chosen: poses [B,4,4] f32 camera-to-world, intrinsics,
+ * image width W; inds: pixel indices (row-major, j * W + i) [N] for all poses (inds_stride 0), [B,N] (inds_stride N) or
+ * NULL (= 0..N-1, every pixel); rays_o, rays_d [B,N,3] f32, directions normalised in camera space then rotated. */
+NGP_API int ngp_get_rays(const float *poses, uint32_t B, float fx, float fy, float cx, float cy, uint32_t W, const int *inds,
+                 uint32_t inds_stride, uint32_t N, float *rays_o, float *rays_d, void *stream);
 /* grid = max(grid*decay, tmp) where both >= 0; *sum_out = sum(clamp(grid, 0)) */
 NGP_API int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, float *sum_out, void *stream);
 /* packbits with thresh = min(*sum * inv_count, density_thresh) read on the device; N = output bytes (N % 4 == 0) */

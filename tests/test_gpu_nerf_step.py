@@ -302,3 +302,45 @@ def test_inference_render_matches_training_quadrature_and_band_sharding():
         assert (a - img1).abs().max() < 2e-3 and (b - depth1).abs().max() < 2e-3, (kw, float((a - img1).abs().max()), float((b - depth1).abs().max()))
     tr.render(ro, rd)
     assert tr.last_render_iters < ref_iters
+
+
+def test_get_rays_matches_reference_construction():
+    """nerf.get_rays (index selection in torch, ray construction in one kernel) against nerf/utils.py:69-134 transcribed."""
+    import nerf
+    from test_oracle import _orbit_poses
+    poses = torch.from_numpy(_orbit_poses(5)).cuda()
+    H, W = 60, 80
+    intr = (70.0, 65.0, 39.5, 30.25)
+
+    def ref(poses, inds):  # utils.py:69-71, 118-134
+        B = poses.shape[0]
+        fx, fy, cx, cy = intr
+        i, j = torch.meshgrid(torch.linspace(0, W - 1, W, device="cuda"), torch.linspace(0, H - 1, H, device="cuda"), indexing="ij")
+        i = i.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
+        j = j.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
+        if inds is not None:
+            i, j = torch.gather(i, -1, inds), torch.gather(j, -1, inds)
+        zs = torch.ones_like(i)
+        d = torch.stack(((i - cx) / fx * zs, (j - cy) / fy * zs, zs), dim=-1)
+        d = d / torch.norm(d, dim=-1, keepdim=True)
+        rays_d = d @ poses[:, :3, :3].transpose(-1, -2)
+        rays_o = poses[..., :3, 3][..., None, :].expand_as(rays_d)
+        return rays_o, rays_d
+
+    full = nerf.get_rays(poses, intr, H, W, -1)
+    ro, rd = ref(poses, None)
+    assert full["rays_o"].shape == (5, H * W, 3) and torch.equal(full["rays_o"], ro.contiguous())
+    assert torch.allclose(full["rays_d"], rd, rtol=0, atol=2e-7)
+    torch.manual_seed(3)
+    some = nerf.get_rays(poses, intr, H, W, 1000)
+    assert some["inds"].shape == (5, 1000) and int(some["inds"].max()) < H * W
+    ro, rd = ref(poses, some["inds"])
+    assert torch.allclose(some["rays_d"], rd, rtol=0, atol=2e-7) and torch.equal(some["rays_o"], ro.contiguous())
+    err = torch.rand(5, 128 * 128, device="cuda")
+    em = nerf.get_rays(poses, intr, H, W, 500, error_map=err)
+    ro, rd = ref(poses, em["inds"])
+    assert em["inds_coarse"].shape == (5, 500) and torch.allclose(em["rays_d"], rd, rtol=0, atol=2e-7)
+    pt = nerf.get_rays(poses[:1], intr, H, W, 64, patch_size=4)
+    assert pt["rays_d"].shape == (1, 64, 3)
+    ro, rd = ref(poses[:1], pt["inds"])
+    assert torch.allclose(pt["rays_d"], rd, rtol=0, atol=2e-7)

@@ -273,6 +273,29 @@ __global__ void __launch_bounds__(256) k_cast_f16(const float4 *__restrict__ src
     dst[i] = make_uint2(h2(v.x, v.y), h2(v.z, v.w));
 }
 
+// ---- ray generation (nerf/utils.py:52-136 get_rays, the part after the pixel indices are chosen) ---------------------
+// One thread per ray of pose blockIdx.y: pixel centre -> camera direction ((i - cx)/fx, (j - cy)/fy, 1) normalised ->
+// world direction (directions @ R^T), origin = camera position.  inds: pixel indices [N] shared by all poses
+// (inds_stride = 0), [B, N] (inds_stride = N), or NULL = every pixel in row-major order.
+__global__ void __launch_bounds__(256) k_get_rays(const float *__restrict__ poses, float fx, float fy, float cx, float cy, uint32_t W,
+                                                  const int *__restrict__ inds, uint32_t inds_stride, uint32_t N, float *__restrict__ rays_o,
+                                                  float *__restrict__ rays_d) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (n >= N) return;
+    const float *P = poses + (size_t)b * 16;
+    const uint32_t pix = inds ? (uint32_t)inds[(size_t)b * inds_stride + n] : n;
+    const float i = (float)(pix % W) + 0.5f, j = (float)(pix / W) + 0.5f;
+    const float xs = __fdiv_rn(__fsub_rn(i, cx), fx), ys = __fdiv_rn(__fsub_rn(j, cy), fy);
+    const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(xs, xs), __fmul_rn(ys, ys)), 1.0f));
+    const float dx = __fdiv_rn(xs, nrm), dy = __fdiv_rn(ys, nrm), dz = __fdiv_rn(1.0f, nrm);
+    const size_t o = ((size_t)b * N + n) * 3;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        rays_d[o + k] = __fadd_rn(__fadd_rn(__fmul_rn(dx, P[4 * k]), __fmul_rn(dy, P[4 * k + 1])), __fmul_rn(dz, P[4 * k + 2]));
+        rays_o[o + k] = P[4 * k + 3];
+    }
+}
+
 // ---- density grid maintenance (nerf/renderer.py:498-598) ----------------------------------------------------
 // grid = max(grid * decay, tmp) where both >= 0 ; partial sums of clamp(grid, 0) -> mean density
 __global__ void __launch_bounds__(256) k_density_ema(float *__restrict__ grid, const float *__restrict__ tmp, float decay, uint32_t n,
@@ -442,6 +465,18 @@ int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream) {
     NGP_CHECK_ARG(src && dst && n % 4 == 0, "cast_f16: null pointer argument or n not a multiple of 4");
     cudaStream_t st = (cudaStream_t)stream;
     { NGP_PROF("k_cast_f16", st); k_cast_f16<<<(uint32_t)((n / 4 + 255) / 256), 256, 0, st>>>((const float4 *)src, (uint2 *)dst, n / 4); }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
+int ngp_get_rays(const float *poses, uint32_t B, float fx, float fy, float cx, float cy, uint32_t W, const int *inds, uint32_t inds_stride,
+                 uint32_t N, float *rays_o, float *rays_d, void *stream) {
+    using namespace ngp;
+    if (B == 0 || N == 0) return NGP_OK;
+    NGP_CHECK_ARG(poses && rays_o && rays_d, "get_rays: null pointer argument");
+    NGP_CHECK_ARG(W > 0 && fx != 0.f && fy != 0.f && B <= 65535, "get_rays: bad image width / focal length / pose count");
+    cudaStream_t st = (cudaStream_t)stream;
+    { NGP_PROF("k_get_rays", st); k_get_rays<<<dim3(div_round_up(N, 256u), B, 1), 256, 0, st>>>(poses, fx, fy, cx, cy, W, inds, inds_stride, N, rays_o, rays_d); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

@@ -54,6 +54,7 @@ SIGNATURES = {
     "ngp_allocate_splitk": (_int, [_sz]),
     "ngp_free_splitk": (_int, []),
     "ngp_sh_encode_forward": (_int, [_vp, _vp, _u32, _u32, _u32, _int, _vp]),
+    "ngp_get_rays": (_int, [_vp, _u32, _f32, _f32, _f32, _f32, _u32, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ngp_sh_encode_backward": (_int, [_vp, _vp, _vp, _u32, _u32, _u32, _vp]),
     "ngp_nerf_x01": (_int, [_vp, _f32, _vp, _u32, _vp]),
     "ngp_nerf_mid_forward": (_int, [_vp, _vp, _f32, _vp, _vp, _u32, _vp]),
