@@ -344,3 +344,31 @@ def test_get_rays_matches_reference_construction():
     assert pt["rays_d"].shape == (1, 64, 3)
     ro, rd = ref(poses[:1], pt["inds"])
     assert torch.allclose(pt["rays_d"], rd, rtol=0, atol=2e-7)
+
+
+def test_checkpoint_round_trip_in_the_reference_layout(tmp_path):
+    """save_checkpoint / load_checkpoint: the reference's keys, and a restored trainer continues bit-for-bit like the
+    original where the step is deterministic (everything but the fp16 table-gradient atomics)."""
+    import nerf
+    tr = _make(num_rays=1024, graph=False, perturb=False, update_interval=0)
+    tr.update_extra_state()
+    for _ in range(3):
+        tr.next_pool_batch(); tr.train_step()
+    path = str(tmp_path / "ngp.pth")
+    tr.save_checkpoint(path)
+    ck = torch.load(path)
+    assert {"model", "mean_count", "mean_density", "global_step"} <= set(ck)
+    assert {"encoder.embeddings", "encoder.offsets", "sigma_net.weights", "color_net.weights", "density_grid", "density_bitfield",
+            "step_counter", "aabb_train", "aabb_infer"} == set(ck["model"])
+    tr2 = _make(num_rays=1024, graph=False, perturb=False, update_interval=0)
+    tr2.load_checkpoint(path)
+    assert torch.equal(tr2.params, tr.params) and torch.equal(tr2.table16, tr.table16) and torch.equal(tr2.exp_avg, tr.exp_avg)
+    assert torch.equal(tr2.density_bitfield, tr.density_bitfield) and torch.equal(tr2.state, tr.state) and tr2.global_step == tr.global_step
+    # the twin module of the reference topology loads the same state dict
+    net = nerf.NeRFNetwork(bound=tr.bound, log2_hashmap_size=17).cuda()
+    missing, unexpected = net.load_state_dict({k: v for k, v in ck["model"].items()}, strict=False)
+    assert not [k for k in missing if k.split(".")[0] in ("encoder", "sigma_net", "color_net")], missing
+    ro, rd = tr._pool[0][:256], tr._pool[1][:256]
+    a, _ = tr.render(ro, rd)
+    b, _ = tr2.render(ro, rd)
+    assert torch.equal(a, b)

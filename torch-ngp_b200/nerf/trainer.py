@@ -453,6 +453,64 @@ class NGPTrainer:
     def mean_density(self):
         return float(self.mean_sum.item()) / self.density_grid.numel()
 
+    # ---- checkpoints in the reference's layout (nerf/utils.py:1175-1311, state-dict names of network_ff.NeRFNetwork) ----
+    def state_dict(self):
+        """Model state with the names the reference's NeRFNetwork(--ff) registers: encoder.embeddings / encoder.offsets
+        (gridencoder/grid.py:787-798), sigma_net.weights / color_net.weights (ffmlp.py:121-122), and the renderer buffers
+        aabb_train, aabb_infer, density_grid, density_bitfield, step_counter (renderer.py:85-100)."""
+        self.flush()
+        return {
+            "encoder.embeddings": self.embeddings.detach().clone(), "encoder.offsets": self.offsets.detach().clone(),
+            "sigma_net.weights": self.sigma_w.detach().clone(), "color_net.weights": self.color_w.detach().clone(),
+            "aabb_train": self.aabb.clone(), "aabb_infer": self.aabb.clone(), "density_grid": self.density_grid.clone(),
+            "density_bitfield": self.density_bitfield.clone(), "step_counter": self.step_counter.clone(),
+        }
+
+    @torch.no_grad()
+    def load_state_dict(self, sd, strict=True):
+        """Inverse of state_dict(); also accepts a state dict written by the reference.  Returns (missing, unexpected)."""
+        self.flush()
+        mine = {"encoder.embeddings": self.embeddings, "sigma_net.weights": self.sigma_w, "color_net.weights": self.color_w,
+                "density_grid": self.density_grid, "density_bitfield": self.density_bitfield, "step_counter": self.step_counter}
+        known = set(mine) | {"encoder.offsets", "aabb_train", "aabb_infer"}
+        missing = [k for k in mine if k not in sd]
+        unexpected = [k for k in sd if k not in known]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"load_state_dict: missing {missing}, unexpected {unexpected}")
+        if "encoder.offsets" in sd and not torch.equal(sd["encoder.offsets"].cpu().int(), self.offsets.cpu().int()):
+            raise RuntimeError("load_state_dict: the checkpoint's hash-grid level offsets differ from this trainer's configuration")
+        for k, dst in mine.items():
+            if k in sd:
+                src = sd[k]
+                if src.numel() != dst.numel():
+                    raise RuntimeError(f"load_state_dict: size mismatch for {k}: {tuple(src.shape)} vs {tuple(dst.shape)}")
+                dst.copy_(src.to(dst.device, dst.dtype).view_as(dst))
+        _ck(abi.lib.ngp_cast_f16(self.params.data_ptr(), self.table16.data_ptr(), self.n16, abi.stream()))  # fp16 shadow of the table
+        return missing, unexpected
+
+    def save_checkpoint(self, path, full=True):
+        """{'model', 'mean_count', 'mean_density', 'global_step'} as Trainer.save_checkpoint writes them (utils.py:1180-1199);
+        full adds this trainer's optimizer state (Adam moments, step / loss-scale state) under 'optimizer_b200'."""
+        state = {"global_step": self.global_step, "mean_count": self.mean_count, "mean_density": self.mean_density(), "model": self.state_dict()}
+        if full:
+            state["optimizer_b200"] = {"exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(), "state": self.state.clone(),
+                                       "iter_density": self.iter_density, "local_step": self.local_step}
+        torch.save(state, path)
+
+    def load_checkpoint(self, path, model_only=False):
+        ck = torch.load(path, map_location=self.dev)
+        if "model" not in ck:  # a bare state dict (utils.py:1249-1252)
+            self.load_state_dict(ck, strict=False)
+            return
+        self.load_state_dict(ck["model"], strict=False)
+        if "mean_count" in ck:
+            self.mean_count = ck["mean_count"]
+        self.global_step = ck.get("global_step", self.global_step)
+        if not model_only and "optimizer_b200" in ck:
+            o = ck["optimizer_b200"]
+            self.exp_avg.copy_(o["exp_avg"]); self.exp_avg_sq.copy_(o["exp_avg_sq"]); self.state.copy_(o["state"])
+            self.iter_density, self.local_step = o["iter_density"], o["local_step"]
+
     # ---- inference rendering (nerf/renderer.py:346-431, the `not self.training` branch of run_cuda) ----------------
     def _render_state(self, N, rows):
         """Buffers of the render loop for N rays and at most `rows` samples per iteration, allocated once and kept (a frame
