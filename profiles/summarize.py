@@ -34,7 +34,7 @@ def launches(csv_path, bench_json, out_md, title="training step"):
     steps = bench["steps"]
     # the timed region and the per-kernel profile pass are the last 2*steps steps of the run: count launches of the
     # once-per-step first kernel backwards to find where they start
-    marker = "k_near_far" if any(n.startswith("k_near_far") for _, n, _ in rows) else "k_step_begin"  # first kernel of a step
+    marker = next((m for m in ("k_near_far", "k_step_begin", "k_grid_fwd") if any(n.startswith(m) for _, n, _ in rows)), None)  # first kernel of a step
     begins = [i for i, (_, n, _) in enumerate(rows) if n.startswith(marker)]
     first = begins[-2 * steps] if len(begins) >= 2 * steps else begins[0]
     nsteps = len([b for b in begins if b >= first])
