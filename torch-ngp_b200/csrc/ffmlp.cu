@@ -1022,6 +1022,9 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (ns_opt == 1 || ns_opt == 2) ns = (uint32_t)ns_opt;
         if (hidden_dim / ns < 32 && hidden_dim >= 32) ns = hidden_dim / 32;
         if (hidden_dim < 32) ns = 1;
+        // tiles in flight beat threads per tile: when one thread per row lets a fourth pipeline fit (shared memory and TMEM
+        // permitting), take it (measured, sigma net 32->64x2->16 at 590 k rows: 4 x 128 threads 89 us, 3 x 256 threads 98 us)
+        if (ns_opt == 0 && ns == 2 && np >= 4) ns = 1;
         if (np * ns > 6) np = 6 / ns;
         const uint32_t per_cta_need = div_round_up(ntiles, (uint32_t)sm_count());
         if (variant != 1 && np > per_cta_need) np = per_cta_need;  // forced (tests): as many pipelines as fit, whatever the batch
