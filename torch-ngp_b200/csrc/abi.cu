@@ -32,6 +32,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
         {"hashgrid_bwd_red4", 2},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours: 0 never, 1 always, 2 when the lanes of a warp do not share groups (random points)
         {"ffmlp_ablate", 0},           // timing experiments only (results are wrong): 1 skip the weight-gradient MMAs, 2 skip the layer MMAs, 3 both
+        {"march_rays_warp", 32768},    // inference marcher: one warp per alive ray while n_alive <= this (0 = always one thread per ray, the reference's mapping)
         {"adam_blocks_per_sm", 0},     // k_adam grid cap (0 = one block per 1024 parameters); NGPTrainer sets it when the optimizer shares the SMs with the marcher
         {"hashgrid_bwd_smem_coarse", 0},  // v3 backward: accumulate the levels that fit in shared memory (unordered points: SDF, configs[0])
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)

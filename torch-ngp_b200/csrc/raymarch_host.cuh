@@ -188,9 +188,17 @@ int ngp_march_rays(uint32_t n_alive, const int *n_alive_dev, uint32_t n_step, co
     NGP_CHECK_ARG(rays_alive && rays_t && rays_o && rays_d && grid && fars && xyzs && dirs && deltas && noises,
                   "march_rays: null pointer argument");
     NGP_CHECK_ARG(aligned(deltas, 8), "march_rays: deltas must be 8-byte aligned");
-    { NGP_PROF("k_march_rays", (cudaStream_t)stream); k_march_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, rays_alive, rays_t, rays_o,
-                                                                               rays_d, bound, dt_gamma, max_steps, C, H, grid, fars,
-                                                                               xyzs, dirs, deltas, noises); }
+    // one warp per ray pays off once the launch no longer fills the GPU with threads (option = largest n_alive it is used for; 0 = never)
+    if (n_alive <= (uint32_t)get_option("march_rays_warp", 32768)) {
+        NGP_PROF("k_march_rays_warp", (cudaStream_t)stream);
+        k_march_rays_warp<<<div_round_up(n_alive, (uint32_t)kWarpRays), kWarpRays * 32, 0, (cudaStream_t)stream>>>(
+            n_alive, n_alive_dev, n_step, rays_alive, rays_t, rays_o, rays_d, bound, dt_gamma, max_steps, C, H, grid, fars, xyzs, dirs, deltas, noises);
+    } else {
+        NGP_PROF("k_march_rays", (cudaStream_t)stream);
+        k_march_rays<<<div_round_up(n_alive, 128u), 128, 0, (cudaStream_t)stream>>>(n_alive, n_alive_dev, n_step, rays_alive, rays_t, rays_o,
+                                                                                    rays_d, bound, dt_gamma, max_steps, C, H, grid, fars,
+                                                                                    xyzs, dirs, deltas, noises);
+    }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }

@@ -39,6 +39,28 @@ __global__ void __launch_bounds__(128) k_march_rays(uint32_t n_alive, const int 
     }
 }
 
+// The same op with one WARP per alive ray (march_ray_warp of the training marcher: 32 consecutive t values tested in
+// parallel, skip rule replayed on ballots -- samples bit-identical to the loop above).  A thread of the kernel above walks
+// its ray alone, one dependent bitfield load per visited voxel; that is the whole cost of the first loop iteration of a
+// frame (every ray crosses empty space to its first hit) and of the late iterations (few rays, up to 64 samples each).
+__global__ void __launch_bounds__(kWarpRays * 32) k_march_rays_warp(uint32_t n_alive, const int *__restrict__ n_alive_dev, uint32_t n_step,
+                                                                     const int *__restrict__ rays_alive, const float *__restrict__ rays_t,
+                                                                     const float *__restrict__ rays_o, const float *__restrict__ rays_d, float bound,
+                                                                     float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t H,
+                                                                     const uint8_t *__restrict__ grid, const float *__restrict__ fars,
+                                                                     float *__restrict__ xyzs, float *__restrict__ dirs, float *__restrict__ deltas,
+                                                                     const float *__restrict__ noises) {
+    const uint32_t n = blockIdx.x * kWarpRays + (threadIdx.x >> 5);
+    if (n_alive_dev) n_alive = min(n_alive, (uint32_t)max(*n_alive_dev, 0));
+    if (n >= n_alive) return;  // whole warps leave together
+    const int index = rays_alive[n];
+    const march_consts_t c = make_consts(bound, dt_gamma, max_steps, C, H, grid);
+    const ray_t r = load_ray(rays_o, rays_d, (uint32_t)index);
+    float t = rays_t[index];
+    t = __fmaf_rn(clampf(__fmul_rn(t, c.dt_gamma), c.dt_min, c.dt_max), noises[n], t);  // :755
+    march_ray_warp<true>(r, c, t, fars[index], n_step, xyzs + 3 * (size_t)n * n_step, dirs + 3 * (size_t)n * n_step, deltas + 2 * (size_t)n * n_step);
+}
+
 // reference :827-914
 __global__ void __launch_bounds__(128) k_composite_rays(uint32_t n_alive, const int *__restrict__ n_alive_dev, uint32_t n_step,
                                                         float T_thresh, int *__restrict__ rays_alive, float *__restrict__ rays_t,
