@@ -52,28 +52,45 @@ extern "C" {
 
 NGP_API const char *ngp_last_error(void);
 NGP_API int ngp_abi_version(void);
-/* Tuning knobs used by bench/tests (e.g. "hashgrid_fwd_variant"); unknown keys -> NGP_EINVAL. */
+/* Development knobs used by bench/tests to A/B kernel VARIANTS that compute the same results (e.g. "hashgrid_fwd_variant",
+ * "march_variant") and to switch the per-launch event profile on; unknown keys -> NGP_EINVAL.  Nothing that changes
+ * what a call computes or which rows it touches lives here: that is ngp_call_opts, passed with each call. */
 NGP_API int ngp_set_option(const char *key, int value);
 NGP_API int ngp_get_option(const char *key, int *value);
 /* Launch accounting: total kernel launches made by the library in this process, and -- while option
  * "profile_events" is 1 (not during CUDA-graph capture) -- per-kernel CUDA-event durations, returned as
  * text lines "<kernel> <count> <total_ms>\n" (the call synchronises on the recorded events and clears them). */
 NGP_API long long ngp_launch_count(void);
-/* Device-side batch size for the per-sample ops.  While a non-NULL pointer is set (process-wide: autograd calls the
- * backward ops from its own threads), the kernels of
- * ngp_grid_encode_forward / _backward, ngp_ffmlp_forward / _inference / _backward and the ngp_nerf_* glue process only the first min(B, *count_dev) rows; *count_dev is read ON THE DEVICE when the kernel runs, so
- * the sample counter that ngp_march_rays_train just wrote (counter[0]) can bound the rest of a captured step without a
- * host read-back.  Rows past the limit are neither read nor written.  The reference sizes these launches from a host
- * copy of the counter (raymarching.py:221-226, a D2H sync) or from a running mean (padded work).  NULL clears it. */
-NGP_API int ngp_set_batch_limit(const int32_t *count_dev);
+/* Per-call options of the per-sample entry points (the trailing `const ngp_call_opts *opts` argument; NULL = defaults).
+ * There is NO process-wide state behind these: every call carries its own, so modules, threads and streams never see
+ * each other's settings (two trainers and a bare GridEncoder may run concurrently).  The struct is read on the host
+ * while the call enqueues its kernels; it may live on the caller's stack.
+ *   batch_limit : device int32 (or NULL).  The kernels of the call process only the first min(B, *batch_limit) rows;
+ *                 *batch_limit is read ON THE DEVICE when the kernel runs, so the sample counter that
+ *                 ngp_march_rays_train just wrote (counter[0]) bounds the rest of a captured step without a host
+ *                 read-back.  Rows past the limit are neither read nor written; strides keep using B.  The reference
+ *                 sizes these launches from a host copy of the counter (raymarching.py:221-226, a D2H sync).
+ *   input_bound : > 0: `inputs` of ngp_grid_encode_forward / _backward are positions in [-bound, bound]^3 and the
+ *                 kernels apply the module's own mapping (x + bound) / (2 bound) (gridencoder/grid.py:807) as they
+ *                 load them (D = 3, C = 2 fast kernels only: NGP_EUNSUPPORTED otherwise).  <= 0: inputs in [0, 1].
+ *   flags       : NGP_OPT_* below.
+ *   grid_cap_blocks_per_sm : > 0 caps the grid of ngp_adam_step at that many blocks per SM (grid-stride), so that the
+ *                 HBM-bound optimizer can share the SMs with another stream's kernels; 0 = one block per 1024 items. */
+typedef struct ngp_call_opts {
+    const int32_t *batch_limit;
+    float input_bound;
+    uint32_t flags;
+    int32_t grid_cap_blocks_per_sm;
+} ngp_call_opts;
+/* dy_dx of ngp_grid_encode_forward with linear interpolation: the reference initialises `float pos_deriv[D] = {1.0f}`
+ * (gridencoder.cu:143), i.e. only d = 0 gets a non-zero input derivative.  DEFAULT = the reference's values, bit for
+ * bit.  This flag selects the mathematically exact derivative (all D components) instead. */
+#define NGP_OPT_EXACT_INPUT_GRAD 1u
+/* ngp_grid_encode_backward: accumulate the levels that fit in shared memory there (fp32, one flush per block) instead
+ * of reducing them in L2 -- for UNORDERED points (SDF batches, random points), where every point lands in one of a few
+ * thousand coarse cells.  Same sums up to addition order. */
+#define NGP_OPT_GRID_BWD_SMEM_COARSE 2u
 NGP_API int ngp_profile_collect(char *buf, size_t buf_bytes);
-
-/* Input range of ngp_grid_encode_forward / _backward.  While bound > 0 (process-wide, like the batch limit), `inputs`
- * are positions in [-bound, bound]^3 and the kernels apply the module's own mapping (x + bound) / (2 bound)
- * (gridencoder/grid.py:807) as they load them -- one pass over the samples less for a caller that owns its buffers
- * (NGPTrainer).  D = 3, C = 2 fast kernels only: any other configuration returns NGP_EUNSUPPORTED while it is set.
- * bound <= 0 restores the default (inputs already in [0, 1]). */
-NGP_API int ngp_set_input_bound(float bound);
 
 /* ---------------------------------------------------------------------------------------------
  * gridencoder  (replaces gridencoder.h:12-15)
@@ -85,13 +102,13 @@ NGP_API int ngp_set_input_bound(float bound);
  * D in {2,3,4,5}, C in {1,2,4,8} ("GridEncoding: C must be 1, 2, 4, or 8." otherwise). */
 NGP_API int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const int *offsets, const int *offsets_host,
                             void *outputs, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
-                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream);
+                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream, const ngp_call_opts *opts);
 /* grid_encode_backward (gridencoder.cu:470-500).  grad dtype in `layout`; grad_embeddings [T,C] dtype,
  * ACCUMULATED into (caller zero-fills, grid.py:89); dy_dx/grad_inputs ([B,D] dtype) both NULL or both set. */
 NGP_API int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int *offsets,
                              const int *offsets_host, void *grad_embeddings, uint32_t B, uint32_t D, uint32_t C, uint32_t L,
                              float S, uint32_t H, const void *dy_dx, void *grad_inputs, uint32_t gridtype, int align_corners,
-                             uint32_t interp, int dtype, int layout, void *stream);
+                             uint32_t interp, int dtype, int layout, void *stream, const ngp_call_opts *opts);
 /* grad_total_variation (gridencoder.cu:636-642).  inputs [B,D] in the TABLE dtype (sic, :505). */
 NGP_API int ngp_grad_total_variation(const void *inputs, const void *embeddings, void *grad, const int *offsets,
                              float weight, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
@@ -157,17 +174,19 @@ NGP_API int ngp_compact_alive(const int *in, uint32_t n, const int *n_dev, int *
  * row-major [out, in] (ffmlp.cu:631-634), fp16 or fp32 (`weights_dtype`; fp32 is rounded to fp16 while
  * staged into shared memory).  Any B >= 0 (the ragged tail tile is masked; FFMLP.forward's padding copy,
  * ffmlp.py:157-159, is not needed).  hidden_dim in {16,32,64,128}, input_dim % 16 == 0 (<= 128),
- * output_dim % 16 == 0 (<= 128), num_layers >= 2 (num_layers + 1 matmuls), activation 0 = ReLU,
- * output_activation 6 = None (all that FFMLP ever passes, ffmlp.py:107-108); anything else -> NGP_EUNSUPPORTED.
+ * output_dim % 16 == 0 (<= 128), num_layers >= 2 (num_layers + 1 matmuls), activation = any of the reference's
+ * codes 0..6 (ffmlp.cu:22-32: ReLU, Exponential, Sine, Sigmoid, Squareplus, Softplus, None; Sine has no backward, as
+ * in the reference, utils.h:552-556), output_activation 6 = None (all that FFMLP ever passes, ffmlp.py:107-108);
+ * anything else -> NGP_EUNSUPPORTED.
  * forward_buffer / inference_buffer / backward_buffer are accepted for signature compatibility and may be
  * NULL: they are never written (activations live in shared memory; the backward recomputes the forward).
  * ------------------------------------------------------------------------------------------- */
 NGP_API int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim,
                       uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
-                      uint32_t output_activation, void *forward_buffer, void *outputs, void *stream);
+                      uint32_t output_activation, void *forward_buffer, void *outputs, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_ffmlp_inference(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim,
                         uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
-                        uint32_t output_activation, void *inference_buffer, void *outputs, void *stream);
+                        uint32_t output_activation, void *inference_buffer, void *outputs, void *stream, const ngp_call_opts *opts);
 /* grad_weights: fp16 like the reference (NGP_DTYPE_F16) or fp32 (NGP_DTYPE_F32); OVERWRITTEN, not accumulated.
  * grad_inputs [B, input_dim] fp16, written iff calc_grad_inputs.  workspace: ngp_ffmlp_backward_workspace_bytes()
  * bytes, zero-initialised once by the caller; the kernel leaves it zeroed for the next call. */
@@ -175,7 +194,7 @@ NGP_API int ngp_ffmlp_backward(const void *grad, const void *inputs, const void 
                        const void *forward_buffer, uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
                        uint32_t num_layers, uint32_t activation, uint32_t output_activation, int calc_grad_inputs,
                        void *backward_buffer, void *grad_inputs, void *grad_weights, int grad_weights_dtype, void *workspace,
-                       size_t workspace_bytes, void *stream);
+                       size_t workspace_bytes, void *stream, const ngp_call_opts *opts);
 NGP_API size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
                                           uint32_t num_layers);
 /* The reference's process-global split-k stream pool (ffmlp.cu:711-740) has no equivalent: no-ops. */
@@ -199,20 +218,20 @@ NGP_API int ngp_sh_encode_backward(const float *grad, const float *inputs, float
  * network nerf/network_ff.py:51-74; optimizer step main_nerf.py:194-197 + nerf/utils.py:974-978).  All device
  * resident, no host reads; `state` is a float[16] device block (see nerf_step.cu) holding step count, lr, bias
  * corrections, loss scale, found_inf flag and the loss accumulator. */
-NGP_API int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *stream);
+NGP_API int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *stream, const ngp_call_opts *opts);
 /* h [M,16] f16, dirs [M,3] -> sigmas [M] f32 = density_scale*exp(h0); cin [M,32] f16 = [SH4(dir) | h1..h15 | 0] */
-NGP_API int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, float *sigmas, void *cin, uint32_t M, void *stream);
+NGP_API int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, float *sigmas, void *cin, uint32_t M, void *stream, const ngp_call_opts *opts);
 /* c [M,16] f16 -> rgbs [M,3] f32 = sigmoid(c0..c2) */
-NGP_API int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream);
+NGP_API int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream, const ngp_call_opts *opts);
 /* MSE loss of image + (1 - weights_sum) * bg against gt [N,3]; loss accumulated into *loss_out; gradients scaled by *loss_scale */
 NGP_API int ngp_nerf_loss(const float *image, const float *weights_sum, const float *gt, float bg, uint32_t N, const float *loss_scale,
                   float *grad_image, float *grad_weights_sum, float *grad_depth, float *loss_out, void *stream);
-NGP_API int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream);
+NGP_API int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *grad_cin, float density_scale, void *grad_h,
-                          uint32_t M, void *stream);
+                          uint32_t M, void *stream, const ngp_call_opts *opts);
 /* SDF regression loss (sdf/utils.py:217-225, loss.py:7-15 mape_loss, mean over B): h [B,16] f16 (column 0 = prediction),
  * target [B] f32 -> *loss_out += loss, grad_h [B,16] f16 (scaled by *loss_scale) */
-NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream);
+NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_step_begin(float *state, float beta1, float beta2, void *stream);
 NGP_API int ngp_step_end(float *state, void *stream);
 /* sets state.found_inf when any gradient is inf/nan: g16 = n16 halves (n16 % 8 == 0), g32 = n32 floats (n32 % 4 == 0) */
@@ -221,7 +240,7 @@ NGP_API int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t 
  * divided by (loss scale * grad_div), consumed and CLEARED; skipped (but still cleared) when state.found_inf;
  * weight_decay32: torch.optim.Adam's L2 weight decay for the fp32-gradient group (main_sdf.py:51-54), 0 for NeRF */
 NGP_API int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
-                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream);
+                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream);
 /* get_rays (nerf/utils.py:52-136) after the pixel indices are chosen: poses [B,4,4] f32 camera-to-world, intrinsics,
  * image width W; inds: pixel indices (row-major, j * W + i) [N] for all poses (inds_stride 0), [B,N] (inds_stride N) or

@@ -46,7 +46,8 @@ def lib():
 
 
 def set_pos_deriv_quirk(on):
-    """1: restate the reference's `pos_deriv[D] = {1.0f}` initialisation bug (see ngp_oracle.c); 0: correct."""
+    """1 (the default state): the reference's `pos_deriv[D] = {1.0f}` (gridencoder.cu:143, see ngp_oracle.c); 0: the exact
+    derivative, for checking the kernels' exact_input_grad opt-in.  Callers that switch it off must switch it back on."""
     lib().orc_set_pos_deriv_quirk(_i32(int(on)))
 
 

@@ -82,9 +82,10 @@ static int orc_oob(const float *x, uint32_t D) {
 
 /* The reference declares `float pos_deriv[D] = {1.0f}` (gridencoder.cu:143): only element 0 is 1, the
  * rest are 0, so with LINEAR interpolation its dy_dx (and therefore grad_inputs) is zero for d > 0.
- * quirk == 1 restates that faithfully (used when checking against the reference extension);
- * quirk == 0 (default) is the mathematically correct derivative, which is what the B200 kernels ship. */
-static int orc_pos_deriv_quirk = 0;
+ * quirk == 1 (DEFAULT) restates that faithfully -- the oracle is the reference's algorithm, and the B200 kernels
+ * reproduce it by default too; quirk == 0 is the mathematically exact derivative, the checker of the kernels'
+ * opt-in NGP_OPT_EXACT_INPUT_GRAD / GridEncoder(exact_input_grad=True). */
+static int orc_pos_deriv_quirk = 1;
 void orc_set_pos_deriv_quirk(int on) { orc_pos_deriv_quirk = on; }
 
 /* gridencoder.cu:146-156: position inside the level; returns base cell + (smooth)fraction. */

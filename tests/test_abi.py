@@ -79,12 +79,14 @@ def test_plugin_api_signatures_match_reference():
     sig = inspect.signature(gridencoder.GridEncoder.__init__)
     expect = dict(input_dim=3, num_levels=16, level_dim=2, per_level_scale=2, base_resolution=16, log2_hashmap_size=19,
                   desired_resolution=None, gridtype="hash", align_corners=False, interpolation="linear")
-    assert {k: v.default for k, v in sig.parameters.items() if k != "self"} == expect
+    got = {k: v.default for k, v in sig.parameters.items() if k != "self"}
+    assert list(got)[:len(expect)] == list(expect) and {k: got[k] for k in expect} == expect  # the reference's, in its order
+    assert {k: v for k, v in got.items() if k not in expect} == {"exact_input_grad": False}  # the one extension, off by default
     assert list(inspect.signature(gridencoder.GridEncoder.forward).parameters) == ["self", "inputs", "bound"]
     assert list(inspect.signature(gridencoder.GridEncoder.grad_total_variation).parameters) == ["self", "weight", "inputs", "bound", "B"]
     fwd = inspect.signature(gridencoder.grid._grid_encode.forward)
-    assert list(fwd.parameters)[1:] == ["inputs", "embeddings", "offsets", "per_level_scale", "base_resolution", "calc_grad_inputs",
-                                        "gridtype", "align_corners", "interpolation"]
+    assert list(fwd.parameters)[1:10] == ["inputs", "embeddings", "offsets", "per_level_scale", "base_resolution", "calc_grad_inputs",
+                                          "gridtype", "align_corners", "interpolation"]
     rm = raymarching.raymarching
     assert list(inspect.signature(rm._march_rays_train.forward).parameters)[1:] == [
         "rays_o", "rays_d", "bound", "density_bitfield", "C", "H", "nears", "fars", "step_counter", "mean_count", "perturb", "align",

@@ -27,13 +27,11 @@ def rel(a, b):
 @pytest.mark.parametrize("tag,tol", [("f32", 1e-5), ("f16", 2e-3)])
 def test_oracle_grid_vs_golden(oracle, tag, tol):
     g = load("grid_" + tag)
-    oracle.set_pos_deriv_quirk(True)  # the reference's linear-interpolation dy_dx is zero for d > 0 (gridencoder.cu:143)
     oracle.set_level_exp2(g["level_exp2"])  # device exp2f of the per-level scale, recorded with the fixture
     try:
         out, dy = oracle.grid_encode_forward(g["x"], g["embeddings"], g["offsets"], float(g["per_level_scale"]), int(g["base_resolution"]), True)
         ge, gi = oracle.grid_encode_backward(g["grad"], g["x"], g["embeddings"], g["offsets"], float(g["per_level_scale"]), int(g["base_resolution"]), dy)
     finally:
-        oracle.set_pos_deriv_quirk(False)
         oracle.set_level_exp2(None)
     assert rel(out, g["outputs"]) < tol
     assert rel(dy, g["dy_dx"]) < tol * 4
@@ -128,14 +126,11 @@ def test_kernels_grid_vs_golden(tag, tol):
     S, H = float(np.log2(float(g["per_level_scale"]))), int(g["base_resolution"])
     out = torch.empty(L, B, C, device="cuda", dtype=dt)
     dy = torch.empty(B, L * 3 * C, device="cuda", dtype=dt)
-    abi.set_option("hashgrid_ref_pos_deriv_quirk", 1)
-    try:
-        be.grid_encode_forward(x, emb, offs, out, B, 3, C, L, S, H, dy, 0, False, 0)
-        ge = torch.zeros_like(emb)
-        gi = torch.zeros(B, 3, device="cuda", dtype=dt)
-        be.grid_encode_backward(_T(g["grad"]).to(dt), x, emb, offs, ge, B, 3, C, L, S, H, dy, gi, 0, False, 0)
-    finally:
-        abi.set_option("hashgrid_ref_pos_deriv_quirk", 0)
+    # default call, no option of any kind: the library's dy_dx is the reference's (gridencoder.cu:143)
+    be.grid_encode_forward(x, emb, offs, out, B, 3, C, L, S, H, dy, 0, False, 0)
+    ge = torch.zeros_like(emb)
+    gi = torch.zeros(B, 3, device="cuda", dtype=dt)
+    be.grid_encode_backward(_T(g["grad"]).to(dt), x, emb, offs, ge, B, 3, C, L, S, H, dy, gi, 0, False, 0)
     assert rel(out.float().cpu().numpy(), g["outputs"]) < tol
     assert rel(ge.float().cpu().numpy(), g["grad_embeddings"]) < tol * 4
     assert rel(gi.float().cpu().numpy(), g["grad_inputs"]) < max(tol * 10, 1e-4)

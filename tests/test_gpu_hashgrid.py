@@ -22,23 +22,23 @@ def _abi():
     return ngp_abi
 
 
-def _run_fwd(x, emb, offsets, pls, H, calc_dy=False, gridtype=0, ac=False, interp=0, layout=0):
+def _run_fwd(x, emb, offsets, pls, H, calc_dy=False, gridtype=0, ac=False, interp=0, layout=0, opts=None):
     be = _be()
     B, D = x.shape
     L, C = offsets.shape[0] - 1, emb.shape[1]
     out = torch.empty((L, B, C) if layout == 0 else (B, L * C), device=DEV, dtype=emb.dtype)
     dy = torch.empty(B, L * D * C, device=DEV, dtype=emb.dtype) if calc_dy else None
-    be.grid_encode_forward(x, emb, offsets, out, B, D, C, L, np.log2(pls), H, dy, gridtype, ac, interp, layout=layout)
+    be.grid_encode_forward(x, emb, offsets, out, B, D, C, L, np.log2(pls), H, dy, gridtype, ac, interp, layout=layout, opts=opts)
     return out, dy
 
 
-def _run_bwd(grad, x, emb, offsets, pls, H, dy=None, gridtype=0, ac=False, interp=0, layout=0):
+def _run_bwd(grad, x, emb, offsets, pls, H, dy=None, gridtype=0, ac=False, interp=0, layout=0, opts=None):
     be = _be()
     B, D = x.shape
     L, C = offsets.shape[0] - 1, emb.shape[1]
     g_emb = torch.zeros_like(emb)
     g_in = torch.zeros(B, D, device=DEV, dtype=emb.dtype) if dy is not None else None
-    be.grid_encode_backward(grad, x, emb, offsets, g_emb, B, D, C, L, np.log2(pls), H, dy, g_in, gridtype, ac, interp, layout=layout)
+    be.grid_encode_backward(grad, x, emb, offsets, g_emb, B, D, C, L, np.log2(pls), H, dy, g_in, gridtype, ac, interp, layout=layout, opts=opts)
     return g_emb, g_in
 
 
@@ -158,7 +158,7 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
     abi = _abi()
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
     ot = torch.from_numpy(offsets).to(DEV)
-    B = 40000  # > 32768: the shared-memory coarse levels of hashgrid_bwd_smem_coarse are exercised
+    B = 40000  # > 32768: the shared-memory coarse levels of NGP_OPT_GRID_BWD_SMEM_COARSE are exercised
     torch.manual_seed(3)
     x = torch.rand(B, 3, device=DEV)
     n_rays = 64
@@ -171,8 +171,8 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
     g = torch.randn(B, 32, device=DEV).to(dtype)
     g[100:400] = 0  # zero-gradient lanes are skipped
     keys = ("hashgrid_fwd_variant", "hashgrid_bwd_variant", "hashgrid_v3_mix_fwd", "hashgrid_v3_mix_bwd", "hashgrid_v3_minb_fwd",
-            "hashgrid_v3_minb_bwd", "hashgrid_bwd_red4", "hashgrid_bwd_smem_coarse")
-    defaults = dict(zip(keys, (-1, -1, 0, 1, -1, -1, 2, 0)))
+            "hashgrid_v3_minb_bwd", "hashgrid_bwd_red4")
+    defaults = dict(zip(keys, (-1, -1, 0, 1, -1, -1, 2)))
 
     def setopts(**kw):
         for k, v in {**defaults, **kw}.items():
@@ -182,10 +182,12 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
         ref, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
         ge_ref, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)
         for kw in (dict(), dict(hashgrid_v3_mix_fwd=1, hashgrid_v3_mix_bwd=0), dict(hashgrid_v3_minb_fwd=4, hashgrid_v3_minb_bwd=6),
-                   dict(hashgrid_v3_minb_fwd=6, hashgrid_bwd_red4=0), dict(hashgrid_bwd_red4=1), dict(hashgrid_bwd_smem_coarse=1)):
+                   dict(hashgrid_v3_minb_fwd=6, hashgrid_bwd_red4=0), dict(hashgrid_bwd_red4=1), dict(coarse_flag=1)):
+            kw = dict(kw)
+            coarse = abi.call_opts(flags=abi.OPT_GRID_BWD_SMEM_COARSE) if kw.pop("coarse_flag", 0) else None  # per-call flag, not an option
             setopts(hashgrid_fwd_variant=3, hashgrid_bwd_variant=3, **kw)
             out, _ = _run_fwd(x, emb, ot, pls, 16, False, gridtype, False, 0, 1)
-            ge, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1)
+            ge, _ = _run_bwd(g, x, emb, ot, pls, 16, None, gridtype, False, 0, 1, opts=coarse)
             if dtype == torch.float32:
                 assert torch.equal(out, ref), kw
                 assert torch.allclose(ge, ge_ref, rtol=1e-4, atol=1e-4), kw
@@ -199,8 +201,9 @@ def test_v3_kernel_options_equal_generic(oracle, dtype, gridtype):
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
 def test_input_bound_is_the_module_mapping(oracle, dtype):
-    """ngp_set_input_bound(b): the kernels map [-b, b] -> [0, 1] as they load the points, bit for bit the
-    (x + b) / (2 b) of GridEncoder.forward (grid.py:807); unsupported configurations refuse loudly."""
+    """ngp_call_opts.input_bound = b: the kernels map [-b, b] -> [0, 1] as they load the points, bit for bit the
+    (x + b) / (2 b) of GridEncoder.forward (grid.py:807); unsupported configurations refuse loudly.  The option travels
+    with the call: a call without it, made right after, sees inputs in [0, 1] again (no process-wide state)."""
     abi = _abi()
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
     ot = torch.from_numpy(offsets).to(DEV)
@@ -211,24 +214,57 @@ def test_input_bound_is_the_module_mapping(oracle, dtype):
     emb = ((torch.rand(int(offsets[-1]), 2, device=DEV) - 0.5) * 2).to(dtype)
     g = torch.randn(B, 32, device=DEV).to(dtype)
     ref, _ = _run_fwd(x01, emb, ot, pls, 16, layout=1)
-    for coarse in (0, 1):
-        abi.set_option("hashgrid_bwd_smem_coarse", coarse)
-        ge_ref, _ = _run_bwd(g, x01, emb, ot, pls, 16, layout=1)
-        abi.lib.ngp_set_input_bound(bound)
-        try:
-            out, _ = _run_fwd(x, emb, ot, pls, 16, layout=1)
-            ge, _ = _run_bwd(g, x, emb, ot, pls, 16, layout=1)
-            with pytest.raises(RuntimeError):  # generic kernels (no host offsets / D != 3) do not take the mapping
-                _run_fwd(x[:, :2].contiguous(), emb, ot, pls, 16, layout=1)
-        finally:
-            abi.lib.ngp_set_input_bound(0.0)
-            abi.set_option("hashgrid_bwd_smem_coarse", 0)
+    for coarse in (0, abi.OPT_GRID_BWD_SMEM_COARSE):
+        ge_ref, _ = _run_bwd(g, x01, emb, ot, pls, 16, layout=1, opts=abi.call_opts(flags=coarse))
+        o = abi.call_opts(input_bound=bound, flags=coarse)
+        out, _ = _run_fwd(x, emb, ot, pls, 16, layout=1, opts=o)
+        ge, _ = _run_bwd(g, x, emb, ot, pls, 16, layout=1, opts=o)
+        with pytest.raises(RuntimeError):  # generic kernels (no host offsets / D != 3) do not take the mapping
+            _run_fwd(x[:, :2].contiguous(), emb, ot, pls, 16, layout=1, opts=o)
+        again, _ = _run_fwd(x01, emb, ot, pls, 16, layout=1)  # nothing lingers after a call that carried the option
+        assert torch.equal(again, ref)
         assert torch.equal(out, ref)
         if dtype == torch.float32:
             assert torch.allclose(ge, ge_ref, rtol=1e-4, atol=1e-4)
         else:
             hashed = slice(int(offsets[6]), None)
             assert torch.allclose(ge[hashed].float(), ge_ref[hashed].float(), rtol=2e-2, atol=2e-2)
+
+
+def test_exact_input_grad_is_opt_in(oracle):
+    """Default dy_dx = the reference's (`pos_deriv[D] = {1.0f}`, gridencoder.cu:143: zero for d > 0 with linear
+    interpolation); NGP_OPT_EXACT_INPUT_GRAD / GridEncoder(exact_input_grad=True) gives the exact derivative.  Both
+    against the oracle in the matching mode."""
+    abi = _abi()
+    offs, pls, x, emb = _cfg(oracle, 3, 2, L=4)
+    xt, et, ot = torch.from_numpy(x).to(DEV), torch.from_numpy(emb).to(DEV), torch.from_numpy(offs).to(DEV)
+    ref_out, ref_dy = oracle.grid_encode_forward(x, emb, offs, pls, 4, True)
+    out, dy = _run_fwd(xt, et, ot, pls, 4, True)
+    assert np.allclose(dy.cpu().numpy(), ref_dy, rtol=1e-4, atol=1e-4 * np.abs(ref_dy).max())
+    d3 = dy.view(x.shape[0], 4, 3, 2)
+    assert float(d3[:, :, 1:].abs().max()) == 0.0 and float(d3[:, :, 0].abs().max()) > 0.0
+    oracle.set_pos_deriv_quirk(False)
+    try:
+        _, ex_dy = oracle.grid_encode_forward(x, emb, offs, pls, 4, True)
+    finally:
+        oracle.set_pos_deriv_quirk(True)
+    out2, dy2 = _run_fwd(xt, et, ot, pls, 4, True, opts=abi.call_opts(flags=abi.OPT_EXACT_INPUT_GRAD))
+    assert torch.equal(out2, out)
+    assert np.allclose(dy2.cpu().numpy(), ex_dy, rtol=1e-4, atol=1e-4 * np.abs(ex_dy).max())
+    assert float(dy2.view(x.shape[0], 4, 3, 2)[:, :, 1:].abs().max()) > 0.0
+    # module level
+    from gridencoder import GridEncoder
+    torch.manual_seed(0)
+    grads = {}
+    for exact in (False, True):
+        enc = GridEncoder(num_levels=4, desired_resolution=64, log2_hashmap_size=12, exact_input_grad=exact).to(DEV)
+        with torch.no_grad():
+            enc.embeddings.copy_(torch.linspace(-1, 1, enc.embeddings.numel(), device=DEV).view_as(enc.embeddings).sin())
+        xr = (torch.from_numpy(x[4:]).to(DEV) * 2 - 1).requires_grad_(True)
+        enc(xr).pow(2).sum().backward()
+        grads[exact] = xr.grad.clone()
+    assert float(grads[False][:, 1:].abs().max()) == 0.0 and float(grads[True][:, 1:].abs().max()) > 0.0
+    assert torch.allclose(grads[False][:, 0], grads[True][:, 0], rtol=1e-5, atol=1e-6)
 
 
 def test_warp_aggregated_backward_coherent_points(oracle):

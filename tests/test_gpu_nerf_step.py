@@ -202,45 +202,58 @@ def test_step_matches_cpu_oracle_step():
 
 
 def test_device_side_batch_limit():
-    """ngp_set_batch_limit: the per-sample kernels stop at min(B, *count) read on the device; rows past it are untouched."""
+    """ngp_call_opts.batch_limit: the per-sample kernels stop at min(B, *count) read on the device; rows past it are
+    untouched; the level-major layout keeps the caller's B as its row stride; a call made without the
+    option right after is unlimited (no process-wide state)."""
+    import numpy as np
     import ngp_abi as abi
     import gridencoder
     import ffmlp
+    gb, fb = gridencoder._backend, ffmlp._backend
     B, n = 5000, 3217
     cnt = torch.tensor([n, 0], dtype=torch.int32, device="cuda")
     enc = gridencoder.GridEncoder(num_levels=16, level_dim=2, base_resolution=16, log2_hashmap_size=15, desired_resolution=512).cuda()
     with torch.no_grad():
         enc.embeddings.uniform_(-1, 1)
-    x = torch.rand(B, 3, device="cuda") * 2 - 1
-    net = ffmlp.FFMLP(32, 16, 64, 2).cuda().train()
+    L, S, H = 16, float(np.log2(enc.per_level_scale)), 16
+    emb16, offs = enc.embeddings.detach().half().contiguous(), enc.offsets
+    x = torch.rand(B, 3, device="cuda")
+    net = ffmlp.FFMLP(32, 16, 64, 2).cuda()
+    w = net.weights.detach()
     g = torch.randn(B, 16, device="cuda").half()
 
-    def run(xs, gs):
-        for p in (enc.embeddings, net.weights):
-            p.grad = None
-        with torch.autocast("cuda", dtype=torch.half):
-            y = net(enc(xs, bound=1))
-        y.backward(gs)
-        return y.detach().clone(), enc.embeddings.grad.clone(), net.weights.grad.clone()
+    def run(xs, gs, opts, layout, fill=7.0):
+        nb = xs.shape[0]
+        feat = torch.full((L, nb, 2) if layout == abi.LAYOUT_LBC else (nb, 32), fill, dtype=torch.half, device="cuda")
+        gb.grid_encode_forward(xs, emb16, offs, feat, nb, 3, 2, L, S, H, None, 0, False, 0, layout=layout, opts=opts)
+        rows = feat.permute(1, 0, 2).reshape(nb, 32).contiguous() if layout == abi.LAYOUT_LBC else feat
+        y = torch.full((nb, 16), fill, dtype=torch.half, device="cuda")
+        fb.ffmlp_forward(rows, w, nb, 32, 16, 64, 2, 0, 6, None, y, opts=opts)
+        gx, gw = torch.full((nb, 32), fill, dtype=torch.half, device="cuda"), torch.empty_like(w)
+        fb.ffmlp_backward(gs, rows, w, None, nb, 32, 16, 64, 2, 0, 6, True, None, gx, gw, opts=opts)
+        gfeat = gx.view(nb, L, 2).permute(1, 0, 2).contiguous() if layout == abi.LAYOUT_LBC else gx
+        ge = torch.zeros_like(emb16)
+        gb.grid_encode_backward(gfeat, xs, emb16, offs, ge, nb, 3, 2, L, S, H, None, None, 0, False, 0, layout=layout, opts=opts)
+        return feat, y, gx, gw, ge
 
-    y_ref, ge_ref, gw_ref = run(x[:n].contiguous(), g[:n].contiguous())
-    abi.check(abi.lib.ngp_set_batch_limit(cnt.data_ptr()))
-    try:
-        y, ge, gw = run(x, g)
-    finally:
-        abi.check(abi.lib.ngp_set_batch_limit(None))
-    assert torch.equal(y[:n], y_ref)
-    assert _rel(gw, gw_ref) < 1e-6
-    assert _rel(ge, ge_ref) < 1e-2  # fp16 atomics, order-dependent
-    # a limit above B is clamped to B
+    for layout in (abi.LAYOUT_BLC, abi.LAYOUT_LBC):
+        f_ref, y_ref, gx_ref, gw_ref, ge_ref = run(x[:n].contiguous(), g[:n].contiguous(), None, layout)
+        f, y, gx, gw, ge = run(x, g, abi.call_opts(batch_limit=cnt), layout)
+        if layout == abi.LAYOUT_LBC:
+            assert torch.equal(f[:, :n], f_ref) and bool((f[:, n:] == 7.0).all())  # stride B, rows past the limit untouched
+        else:
+            assert torch.equal(f[:n], f_ref) and bool((f[n:] == 7.0).all())
+        assert torch.equal(y[:n], y_ref) and bool((y[n:] == 7.0).all())
+        assert torch.equal(gx[:n], gx_ref) and bool((gx[n:] == 7.0).all())
+        assert _rel(gw, gw_ref) < 1e-6
+        assert _rel(ge, ge_ref) < 1e-2  # fp16 atomics, order-dependent
+    # a limit above B is clamped to B; and the call after a limited one is unlimited
     cnt[0] = 10 * B
-    abi.check(abi.lib.ngp_set_batch_limit(cnt.data_ptr()))
-    try:
-        y2, _, gw2 = run(x, g)
-    finally:
-        abi.check(abi.lib.ngp_set_batch_limit(None))
-    y_full, _, gw_full = run(x, g)
-    assert torch.equal(y2, y_full) and _rel(gw2, gw_full) < 1e-6
+    _, y2, _, gw2, _ = run(x, g, abi.call_opts(batch_limit=cnt), abi.LAYOUT_BLC)
+    cnt[0] = 1
+    run(x, g, abi.call_opts(batch_limit=cnt), abi.LAYOUT_BLC)
+    _, y_full, _, gw_full, _ = run(x, g, None, abi.LAYOUT_BLC)
+    assert torch.equal(y2, y_full) and _rel(gw2, gw_full) < 1e-6 and bool((y_full != 7.0).any(dim=1).all())
 
 
 def test_inference_render_matches_training_quadrature_and_band_sharding():
@@ -271,9 +284,9 @@ def test_inference_render_matches_training_quadrature_and_band_sharding():
     import ngp_abi as abi
     tr._encode(xyzs.contiguous(), x01, enc, M)
     tr._sigma_forward(enc, h, M, True)
-    abi.check(abi.lib.ngp_nerf_mid_forward(h.data_ptr(), dirs.contiguous().data_ptr(), tr.density_scale, sig.data_ptr(), cin.data_ptr(), M, abi.stream()))
+    abi.check(abi.lib.ngp_nerf_mid_forward(h.data_ptr(), dirs.contiguous().data_ptr(), tr.density_scale, sig.data_ptr(), cin.data_ptr(), M, abi.stream(), None))
     tr._color_forward(cin, c, M, True)
-    abi.check(abi.lib.ngp_nerf_rgb_forward(c.data_ptr(), rgb.data_ptr(), M, abi.stream()))
+    abi.check(abi.lib.ngp_nerf_rgb_forward(c.data_ptr(), rgb.data_ptr(), M, abi.stream(), None))
     ws, dep, im = raymarching.composite_rays_train(sig, rgb, deltas, rays, 1e-4)
     ref = im + (1 - ws).unsqueeze(-1) * tr.bg_color
     assert (img - ref).abs().max() < 2e-3, float((img - ref).abs().max())

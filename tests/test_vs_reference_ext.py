@@ -50,10 +50,8 @@ def test_grid_encoder_vs_reference(oracle, dtype, request):
     import gridencoder
     import ngp_abi as abi
     be = gridencoder._backend
-    # the reference's linear-interpolation dy_dx is zero for d > 0 (`pos_deriv[D] = {1.0f}`, gridencoder.cu:143);
-    # this switch makes the new kernel reproduce that so the comparison can be bit-exact
-    abi.set_option("hashgrid_ref_pos_deriv_quirk", 1)
-    request.addfinalizer(lambda: abi.set_option("hashgrid_ref_pos_deriv_quirk", 0))
+    # no option is set anywhere in this file: the library's defaults ARE the reference's behaviour, including its
+    # linear-interpolation dy_dx that is zero for d > 0 (`pos_deriv[D] = {1.0f}`, gridencoder.cu:143)
     offsets, pls = oracle.make_offsets(desired_resolution=2048)
     L, C, D, H, S = 16, 2, 3, 16, np.log2(pls)
     B = 1 << 16

@@ -31,13 +31,12 @@ static std::map<std::string, int> &options() {
         {"hashgrid_v3_mix_fwd", 0},    // v3 forward: warps of one block work on different level groups (1) or whole blocks do (0)
         {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
         {"hashgrid_bwd_red4", 2},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours: 0 never, 1 always, 2 when the lanes of a warp do not share groups (random points)
-        {"ffmlp_ablate", 0},           // timing experiments only (results are wrong): 1 skip the weight-gradient MMAs, 2 skip the layer MMAs, 3 both
+#ifdef NGP_FFMLP_DEBUG
+        {"ffmlp_ablate", 0},           // developer builds only: timing experiments with WRONG results (1 skip the weight-gradient MMAs, 2 the layer MMAs, 3 both)
+#endif
         {"march_rays_warp", 32768},    // inference marcher: one warp per alive ray while n_alive <= this (0 = always one thread per ray, the reference's mapping)
-        {"adam_blocks_per_sm", 0},     // k_adam grid cap (0 = one block per 1024 parameters); NGPTrainer sets it when the optimizer shares the SMs with the marcher
-        {"hashgrid_bwd_smem_coarse", 0},  // v3 backward: accumulate the levels that fit in shared memory (unordered points: SDF, configs[0])
         {"hashgrid_smem_levels", 1},   // keep coarse levels in shared memory (fast paths)
         {"hashgrid_bwd_warp_agg", 1},  // collapse warp-uniform cells before the L2 reduction
-        {"hashgrid_ref_pos_deriv_quirk", 0},  // 1: reproduce the reference's zero dy_dx for d>0 (linear interp)
         {"march_variant", -1},         // training marcher: -1 auto / 1 warp per ray (ballot replay of the skip rule), 0 thread per ray
         {"march_masks", 1},            // warp marcher: record emit masks in pass 1 when the workspace has room (0: always re-march)
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
@@ -87,13 +86,15 @@ prof_scope::~prof_scope() {
     cudaEventRecord(g_prof_recs[slot].b, st);
 }
 
-// process-wide on purpose: autograd runs backward functions on its own worker threads
-static std::atomic<const int *> g_batch_limit{nullptr};
-const int *batch_limit() { return g_batch_limit.load(std::memory_order_acquire); }
-void set_batch_limit(const int *p) { g_batch_limit.store(p, std::memory_order_release); }
-static std::atomic<float> g_input_bound{0.0f};
-float input_bound() { return g_input_bound.load(std::memory_order_acquire); }
-void set_input_bound(float b) { g_input_bound.store(b, std::memory_order_release); }
+// Per-call options (include/ngp_b200.h ngp_call_opts): an extern "C" entry point opens an opts_scope for the duration
+// of the call; the launch code below it reads the accessors.  Thread-local, so nothing is shared between callers.
+static thread_local const ngp_call_opts *t_opts = nullptr;
+opts_scope::opts_scope(const ngp_call_opts *o) : prev(t_opts) { t_opts = o; }
+opts_scope::~opts_scope() { t_opts = prev; }
+const int *batch_limit() { return t_opts ? reinterpret_cast<const int *>(t_opts->batch_limit) : nullptr; }
+float input_bound() { return (t_opts && t_opts->input_bound > 0.f) ? t_opts->input_bound : 0.f; }
+uint32_t call_flags() { return t_opts ? t_opts->flags : 0u; }
+int grid_cap_blocks_per_sm() { return t_opts ? t_opts->grid_cap_blocks_per_sm : 0; }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -128,16 +129,6 @@ int ngp_set_option(const char *key, int value) {
 }
 
 long long ngp_launch_count(void) { return ngp::g_launches.load(); }
-
-int ngp_set_input_bound(float bound) {
-    ngp::set_input_bound(bound > 0.f ? bound : 0.f);
-    return NGP_OK;
-}
-
-int ngp_set_batch_limit(const int32_t *count_dev) {
-    ngp::set_batch_limit(reinterpret_cast<const int *>(count_dev));
-    return NGP_OK;
-}
 
 // Synchronises the recorded events and writes one line per kernel name: "<name> <count> <total_ms>\n".
 // Returns the number of bytes written (excluding the NUL), or a negative error code; clears the records.

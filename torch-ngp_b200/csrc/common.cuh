@@ -12,10 +12,17 @@ namespace ngp {
 void set_error(const char *fmt, ...);
 int get_option(const char *key, int dflt);
 int sm_count();  // SMs of the current device (148 on B200), cached
-const int *batch_limit();  // device pointer set by ngp_set_batch_limit (process-wide), or nullptr
-void set_batch_limit(const int *p);
-float input_bound();  // ngp_set_input_bound (process-wide): > 0 -> the grid kernels map inputs from [-bound, bound] to [0, 1] themselves
-void set_input_bound(float b);
+// Per-call options (ngp_call_opts, include/ngp_b200.h): valid inside an opts_scope opened by the extern "C" entry point
+// on the calling thread; defaults (nullptr / 0) outside.  No process-wide state.
+struct opts_scope {
+    const ngp_call_opts *prev;
+    explicit opts_scope(const ngp_call_opts *o);
+    ~opts_scope();
+};
+const int *batch_limit();        // opts->batch_limit (device int) or nullptr
+float input_bound();             // opts->input_bound if > 0, else 0: the grid kernels map [-bound, bound] -> [0, 1] themselves
+uint32_t call_flags();           // opts->flags (NGP_OPT_*)
+int grid_cap_blocks_per_sm();    // opts->grid_cap_blocks_per_sm
 
 // Effective batch of a per-sample kernel: min(B, *limit * mult) when a device-side limit is set.  The launch is
 // still sized for B; blocks past the limit exit at once.  `limit` was written by an earlier kernel on the stream.

@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar[8];
-    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_set_batch_limit)
+    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_call_opts.batch_limit)
     ntiles = min(ntiles, div_round_up(Beff, kTileRows));
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
     const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(128 * split_of<HID>::NS) k_ffmlp_bwd(const __h
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
-    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_set_batch_limit)
+    const uint32_t Beff = eff_batch(m.B, limit);  // device-side batch (ngp_call_opts.batch_limit)
     ntiles = min(ntiles, div_round_up(Beff, kTileRows));
     __shared__ __align__(8) uint64_t s_bar;
     constexpr int NS = split_of<HID>::NS, CW = HID / NS;
@@ -604,7 +604,11 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
     fence_after_sync();
     const uint32_t tmem = s_tmem;
     const uint32_t stride = gridDim.x * np;
-    const bool abl_dw = (dual >> 4) & 1, abl_mm = (dual >> 5) & 1;  // timing ablations (option ffmlp_ablate): wrong results
+#ifdef NGP_FFMLP_DEBUG
+    const bool abl_dw = (dual >> 4) & 1, abl_mm = (dual >> 5) & 1;  // timing ablations (developer builds, option ffmlp_ablate): wrong results
+#else
+    constexpr bool abl_dw = false, abl_mm = false;
+#endif
     // self-issue: every pipeline issues its own layer products (one elected thread of its first warp, after a named
     // barrier over the pipeline's threads) instead of handing them to warp 0.  The central issuer's control code
     // (poll, bookkeeping, ~1.2k cycles per service, three pipelines served in turn) was the critical path of the
@@ -940,7 +944,8 @@ extern "C" {
 
 int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim, uint32_t output_dim,
                       uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation, void *forward_buffer,
-                      void *outputs, void *stream) {
+                      void *outputs, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     (void)forward_buffer;  // never written: the backward recomputes the activations
     return ngp::run_forward("ffmlp_forward", inputs, weights, weights_dtype, B, input_dim, output_dim, hidden_dim, num_layers, activation,
                             output_activation, outputs, stream);
@@ -948,7 +953,8 @@ int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype
 
 int ngp_ffmlp_inference(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim, uint32_t output_dim,
                         uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation, void *inference_buffer,
-                        void *outputs, void *stream) {
+                        void *outputs, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     (void)inference_buffer;
     return ngp::run_forward("ffmlp_inference", inputs, weights, weights_dtype, B, input_dim, output_dim, hidden_dim, num_layers, activation,
                             output_activation, outputs, stream);
@@ -962,7 +968,8 @@ size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_di
 int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, int weights_dtype, const void *forward_buffer, uint32_t B,
                        uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
                        uint32_t output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs, void *grad_weights,
-                       int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream) {
+                       int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     (void)forward_buffer;
     (void)backward_buffer;
@@ -1032,7 +1039,10 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         if (variant != 0 && (np >= 2 || (variant == 1 && np >= 1))) {
             const size_t smem_mp = m.wbytes + np * per_pipe;
             const int nis = get_option("ffmlp_bwd_issuers", 3);  // 1 one central issuer, 2 two (layer products / weight gradients), 3 pipelines issue their own layer products
-            const int dual = (nis != 1 ? 1 : 0) | (nis >= 3 ? 2 : 0) | (get_option("ffmlp_ablate", 0) << 4);
+            int dual = (nis != 1 ? 1 : 0) | (nis >= 3 ? 2 : 0);
+#ifdef NGP_FFMLP_DEBUG  // developer builds only: timing ablations that produce WRONG results are not reachable from the shipped library
+            dual |= get_option("ffmlp_ablate", 0) << 4;
+#endif
             const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
             uint32_t grid_mp = div_round_up(ntiles, np);
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
                                                           uint32_t B, uint32_t L, float S, uint32_t H,
                                                           T *__restrict__ dy_dx, uint32_t gridtype, bool align_corners,
                                                           uint32_t interp, int layout, bool pos_deriv_quirk, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     using A = typename acc_of<T>::type;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
     const uint32_t level = blockIdx.y;
     const level_t lv = level_consts(offsets, level, S, H);
     grid += (size_t)lv.offset * C;
-    T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * C : ((size_t)b * L + level) * C);
+    T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * C : ((size_t)b * L + level) * C);
     if (dy_dx) dy_dx += ((size_t)b * L + level) * D * C;
 
     float x[D];
@@ -131,8 +132,8 @@ __global__ void __launch_bounds__(256) k_grid_fwd_generic(const float *__restric
         pg[d] = (uint32_t)floorf(pos[d]);
         pos[d] -= (float)pg[d];
         // The reference initialises `float pos_deriv[D] = {1.0f}` (gridencoder.cu:143): only element 0 is 1, so its
-        // linear-interpolation dy_dx is zero for d > 0.  Default here is the correct derivative (all ones);
-        // option hashgrid_ref_pos_deriv_quirk=1 reproduces the reference bit for bit.
+        // linear-interpolation dy_dx is zero for d > 0.  That is the DEFAULT here too (bit for bit); the flag
+        // NGP_OPT_EXACT_INPUT_GRAD of ngp_call_opts selects the mathematically exact derivative (all ones).
         pos_deriv[d] = (pos_deriv_quirk && d > 0) ? 0.0f : 1.0f;
         if (interp == 1) {
             pos_deriv[d] = smoothstep_df(pos[d]);
@@ -225,6 +226,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_generic(const T *__restrict__ 
                                                           const int *__restrict__ offsets, T *__restrict__ grad_grid,
                                                           uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
                                                           bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     using A = typename acc_of<T>::type;
     constexpr uint32_t N_C = C < 2 ? C : 2;
@@ -250,7 +252,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_generic(const T *__restrict__ 
         pos[d] -= (float)pg[d];
         if (interp == 1) pos[d] = smoothstep_f(pos[d]);
     }
-    const T *g = grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * C : ((size_t)b * L + level) * C) + ch;
+    const T *g = grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * C : ((size_t)b * L + level) * C) + ch;
     A gc[N_C];
 #pragma unroll
     for (uint32_t c = 0; c < N_C; ++c) gc[c] = to_acc<T>(g[c]);

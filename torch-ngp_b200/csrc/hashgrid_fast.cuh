@@ -179,13 +179,14 @@ __global__ void __launch_bounds__(256) k_grid_fwd_d3c2(const float *__restrict__
                                                        const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B,
                                                        uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                                                        uint32_t interp, int layout, uint32_t level_begin, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint32_t level = level_begin + blockIdx.y;
     const level_t lv = level_consts(offsets, level, S, H);
     const geo3_t g = make_geo3(lv, gridtype, align_corners);
-    T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2);
+    T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * 2 : ((size_t)b * L + level) * 2);
     loc3_t o;
     if (!locate3(inputs, b, lv.scale, align_corners, interp, o)) {
         entry_io<T>::store1(out, 0.f, 0.f);
@@ -207,6 +208,7 @@ __global__ void __launch_bounds__(1024) k_grid_fwd_d3c2_smem(const float *__rest
                                                              const int *__restrict__ offsets, T *__restrict__ outputs,
                                                              uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
                                                              bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *tab = reinterpret_cast<T *>(smem_raw);
@@ -221,7 +223,7 @@ __global__ void __launch_bounds__(1024) k_grid_fwd_d3c2_smem(const float *__rest
     }
     __syncthreads();
     for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
-        T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2);
+        T *out = outputs + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * 2 : ((size_t)b * L + level) * 2);
         loc3_t o;
         if (!locate3(inputs, b, lv.scale, align_corners, interp, o)) {
             entry_io<T>::store1(out, 0.f, 0.f);
@@ -265,6 +267,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2(const T *__restrict__ gra
                                                        const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B,
                                                        uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                                                        uint32_t interp, int layout, uint32_t level_begin, int warp_agg, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x is a multiple of 32: warps exit whole or not at all
     const uint32_t level = level_begin + blockIdx.y;
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2(const T *__restrict__ gra
     const bool valid = (b < B) && locate3(inputs, b, lv.scale, align_corners, interp, o);
     if (!warp_agg) {
         if (!valid) return;
-        const float2 gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2));
+        const float2 gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * 2 : ((size_t)b * L + level) * 2));
         rows3_t r;
         make_rows3(g, o, r);
         scatter8<T>(tab, r, gv.x, gv.y);
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2(const T *__restrict__ gra
     rows3_t r;
     unsigned long long key = ~0ull - threadIdx.x;  // distinct per lane when invalid
     if (valid) {
-        gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2));
+        gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * 2 : ((size_t)b * L + level) * 2));
         make_rows3(g, o, r);
         key = (unsigned long long)o.p0 | ((unsigned long long)o.p1 << 21) | ((unsigned long long)o.p2 << 42);
     }
@@ -326,6 +329,7 @@ __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict
                                                              uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
                                                              bool align_corners, uint32_t interp, int layout, const int *__restrict__ limit,
                                                              float in_bound = 0.f) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *acc = reinterpret_cast<float *>(smem_raw);
@@ -338,7 +342,7 @@ __global__ void __launch_bounds__(1024) k_grid_bwd_d3c2_smem(const T *__restrict
     for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
         loc3_t o;
         if (!locate3(inputs, b, lv.scale, align_corners, interp, o, in_bound)) continue;
-        const float2 gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * B + b) * 2 : ((size_t)b * L + level) * 2));
+        const float2 gv = entry_io<T>::loadg(grad + (layout == NGP_LAYOUT_LBC ? ((size_t)level * Bs + b) * 2 : ((size_t)b * L + level) * 2));
         rows3_t r;
         make_rows3(g, o, r);
 #pragma unroll
@@ -468,6 +472,7 @@ __global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restri
                                                            const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B,
                                                            uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                                                            uint32_t interp, int layout, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t l0 = blockIdx.y * 4;
@@ -500,7 +505,7 @@ __global__ void __launch_bounds__(256) k_grid_fwd_d3c2_lg4(const float *__restri
         store_row4(outputs + ((size_t)b * L + l0) * 2, res);
     } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) entry_io<T>::store1(outputs + ((size_t)(l0 + k) * B + b) * 2, res[k].x, res[k].y);
+        for (int k = 0; k < 4; ++k) entry_io<T>::store1(outputs + ((size_t)(l0 + k) * Bs + b) * 2, res[k].x, res[k].y);
     }
 }
 
@@ -510,6 +515,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__
                                                            const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B,
                                                            uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                                                            uint32_t interp, int layout, int warp_agg, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t l0 = blockIdx.y * 4;
@@ -533,7 +539,7 @@ __global__ void __launch_bounds__(256) k_grid_bwd_d3c2_lg4(const T *__restrict__
             load_row4(grad + ((size_t)b * L + l0) * 2, gv);
         } else {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * B + b) * 2);
+            for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * Bs + b) * 2);
         }
     }
 #pragma unroll

@@ -11,7 +11,7 @@ template <typename T, uint32_t D>
 int launch_fwd_generic(const float *inputs, const T *emb, const int *offsets, T *out, uint32_t B, uint32_t C, uint32_t L,
                        float S, uint32_t H, T *dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     const dim3 grid(div_round_up(B, 256u), L, 1);
-    const bool quirk = get_option("hashgrid_ref_pos_deriv_quirk", 0) != 0;
+    const bool quirk = (call_flags() & NGP_OPT_EXACT_INPUT_GRAD) == 0;  // default: the reference's dy_dx (gridencoder.cu:143)
     switch (C) {
         case 1: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 1><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
         case 2: { NGP_PROF("k_grid_fwd_generic", st); k_grid_fwd_generic<T, D, 2><<<grid, 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, dy_dx, gridtype, ac, interp, layout, quirk, batch_limit()); } break;
@@ -109,7 +109,7 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
-    if (input_bound() > 0.f) { set_error("grid_encode_forward: ngp_set_input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
+    if (input_bound() > 0.f) { set_error("grid_encode_forward: ngp_call_opts.input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
     if (variant == 2 && L % 4 == 0 && ((uintptr_t)emb & 31) == 0 && ((uintptr_t)out & 31) == 0) {
         { NGP_PROF("k_grid_fwd_d3c2_lg4", st); k_grid_fwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(inputs, emb, offsets, out, B, L, S, H, gridtype, ac, interp, layout, batch_limit()); }
         NGP_CHECK_LAUNCH();
@@ -118,11 +118,8 @@ int fwd_d3c2(const float *inputs, const T *emb, const int *offsets, const int *o
     size_t smem = 0;
     const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(T), &smem);
     if (ns > 0) {
-        static bool attr_done = false;  // per instantiation
-        if (!attr_done) {
-            NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_fwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
-            attr_done = true;
-        }
+        NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_fwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
+
         const uint32_t per_sm = smem <= 100 * 1024 ? 2 : 1;
         uint32_t nb = (uint32_t)sm_count() * per_sm / ns;
         nb = nb < 1 ? 1 : nb;
@@ -151,20 +148,17 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         const int minb = get_option("hashgrid_v3_minb_bwd", -1);
         const bool occ6 = minb < 0 ? false : minb >= 6;
         const int red4 = get_option("hashgrid_bwd_red4", 2);
-        // Unordered points (hashgrid_bwd_smem_coarse = 1; the SDF step, configs[0]): every point lands in one of a few
+        // Unordered points (NGP_OPT_GRID_BWD_SMEM_COARSE; the SDF step, configs[0]): every point lands in one of a few
         // thousand coarse cells and the L2 atomic unit serialises same-address reductions.  The levels that fit are
         // accumulated in shared memory instead (fp32, one flush per block).  Ray-ordered samples keep them in the warp
         // reduction (runs of equal cells collapse before they reach L2).
         uint32_t skip = 0;
-        if (get_option("hashgrid_bwd_smem_coarse", 0)) {
+        if (call_flags() & NGP_OPT_GRID_BWD_SMEM_COARSE) {
             size_t smem = 0;
             const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(float), &smem);
             if (ns > 0) {
-                static bool attr_done = false;
-                if (!attr_done) {
-                    NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
-                    attr_done = true;
-                }
+                NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
+
                 const uint32_t per_sm = smem <= 100 * 1024 ? 2 : 1;
                 uint32_t nb = (uint32_t)sm_count() * per_sm / ns;
                 nb = nb < 1 ? 1 : nb;
@@ -183,7 +177,7 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
-    if (input_bound() > 0.f) { set_error("grid_encode_backward: ngp_set_input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
+    if (input_bound() > 0.f) { set_error("grid_encode_backward: ngp_call_opts.input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
     if (variant == 2 && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
         { NGP_PROF("k_grid_bwd_d3c2_lg4", st); k_grid_bwd_d3c2_lg4<T><<<dim3(div_round_up(B, 256u), L / 4, 1), 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, batch_limit()); }
@@ -193,11 +187,8 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
     size_t smem = 0;
     const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(float), &smem);  // fp32 accumulators
     if (ns > 0) {
-        static bool attr_done = false;
-        if (!attr_done) {
-            NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
-            attr_done = true;
-        }
+        NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
+
         const uint32_t per_sm = smem <= 100 * 1024 ? 2 : 1;
         uint32_t nb = (uint32_t)sm_count() * per_sm / ns;
         nb = nb < 1 ? 1 : nb;
@@ -240,7 +231,8 @@ extern "C" {
 
 int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const int *offsets, const int *offsets_host,
                             void *outputs, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
-                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream) {
+                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (B == 0) return NGP_OK;
     NGP_CHECK_ARG(inputs && embeddings && offsets && outputs, "grid_encode_forward: null pointer argument");
@@ -252,7 +244,7 @@ int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const i
     const int variant = get_option("hashgrid_fwd_variant", -1);
     const bool fast = D == 3 && C == 2 && !dy_dx && variant != 0 && fast_path_ok(offsets_host, L);
     if (input_bound() > 0.f && !(fast && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
-        set_error("grid_encode_forward: ngp_set_input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
+        set_error("grid_encode_forward: ngp_call_opts.input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
         return NGP_EUNSUPPORTED;
     }
     switch (dtype) {
@@ -271,7 +263,8 @@ int ngp_grid_encode_forward(const float *inputs, const void *embeddings, const i
 int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int *offsets,
                              const int *offsets_host, void *grad_embeddings, uint32_t B, uint32_t D, uint32_t C, uint32_t L,
                              float S, uint32_t H, const void *dy_dx, void *grad_inputs, uint32_t gridtype, int align_corners,
-                             uint32_t interp, int dtype, int layout, void *stream) {
+                             uint32_t interp, int dtype, int layout, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     (void)embeddings;
     if (B == 0) return NGP_OK;
@@ -285,7 +278,7 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
     const int variant = get_option("hashgrid_bwd_variant", -1);
     const bool fast = D == 3 && C == 2 && variant != 0 && fast_path_ok(offsets_host, L);
     if (input_bound() > 0.f && !(fast && !dy_dx && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
-        set_error("grid_encode_backward: ngp_set_input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
+        set_error("grid_encode_backward: ngp_call_opts.input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
         return NGP_EUNSUPPORTED;
     }
     int rc;

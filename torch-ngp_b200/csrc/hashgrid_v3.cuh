@@ -199,6 +199,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_fwd_v3(const float *__restri
                                                      const int *__restrict__ offsets, T *__restrict__ outputs, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
                                                      int layout, float in_bound, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     uint32_t b, l0;
     map_thread<MIX>(L, b, l0);
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_fwd_v3(const float *__restri
         store_row4(outputs + ((size_t)b * L + l0) * 2, res);
     } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) entry_io<T>::store1(outputs + ((size_t)(l0 + k) * B + b) * 2, res[k].x, res[k].y);
+        for (int k = 0; k < 4; ++k) entry_io<T>::store1(outputs + ((size_t)(l0 + k) * Bs + b) * 2, res[k].x, res[k].y);
     }
 }
 
@@ -278,6 +279,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
                                                      const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
                                                      int layout, int warp_agg, int red4, uint32_t skip, float in_bound, const int *__restrict__ limit) {
+    const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     uint32_t b, l0;
     map_thread<MIX>(L, b, l0);
@@ -298,7 +300,7 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
             load_row4(grad + ((size_t)b * L + l0) * 2, gv);
         } else {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * B + b) * 2);
+            for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * Bs + b) * 2);
         }
     }
 #pragma unroll

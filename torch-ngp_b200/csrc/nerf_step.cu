@@ -337,7 +337,8 @@ extern "C" {
 
 #define NGP_GRID1(n) ngp::div_round_up((uint32_t)(n), 256u), 256, 0, st
 
-int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *stream) {
+int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(xyzs && x01, "nerf_x01: null pointer argument");
@@ -347,7 +348,8 @@ int ngp_nerf_x01(const float *xyzs, float bound, float *x01, uint32_t M, void *s
     return NGP_OK;
 }
 
-int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, float *sigmas, void *cin, uint32_t M, void *stream) {
+int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, float *sigmas, void *cin, uint32_t M, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(h && dirs && sigmas && cin, "nerf_mid_forward: null pointer argument");
@@ -357,7 +359,8 @@ int ngp_nerf_mid_forward(const void *h, const float *dirs, float density_scale, 
     return NGP_OK;
 }
 
-int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream) {
+int ngp_nerf_rgb_forward(const void *c, float *rgbs, uint32_t M, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(c && rgbs, "nerf_rgb_forward: null pointer argument");
@@ -378,7 +381,8 @@ int ngp_nerf_loss(const float *image, const float *weights_sum, const float *gt,
     return NGP_OK;
 }
 
-int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream) {
+int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(grad_rgbs && rgbs && grad_c, "nerf_rgb_backward: null pointer argument");
@@ -389,7 +393,8 @@ int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_
 }
 
 int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *grad_cin, float density_scale, void *grad_h, uint32_t M,
-                          void *stream) {
+                          void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (M == 0) return NGP_OK;
     NGP_CHECK_ARG(grad_sigmas && h && grad_cin && grad_h, "nerf_mid_backward: null pointer argument");
@@ -399,7 +404,8 @@ int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *g
     return NGP_OK;
 }
 
-int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream) {
+int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     if (B == 0) return NGP_OK;
     NGP_CHECK_ARG(h && target && grad_h && loss_out, "sdf_loss: null pointer argument");
@@ -443,7 +449,8 @@ int ngp_found_inf(const void *g16, size_t n16, const float *g32, size_t n32, flo
 }
 
 int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, float *g32, void *shadow16, size_t n16, size_t n32,
-                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream) {
+                  const float *state, float beta1, float beta2, float eps, float grad_div, float weight_decay32, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
     using namespace ngp;
     NGP_CHECK_ARG(params && exp_avg && exp_avg_sq && state && (n16 == 0 || (g16 && shadow16)) && (n32 == 0 || g32), "adam_step: null pointer argument");
     NGP_CHECK_ARG(n16 % 4 == 0 && n32 % 4 == 0, "adam_step: segment sizes must be multiples of 4");
@@ -451,7 +458,7 @@ int ngp_adam_step(float *params, float *exp_avg, float *exp_avg_sq, void *g16, f
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n4 = (n16 + n32) / 4;
     uint32_t grid = (uint32_t)((n4 + 255) / 256);
-    const int per_sm = get_option("adam_blocks_per_sm", 0);
+    const int per_sm = grid_cap_blocks_per_sm();  // ngp_call_opts: share the SMs with another stream's kernels
     if (per_sm > 0 && grid > (uint32_t)(per_sm * sm_count())) grid = (uint32_t)(per_sm * sm_count());
     { NGP_PROF("k_adam", st); k_adam<<<grid, 256, 0, st>>>((float4 *)params, (float4 *)exp_avg, (float4 *)exp_avg_sq, (uint2 *)g16, (float4 *)g32,
                                                            (uint2 *)shadow16, n16 / 4, n32 / 4, state, beta1, beta2, eps, grad_div, weight_decay32); }

@@ -90,7 +90,9 @@ __global__ void __launch_bounds__(kMarchBlock) k_march_train_count(
     uint32_t sum = 0;
     for (uint32_t i = lo; i < hi; ++i) sum += __ldcg(ws->block_sums + i);
     uint32_t grand;
-    uint32_t run = block_excl_scan(sum, s_warp, grand) + (uint32_t)counter[0];
+    const uint32_t base = (uint32_t)counter[0];  // read by every thread BEFORE thread 0 bumps it below
+    uint32_t run = block_excl_scan(sum, s_warp, grand) + base;
+    __syncthreads();  // as in the warp variant (raymarch_warp.cuh): no thread may still be reading counter[0] when it is updated
     for (uint32_t i = lo; i < hi; ++i) {
         const uint32_t v = __ldcg(ws->block_sums + i);
         ws->block_sums[i] = run;

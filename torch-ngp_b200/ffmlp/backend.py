@@ -15,7 +15,9 @@ _ws_cache = {}
 
 
 def _workspace(device, nbytes):
-    key = (device.type, device.index)
+    """Zero-initialised dW accumulation workspace, one per (device, stream): the kernel leaves it zeroed for the next
+    call ON THE SAME STREAM; two streams (or two threads with their own streams) never share one."""
+    key = (device.type, device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.zeros(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
@@ -39,7 +41,7 @@ def _wdtype(weights):
 
 
 def ffmlp_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
-                  forward_buffer, outputs):
+                  forward_buffer, outputs, opts=None):
     _check_dims(B, input_dim, output_dim, hidden_dim, num_layers)
     abi.check_tensor(inputs, "inputs", _f16, "a half", B * input_dim)
     abi.check_tensor(weights, "weights", None, None, _n_weights(input_dim, output_dim, hidden_dim, num_layers))
@@ -50,21 +52,21 @@ def ffmlp_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_lay
         forward_buffer = None
     abi.check(abi.lib.ngp_ffmlp_forward(inputs.data_ptr(), weights.data_ptr(), _wdtype(weights), B, input_dim, output_dim, hidden_dim,
                                         num_layers, activation, output_activation, abi.ptr(forward_buffer), outputs.data_ptr(),
-                                        abi.stream()))
+                                        abi.stream(), opts))
 
 
 def ffmlp_inference(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
-                    inference_buffer, outputs):
+                    inference_buffer, outputs, opts=None):
     _check_dims(B, input_dim, output_dim, hidden_dim, num_layers)
     abi.check_tensor(inputs, "inputs", _f16, "a half", B * input_dim)
     abi.check_tensor(weights, "weights", None, None, _n_weights(input_dim, output_dim, hidden_dim, num_layers))
     abi.check_tensor(outputs, "outputs", _f16, "a half", B * output_dim)
     abi.check(abi.lib.ngp_ffmlp_inference(inputs.data_ptr(), weights.data_ptr(), _wdtype(weights), B, input_dim, output_dim, hidden_dim,
-                                          num_layers, activation, output_activation, None, outputs.data_ptr(), abi.stream()))
+                                          num_layers, activation, output_activation, None, outputs.data_ptr(), abi.stream(), opts))
 
 
 def ffmlp_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers, activation,
-                   output_activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights):
+                   output_activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, opts=None):
     _check_dims(B, input_dim, output_dim, hidden_dim, num_layers)
     nw = _n_weights(input_dim, output_dim, hidden_dim, num_layers)
     abi.check_tensor(grad, "grad", _f16, "a half", B * output_dim)
@@ -80,7 +82,7 @@ def ffmlp_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_d
     abi.check(abi.lib.ngp_ffmlp_backward(
         grad.data_ptr(), inputs.data_ptr(), weights.data_ptr(), _wdtype(weights), None, B, input_dim, output_dim, hidden_dim, num_layers,
         activation, output_activation, int(bool(calc_grad_inputs)), None, grad_inputs.data_ptr() if calc_grad_inputs else None,
-        grad_weights.data_ptr(), abi.dtype_code(grad_weights, "grad_weights"), ws.data_ptr(), ws.numel(), abi.stream()))
+        grad_weights.data_ptr(), abi.dtype_code(grad_weights, "grad_weights"), ws.data_ptr(), ws.numel(), abi.stream(), opts))
 
 
 def allocate_splitk(size):

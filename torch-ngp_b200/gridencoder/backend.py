@@ -29,8 +29,10 @@ def _check_common(inputs, embeddings, offsets):
         raise RuntimeError("inputs must be a float32 tensor")
 
 
-def grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners, interp,
-                        layout=abi.LAYOUT_LBC, offsets_host=None):
+def grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners, interp=0,
+                        layout=abi.LAYOUT_LBC, offsets_host=None, opts=None):
+    """Reference positional arguments (gridencoder.h:12).  Keyword extras of this library: layout (NGP_LAYOUT_*),
+    offsets_host (skips the cached D2H read), opts (abi.CallOpts: per-call options)."""
     _check_common(inputs, embeddings, offsets)
     abi.check_tensor(outputs, "outputs", embeddings.dtype, "the embeddings' dtype", B * L * C)
     abi.check_numel(inputs, B * D, "inputs")
@@ -41,11 +43,11 @@ def grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, 
     abi.check(abi.lib.ngp_grid_encode_forward(
         inputs.data_ptr(), embeddings.data_ptr(), offsets.data_ptr(), oh.ctypes.data, outputs.data_ptr(), B, D, C, L,
         float(S), H, abi.ptr(dy_dx), gridtype, int(bool(align_corners)), interp, abi.dtype_code(embeddings, "embeddings"),
-        layout, abi.stream()))
+        layout, abi.stream(), opts))
 
 
 def grid_encode_backward(grad, inputs, embeddings, offsets, grad_embeddings, B, D, C, L, S, H, dy_dx, grad_inputs, gridtype,
-                         align_corners, interp, layout=abi.LAYOUT_LBC, offsets_host=None):
+                         align_corners, interp=0, layout=abi.LAYOUT_LBC, offsets_host=None, opts=None):
     _check_common(inputs, embeddings, offsets)
     abi.check_tensor(grad, "grad", None, None, B * L * C)
     abi.check_tensor(grad_embeddings, "grad_embeddings", grad.dtype, "the grad's dtype", embeddings.numel())
@@ -58,7 +60,7 @@ def grid_encode_backward(grad, inputs, embeddings, offsets, grad_embeddings, B, 
     abi.check(abi.lib.ngp_grid_encode_backward(
         grad.data_ptr(), inputs.data_ptr(), embeddings.data_ptr(), offsets.data_ptr(), oh.ctypes.data,
         grad_embeddings.data_ptr(), B, D, C, L, float(S), H, abi.ptr(dy_dx), abi.ptr(grad_inputs), gridtype,
-        int(bool(align_corners)), interp, abi.dtype_code(grad, "grad"), layout, abi.stream()))
+        int(bool(align_corners)), interp, abi.dtype_code(grad, "grad"), layout, abi.stream(), opts))
 
 
 def grad_total_variation(inputs, embeddings, grad, offsets, weight, B, D, C, L, S, H, gridtype, align_corners):

@@ -5,6 +5,11 @@ Differences from the reference, all below the API:
   * the kernels read / write the point-major [B, L*C] layout directly, so the transposing copies of
     grid.py:69 (forward) and grid.py:87 (backward) do not exist;
   * coarse levels are served from shared memory and x-adjacent corners move as one wide access.
+
+Input gradients: with linear interpolation the reference's dy_dx is non-zero for the first input dimension only
+(`float pos_deriv[D] = {1.0f}`, gridencoder.cu:143).  The DEFAULT here reproduces that bit for bit, so that a model
+switched over from the reference trains the same; `GridEncoder(..., exact_input_grad=True)` opts into the
+mathematically exact derivative for all D dimensions (an extension, not reference behaviour).
 """
 import numpy as np
 import torch
@@ -22,7 +27,7 @@ class _grid_encode(Function):
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda")
     def forward(ctx, inputs, embeddings, offsets, per_level_scale, base_resolution, calc_grad_inputs=False, gridtype=0,
-                align_corners=False, interpolation=0):
+                align_corners=False, interpolation=0, exact_input_grad=False):
         # inputs [B, D] float in [0, 1]; embeddings [T, C]; offsets [L + 1] int32  ->  [B, L * C]
         inputs = inputs.contiguous()
         B, D = inputs.shape
@@ -39,8 +44,9 @@ class _grid_encode(Function):
         outputs = torch.empty(B, L * C, device=inputs.device, dtype=embeddings.dtype)
         dy_dx = torch.empty(B, L * D * C, device=inputs.device, dtype=embeddings.dtype) if calc_grad_inputs else None
 
+        opts = abi.call_opts(flags=abi.OPT_EXACT_INPUT_GRAD) if (exact_input_grad and calc_grad_inputs) else None
         _backend.grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners,
-                                     interpolation, layout=abi.LAYOUT_BLC)
+                                     interpolation, layout=abi.LAYOUT_BLC, opts=opts)
 
         ctx.save_for_backward(inputs, embeddings, offsets, dy_dx)
         ctx.dims = [B, D, C, L, S, H, gridtype, interpolation]
@@ -65,7 +71,7 @@ class _grid_encode(Function):
 
         if dy_dx is not None:
             grad_inputs = grad_inputs.to(inputs.dtype)
-        return grad_inputs, grad_embeddings, None, None, None, None, None, None, None
+        return grad_inputs, grad_embeddings, None, None, None, None, None, None, None, None
 
 
 grid_encode = _grid_encode.apply
@@ -73,7 +79,7 @@ grid_encode = _grid_encode.apply
 
 class GridEncoder(nn.Module):
     def __init__(self, input_dim=3, num_levels=16, level_dim=2, per_level_scale=2, base_resolution=16, log2_hashmap_size=19,
-                 desired_resolution=None, gridtype="hash", align_corners=False, interpolation="linear"):
+                 desired_resolution=None, gridtype="hash", align_corners=False, interpolation="linear", exact_input_grad=False):
         super().__init__()
         # the finest resolution desired at the last level, if provided, overrides per_level_scale
         if desired_resolution is not None:
@@ -91,6 +97,7 @@ class GridEncoder(nn.Module):
         self.interpolation = interpolation
         self.interp_id = _interp_to_id[interpolation]
         self.align_corners = align_corners
+        self.exact_input_grad = bool(exact_input_grad)  # False: the reference's dy_dx (see the module docstring)
 
         # level slices: min(2^log2_hashmap_size, dense size) rounded up to a multiple of 8 entries
         self.max_params = 2 ** log2_hashmap_size
@@ -122,7 +129,7 @@ class GridEncoder(nn.Module):
         prefix_shape = list(inputs.shape[:-1])
         inputs = inputs.view(-1, self.input_dim)
         outputs = grid_encode(inputs, self.embeddings, self.offsets, self.per_level_scale, self.base_resolution,
-                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id)
+                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id, self.exact_input_grad)
         return outputs.view(prefix_shape + [self.output_dim])
 
     @torch.amp.autocast("cuda", enabled=False)

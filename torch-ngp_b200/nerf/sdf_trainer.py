@@ -59,36 +59,27 @@ class SDFTrainer:
     def _forward_backward(self):
         s, lib, B = abi.stream(), abi.lib, self.B
         _ck(lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s))
-        # encoder(x, bound=1): (x + 1) / 2, applied by the grid kernels as they load the points (ngp_set_input_bound)
-        lib.ngp_set_input_bound(1.0)
-        try:
-            _ck(lib.ngp_grid_encode_forward(self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                            self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                            abi.LAYOUT_BLC, s))
-        finally:
-            lib.ngp_set_input_bound(0.0)
-        _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s))
+        # encoder(x, bound=1): (x + 1) / 2, applied by the grid kernels as they load the points (ngp_call_opts.input_bound)
+        _ck(lib.ngp_grid_encode_forward(self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                        self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                        abi.LAYOUT_BLC, s, abi.call_opts(input_bound=1.0)))
+        _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s, None))
         _ck(lib.ngp_sdf_loss(self.h.data_ptr(), self.sdfs.data_ptr(), B, self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(),
-                             self.state[_ST_LOSS:].data_ptr(), s))
+                             self.state[_ST_LOSS:].data_ptr(), s, None))
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, None, B, 32, 16, self.hid, self.nl, 0, 6, 1,
-                                   None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
+                                   None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, None))
         # unordered surface samples: a few thousand coarse cells take every point -> those levels go through shared memory
-        abi.set_option("hashgrid_bwd_smem_coarse", 1)
-        lib.ngp_set_input_bound(1.0)
-        try:
-            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
-                                             self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
-                                             None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
-        finally:
-            lib.ngp_set_input_bound(0.0)
-            abi.set_option("hashgrid_bwd_smem_coarse", 0)
+        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.points.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
+                                         self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
+                                         None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s,
+                                         abi.call_opts(input_bound=1.0, flags=abi.OPT_GRID_BWD_SMEM_COARSE)))
 
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
         _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
         _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
                               self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world),
-                              self.wd, s))
+                              self.wd, s, None))
         _ck(lib.ngp_step_end(self.state.data_ptr(), s))
 
     def _step_eager(self):
@@ -134,10 +125,10 @@ class SDFTrainer:
         n = points.shape[0]
         x01, enc, h = torch.empty(n, 3, device=self.dev), torch.empty(n, 32, dtype=torch.half, device=self.dev), torch.empty(n, 16, dtype=torch.half, device=self.dev)
         s = abi.stream()
-        _ck(abi.lib.ngp_nerf_x01(points.contiguous().data_ptr(), 1.0, x01.data_ptr(), n, s))
+        _ck(abi.lib.ngp_nerf_x01(points.contiguous().data_ptr(), 1.0, x01.data_ptr(), n, s, None))
         _ck(abi.lib.ngp_grid_encode_forward(x01.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data, enc.data_ptr(),
-                                            n, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
-        _ck(abi.lib.ngp_ffmlp_inference(enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, n, 32, 16, self.hid, self.nl, 0, 6, None, h.data_ptr(), s))
+                                            n, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s, None))
+        _ck(abi.lib.ngp_ffmlp_inference(enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, n, 32, 16, self.hid, self.nl, 0, 6, None, h.data_ptr(), s, None))
         return h[:, 0].float()
 
 

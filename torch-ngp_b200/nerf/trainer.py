@@ -142,40 +142,45 @@ class NGPTrainer:
         self._graph = None
 
     # ---- network pieces on raw buffers (shared by the step, the density query and the renderer) -----------
-    def _encode(self, xyzs, x01, enc, M):
+    def _opts(self, limit=None, grid=False):
+        """Per-call options (ngp_call_opts): `limit` = device int32 holding the number of rows really in use (the kernels
+        stop at min(M, *limit), read on the device); grid=True adds the [-bound, bound] -> [0, 1] input mapping of
+        GridEncoder.forward for the grid kernels.  Passed with every call: nothing is set process-wide."""
+        if limit is None and not (grid and self.fuse_x01):
+            return None
+        return abi.call_opts(batch_limit=limit, input_bound=self.bound if (grid and self.fuse_x01) else 0.0)
+
+    def _encode(self, xyzs, x01, enc, M, limit=None):
         """xyzs in [-bound, bound] -> hash-grid features.  The (x + bound) / (2 bound) of GridEncoder.forward is applied by
-        the grid kernels as they load the points (ngp_set_input_bound) when the fast kernels serve this table; otherwise
-        through the x01 buffer."""
+        the grid kernels as they load the points (ngp_call_opts.input_bound) when the fast kernels serve this table;
+        otherwise through the x01 buffer."""
         s = abi.stream()
         if self.fuse_x01:
             src = xyzs
-            abi.lib.ngp_set_input_bound(self.bound)
         else:
             src = x01
-            _ck(abi.lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s))
-        try:
-            _ck(abi.lib.ngp_grid_encode_forward(src.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
-                                                enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
-                                                abi.LAYOUT_BLC, s))
-        finally:
-            abi.lib.ngp_set_input_bound(0.0)
+            _ck(abi.lib.ngp_nerf_x01(xyzs.data_ptr(), self.bound, x01.data_ptr(), M, s, self._opts(limit)))
+        _ck(abi.lib.ngp_grid_encode_forward(src.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
+                                            enc.data_ptr(), M, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
+                                            abi.LAYOUT_BLC, s, self._opts(limit, grid=True)))
 
-    def _sigma_forward(self, enc, h, M, inference):
+    def _sigma_forward(self, enc, h, M, inference, limit=None):
         fn = abi.lib.ngp_ffmlp_inference if inference else abi.lib.ngp_ffmlp_forward
-        _ck(fn(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, h.data_ptr(), abi.stream()))
+        _ck(fn(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, h.data_ptr(), abi.stream(), self._opts(limit)))
 
-    def _color_forward(self, cin, c, M, inference):
+    def _color_forward(self, cin, c, M, inference, limit=None):
         fn = abi.lib.ngp_ffmlp_inference if inference else abi.lib.ngp_ffmlp_forward
-        _ck(fn(cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, c.data_ptr(), abi.stream()))
+        _ck(fn(cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, c.data_ptr(), abi.stream(), self._opts(limit)))
 
-    def _network_forward(self, M, inference=False):
+    def _network_forward(self, M, inference=False, limit=None):
         """xyzs, dirs -> sigmas, rgbs on the sample buffers (network_ff.py:51-74)."""
         s = abi.stream()
-        self._encode(self.xyzs, self.x01, self.enc, M)
-        self._sigma_forward(self.enc, self.h, M, inference)
-        _ck(abi.lib.ngp_nerf_mid_forward(self.h.data_ptr(), self.dirs.data_ptr(), self.density_scale, self.sigmas.data_ptr(), self.cin.data_ptr(), M, s))
-        self._color_forward(self.cin, self.c, M, inference)
-        _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s))
+        self._encode(self.xyzs, self.x01, self.enc, M, limit)
+        self._sigma_forward(self.enc, self.h, M, inference, limit)
+        _ck(abi.lib.ngp_nerf_mid_forward(self.h.data_ptr(), self.dirs.data_ptr(), self.density_scale, self.sigmas.data_ptr(), self.cin.data_ptr(), M, s,
+                                         self._opts(limit)))
+        self._color_forward(self.cin, self.c, M, inference, limit)
+        _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s, self._opts(limit)))
 
     # ---- one training step as a fixed launch sequence ---------------------------------------------------------
     def _march(self):
@@ -199,15 +204,12 @@ class NGPTrainer:
         counter = self.step_counter[0]
         lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s)
         # everything per-sample below runs on min(M, counter[0]) rows, read on the device: no host sync, no padded work
-        lib.ngp_set_batch_limit(counter.data_ptr())
-        try:
-            self._samples_forward_backward(counter)
-        finally:
-            lib.ngp_set_batch_limit(None)
+        self._samples_forward_backward(counter)
 
     def _samples_forward_backward(self, counter):
         s, N, M, lib = abi.stream(), self.N, self.M, abi.lib
-        self._network_forward(M)
+        lim = self._opts(counter)
+        self._network_forward(M, limit=counter)
         _ck(lib.ngp_composite_rays_train_forward(self.sigmas.data_ptr(), self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), M, N,
                                                  self.T_thresh, self.ws.data_ptr(), self.depth.data_ptr(), self.image.data_ptr(), s))
         _ck(lib.ngp_nerf_loss(self.image.data_ptr(), self.ws.data_ptr(), self.gt.data_ptr(), self.bg_color, N, self.state[_ST_SCALE:].data_ptr(),
@@ -219,28 +221,23 @@ class NGPTrainer:
                                                   self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), self.ws.data_ptr(),
                                                   self.depth.data_ptr(), self.image.data_ptr(), M, N, self.T_thresh, self.g_sigmas.data_ptr(),
                                                   self.g_rgbs.data_ptr(), s))
-        _ck(lib.ngp_nerf_rgb_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_c.data_ptr(), M, s))
+        _ck(lib.ngp_nerf_rgb_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_c.data_ptr(), M, s, lim))
         _ck(lib.ngp_ffmlp_backward(self.g_c.data_ptr(), self.cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 3, 0, 6, 1,
-                                   None, self.g_cin.data_ptr(), self.g_col.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
-        _ck(lib.ngp_nerf_mid_backward(self.g_sigmas.data_ptr(), self.h.data_ptr(), self.g_cin.data_ptr(), self.density_scale, self.g_h.data_ptr(), M, s))
+                                   None, self.g_cin.data_ptr(), self.g_col.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
+        _ck(lib.ngp_nerf_mid_backward(self.g_sigmas.data_ptr(), self.h.data_ptr(), self.g_cin.data_ptr(), self.density_scale, self.g_h.data_ptr(), M, s, lim))
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 2, 0, 6, 1,
-                                   None, self.g_enc.data_ptr(), self.g_sig.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s))
+                                   None, self.g_enc.data_ptr(), self.g_sig.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
         # table gradient: g16 was cleared by the previous optimizer step (k_adam consumes and zeroes it)
-        if self.fuse_x01:
-            lib.ngp_set_input_bound(self.bound)
-        try:
-            _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), (self.xyzs if self.fuse_x01 else self.x01).data_ptr(), self.table16.data_ptr(),
-                                             self.offsets.data_ptr(), self.offsets_host.ctypes.data, self.g16.data_ptr(), M, 3, self.C, self.L, self.S,
-                                             self.base_resolution, None, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s))
-        finally:
-            lib.ngp_set_input_bound(0.0)
+        _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), (self.xyzs if self.fuse_x01 else self.x01).data_ptr(), self.table16.data_ptr(),
+                                         self.offsets.data_ptr(), self.offsets_host.ctypes.data, self.g16.data_ptr(), M, 3, self.C, self.L, self.S,
+                                         self.base_resolution, None, None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s, self._opts(counter, grid=True)))
 
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
         _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
-        abi.set_option("adam_blocks_per_sm", self.adam_blocks_per_sm if self.overlap_optimizer else 0)
+        cap = abi.call_opts(grid_cap_blocks_per_sm=self.adam_blocks_per_sm) if self.overlap_optimizer else None
         _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
-                              self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world), 0.0, s))
+                              self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world), 0.0, s, cap))
         _ck(lib.ngp_step_end(self.state.data_ptr(), s))
 
     def _allreduce(self):
@@ -549,15 +546,13 @@ class NGPTrainer:
                                rs["rays_d"].data_ptr(), self.bound, self.dt_gamma, self.max_steps, self.cascade, self.H,
                                self.density_bitfield.data_ptr(), rs["nears"].data_ptr(), rs["fars"].data_ptr(), rs["xyzs"].data_ptr(),
                                rs["dirs"].data_ptr(), rs["deltas"].data_ptr(), noises.data_ptr(), s))
-        lib.ngp_set_batch_limit(rs["rows_dev"].data_ptr())
-        try:  # shade the samples (inference kernels: no activations kept)
-            self._encode(rs["xyzs"], rs["x01"], rs["enc"], M)
-            _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s))
-            _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s))
-            _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s))
-            _ck(lib.ngp_nerf_rgb_forward(rs["c"].data_ptr(), rs["rgbs"].data_ptr(), M, s))
-        finally:
-            lib.ngp_set_batch_limit(None)
+        # shade the samples (inference kernels: no activations kept); rows_dev bounds every kernel on the device
+        lim, rows_dev = self._opts(rs["rows_dev"]), rs["rows_dev"]
+        self._encode(rs["xyzs"], rs["x01"], rs["enc"], M, rows_dev)
+        _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s, lim))
+        _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s, lim))
+        _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s, lim))
+        _ck(lib.ngp_nerf_rgb_forward(rs["c"].data_ptr(), rs["rgbs"].data_ptr(), M, s, lim))
         _ck(lib.ngp_composite_rays(n_alive, n_dev.data_ptr(), n_step, T_thresh, rs["alive"][cur].data_ptr(), rs["rays_t"].data_ptr(),
                                    rs["sigmas"].data_ptr(), rs["rgbs"].data_ptr(), rs["deltas"].data_ptr(), rs["ws"].data_ptr(), rs["depth"].data_ptr(),
                                    rs["image"].data_ptr(), s))
@@ -571,7 +566,7 @@ class NGPTrainer:
         drop the finished rays -- on buffers kept per ray count, with the alive list compacted on the device
         (raymarching.compact_alive).  The alive count is read back only every `sync_every` iterations: in between, the
         launches are sized by an upper bound of the count (it never grows) and the kernels clamp to the count on the
-        device (n_alive_dev / ngp_set_batch_limit), so the host does not wait on the GPU 200 times per frame.  With
+        device (n_alive_dev / ngp_call_opts.batch_limit), so the host does not wait on the GPU 200 times per frame.  With
         use_graph the bound is rounded up a 2^(1/8) ladder and each group of `sync_every` iterations with the same
         (bound, n_step) is one CUDA graph, captured on first use and replayed for every later frame of the same size.
         A different cut of a ray's samples into iterations moves the points where the march resumes from the compositor's

@@ -18,6 +18,22 @@ LAYOUT_LBC, LAYOUT_BLC = 0, 1
 
 _u32, _f32, _int, _sz, _vp = ctypes.c_uint32, ctypes.c_float, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p
 
+OPT_EXACT_INPUT_GRAD, OPT_GRID_BWD_SMEM_COARSE = 1, 2
+
+
+class CallOpts(ctypes.Structure):
+    """ngp_call_opts (include/ngp_b200.h): per-call options, passed by pointer as the last argument of the per-sample
+    entry points (None = defaults).  Nothing here is process-wide."""
+    _fields_ = [("batch_limit", _vp), ("input_bound", _f32), ("flags", _u32), ("grid_cap_blocks_per_sm", ctypes.c_int32)]
+
+
+_op = ctypes.POINTER(CallOpts)
+
+
+def call_opts(batch_limit=None, input_bound=0.0, flags=0, grid_cap_blocks_per_sm=0):
+    """-> a CallOpts to pass as `opts` (ctypes converts it to a pointer); batch_limit: int32 device tensor or None."""
+    return CallOpts(None if batch_limit is None else batch_limit.data_ptr(), float(input_bound), int(flags), int(grid_cap_blocks_per_sm))
+
 # name -> (restype, argtypes): mirrors include/ngp_b200.h one to one (tests/test_abi.py checks the
 # header against this table and against the symbols the .so exports).
 SIGNATURES = {
@@ -26,11 +42,9 @@ SIGNATURES = {
     "ngp_set_option": (_int, [ctypes.c_char_p, _int]),
     "ngp_get_option": (_int, [ctypes.c_char_p, ctypes.POINTER(_int)]),
     "ngp_launch_count": (ctypes.c_longlong, []),
-    "ngp_set_batch_limit": (_int, [_vp]),
     "ngp_profile_collect": (_int, [ctypes.c_char_p, _sz]),
-    "ngp_set_input_bound": (_int, [_f32]),
-    "ngp_grid_encode_forward": (_int, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _u32, _int, _u32, _int, _int, _vp]),
-    "ngp_grid_encode_backward": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _vp, _u32, _int, _u32, _int, _int, _vp]),
+    "ngp_grid_encode_forward": (_int, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _u32, _int, _u32, _int, _int, _vp, _op]),
+    "ngp_grid_encode_backward": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _u32, _vp, _vp, _u32, _int, _u32, _int, _int, _vp, _op]),
     "ngp_grad_total_variation": (_int, [_vp, _vp, _vp, _vp, _f32, _u32, _u32, _u32, _u32, _f32, _u32, _u32, _int, _int, _vp]),
     "ngp_near_far_from_aabb": (_int, [_vp, _vp, _vp, _u32, _f32, _vp, _vp, _vp]),
     "ngp_sph_from_ray": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
@@ -47,26 +61,26 @@ SIGNATURES = {
     "ngp_composite_rays": (_int, [_u32, _vp, _u32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ngp_compact_alive_workspace_bytes": (_sz, [_u32]),
     "ngp_compact_alive": (_int, [_vp, _u32, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "ngp_ffmlp_forward": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
-    "ngp_ffmlp_inference": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp]),
-    "ngp_ffmlp_backward": (_int, [_vp, _vp, _vp, _int, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp, _vp, _vp, _int, _vp, _sz, _vp]),
+    "ngp_ffmlp_forward": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _op]),
+    "ngp_ffmlp_inference": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _op]),
+    "ngp_ffmlp_backward": (_int, [_vp, _vp, _vp, _int, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp, _vp, _vp, _int, _vp, _sz, _vp, _op]),
     "ngp_ffmlp_backward_workspace_bytes": (_sz, [_u32, _u32, _u32, _u32]),
     "ngp_allocate_splitk": (_int, [_sz]),
     "ngp_free_splitk": (_int, []),
     "ngp_sh_encode_forward": (_int, [_vp, _vp, _u32, _u32, _u32, _int, _vp]),
     "ngp_get_rays": (_int, [_vp, _u32, _f32, _f32, _f32, _f32, _u32, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ngp_sh_encode_backward": (_int, [_vp, _vp, _vp, _u32, _u32, _u32, _vp]),
-    "ngp_nerf_x01": (_int, [_vp, _f32, _vp, _u32, _vp]),
-    "ngp_nerf_mid_forward": (_int, [_vp, _vp, _f32, _vp, _vp, _u32, _vp]),
-    "ngp_nerf_rgb_forward": (_int, [_vp, _vp, _u32, _vp]),
+    "ngp_nerf_x01": (_int, [_vp, _f32, _vp, _u32, _vp, _op]),
+    "ngp_nerf_mid_forward": (_int, [_vp, _vp, _f32, _vp, _vp, _u32, _vp, _op]),
+    "ngp_nerf_rgb_forward": (_int, [_vp, _vp, _u32, _vp, _op]),
     "ngp_nerf_loss": (_int, [_vp, _vp, _vp, _f32, _u32, _vp, _vp, _vp, _vp, _vp, _vp]),
-    "ngp_nerf_rgb_backward": (_int, [_vp, _vp, _vp, _u32, _vp]),
-    "ngp_nerf_mid_backward": (_int, [_vp, _vp, _vp, _f32, _vp, _u32, _vp]),
+    "ngp_nerf_rgb_backward": (_int, [_vp, _vp, _vp, _u32, _vp, _op]),
+    "ngp_nerf_mid_backward": (_int, [_vp, _vp, _vp, _f32, _vp, _u32, _vp, _op]),
     "ngp_step_begin": (_int, [_vp, _f32, _f32, _vp]),
     "ngp_step_end": (_int, [_vp, _vp]),
     "ngp_found_inf": (_int, [_vp, _sz, _vp, _sz, _vp, _vp]),
-    "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _f32, _vp]),
-    "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp]),
+    "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _f32, _vp, _op]),
+    "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _op]),
     "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
     "ngp_density_ema": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
     "ngp_packbits_mean": (_int, [_vp, _u32, _vp, _f32, _f32, _vp, _vp]),
