@@ -167,6 +167,16 @@ NGP_API int ngp_composite_rays(uint32_t n_alive, const int *n_alive_dev, uint32_
 NGP_API size_t ngp_compact_alive_workspace_bytes(uint32_t n);
 NGP_API int ngp_compact_alive(const int *in, uint32_t n, const int *n_dev, int *out, int *n_out, void *workspace,
                       size_t workspace_bytes, void *stream);
+/* The same compaction for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO counterpart in the reference.  Takes no
+ * workspace: the scan scratch is a file-scope `static __device__` array inside the library (about 16 KB, held by every
+ * GPU that loads the library until the process exits), so the call performs no cudaMalloc / cudaFree / allocating
+ * library routine.  n > NGP_COMPACT_STATIC_MAX_N -> NGP_EINVAL with a message naming the limit.  Results are identical
+ * to ngp_compact_alive.  All calls on one device share that array: calls that overlap on the GPU (different streams or
+ * threads) race -- serialise them on one stream or use ngp_compact_alive with a workspace per stream.  in != out;
+ * n_out may alias n_dev. */
+#define NGP_COMPACT_STATIC_MAX_N 4194304 /* 2^22 ids: two 1920x1080 frames' worth of rays */
+NGP_API int ngp_compact_alive_static(const int *in, uint32_t n, const int *n_dev, int *out, int *n_out, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * ffmlp  (replaces ffmlp.h:8-14).  fp16 activations, fp32 accumulation on tcgen05 tensor cores (TMEM).

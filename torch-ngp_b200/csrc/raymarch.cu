@@ -259,3 +259,70 @@ __global__ void k_packbits_tail(const float *__restrict__ grid, uint32_t n_begin
 #include "raymarch_warp.cuh"
 #include "raymarch_infer.cuh"
 #include "raymarch_host.cuh"
+
+// ==========================================================================================================
+// ngp_compact_alive_static -- the same compaction with NO caller workspace and no allocation of any kind
+// ==========================================================================================================
+// No counterpart in the reference: added for callers that cannot allocate
+// (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The chained-scan scratch
+// (march_ws_t: done flag, grand total, one block total per 1024 ids) lives in a file-scope device array of a fixed,
+// modest size; every GPU that loads the library holds these ~16 KB until the process exits.
+//
+// In HOST code `g_compact_scratch` is only a host-side stand-in for the symbol, not a device address: passing it to a
+// kernel faults (or, where the GPU can reach host memory, silently uses the wrong memory).  The device address is
+// looked up once per device with cudaGetSymbolAddress, with that device current, and that pointer is what the kernels get.
+//
+// Every call on a device shares the one array.  The two words that must start at zero are cleared on the stream at the
+// start of each call; the block totals are fully rewritten by k_compact_count before k_compact_write reads them, so
+// the contents a previous call left behind are never read.  Calls that OVERLAP on the GPU (two streams or two threads
+// of one process on the same device) race on the array: serialise them on one stream, or use ngp_compact_alive with
+// one workspace per stream.
+#include <mutex>
+
+static __device__ __align__(256) uint32_t g_compact_scratch[2 + NGP_COMPACT_STATIC_MAX_N / (128 * 8)];
+static_assert(ngp::kMarchBlock * ngp::kCompactItems == 128 * 8, "NGP_COMPACT_STATIC_MAX_N assumes 1024 ids per block");
+
+namespace ngp {
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+march_ws_t *g_scratch_ptr[kMaxDevices] = {nullptr};
+
+// device address of g_compact_scratch on the CURRENT device (looked up once per device)
+int compact_scratch(march_ws_t **out) {
+    int dev = -1;
+    NGP_CHECK_CUDA(cudaGetDevice(&dev));
+    NGP_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "compact_alive_static: device index %d out of range", dev);
+    std::lock_guard<std::mutex> l(g_scratch_mu);
+    if (g_scratch_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        NGP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_compact_scratch));
+        NGP_CHECK_ARG(p != nullptr, "compact_alive_static: cudaGetSymbolAddress returned a null device address");
+        g_scratch_ptr[dev] = reinterpret_cast<march_ws_t *>(p);
+    }
+    *out = g_scratch_ptr[dev];
+    return NGP_OK;
+}
+}  // namespace
+}  // namespace ngp
+
+extern "C" int ngp_compact_alive_static(const int *in, uint32_t n, const int *n_dev, int *out, int *n_out, void *stream) {
+    using namespace ngp;
+    NGP_CHECK_ARG(in && out && n_out && in != out, "compact_alive_static: null or aliasing in/out");
+    NGP_CHECK_ARG(n <= (uint32_t)NGP_COMPACT_STATIC_MAX_N,
+                  "compact_alive_static: n = %u exceeds NGP_COMPACT_STATIC_MAX_N = %u (the fixed device scratch); use ngp_compact_alive "
+                  "with a caller workspace for larger lists", n, (uint32_t)NGP_COMPACT_STATIC_MAX_N);
+    march_ws_t *ws = nullptr;
+    const int rc = compact_scratch(&ws);
+    if (rc != NGP_OK) return rc;
+    const uint32_t nb = div_round_up(n ? n : 1u, (uint32_t)(kMarchBlock * kCompactItems));
+    cudaStream_t st = (cudaStream_t)stream;
+    NGP_CHECK_CUDA(cudaMemsetAsync(ws, 0, 2 * sizeof(uint32_t), st));  // done flag + grand total start at zero; no allocation
+    { NGP_PROF("k_compact_count", st); k_compact_count<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, n_out, ws); }
+    NGP_CHECK_LAUNCH();
+    { NGP_PROF("k_compact_write", st); k_compact_write<<<nb, kMarchBlock, 0, st>>>(in, n, n_dev, out, ws); }
+    NGP_CHECK_LAUNCH();
+    { NGP_PROF("k_compact_publish", st); k_compact_publish<<<1, 1, 0, st>>>(ws, n_out); }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}

@@ -19,6 +19,7 @@ LAYOUT_LBC, LAYOUT_BLC = 0, 1
 _u32, _f32, _int, _sz, _vp = ctypes.c_uint32, ctypes.c_float, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p
 
 OPT_EXACT_INPUT_GRAD, OPT_GRID_BWD_SMEM_COARSE = 1, 2
+COMPACT_STATIC_MAX_N = 4194304  # NGP_COMPACT_STATIC_MAX_N
 
 
 class CallOpts(ctypes.Structure):
@@ -61,6 +62,7 @@ SIGNATURES = {
     "ngp_composite_rays": (_int, [_u32, _vp, _u32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ngp_compact_alive_workspace_bytes": (_sz, [_u32]),
     "ngp_compact_alive": (_int, [_vp, _u32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ngp_compact_alive_static": (_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
     "ngp_ffmlp_forward": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _op]),
     "ngp_ffmlp_inference": (_int, [_vp, _vp, _int, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _op]),
     "ngp_ffmlp_backward": (_int, [_vp, _vp, _vp, _int, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp, _vp, _vp, _int, _vp, _sz, _vp, _op]),
