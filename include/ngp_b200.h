@@ -257,10 +257,12 @@ NGP_API int ngp_cast_f16(const float *src, void *dst, size_t n, void *stream);
  * NULL (= 0..N-1, every pixel); rays_o, rays_d [B,N,3] f32, directions normalised in camera space then rotated. */
 NGP_API int ngp_get_rays(const float *poses, uint32_t B, float fx, float fy, float cx, float cy, uint32_t W, const int *inds,
                  uint32_t inds_stride, uint32_t N, float *rays_o, float *rays_d, void *stream);
-/* grid = max(grid*decay, tmp) where both >= 0; *sum_out = sum(clamp(grid, 0)) */
-NGP_API int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, float *sum_out, void *stream);
-/* packbits with thresh = min(*sum * inv_count, density_thresh) read on the device; N = output bytes (N % 4 == 0) */
-NGP_API int ngp_packbits_mean(const float *grid, uint32_t N, const float *sum, float inv_count, float density_thresh, uint8_t *bitfield,
+/* nerf/renderer.py:582-584: grid = max(grid*decay, tmp) where both >= 0; *sum_out = sum(clamp(grid, 0)) carried in DOUBLE
+ * (device), so that mean = (float)(*sum_out / n) is the correctly rounded fp32 mean in any addition order */
+NGP_API int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, double *sum_out, void *stream);
+/* renderer.py:589-590: packbits with thresh = min((float)(*sum * inv_count), density_thresh) read on the device;
+ * N = output bytes (N % 4 == 0) */
+NGP_API int ngp_packbits_mean(const float *grid, uint32_t N, const double *sum, double inv_count, float density_thresh, uint8_t *bitfield,
                       void *stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -89,11 +89,44 @@ def build_one(key):
     return so
 
 
+# The reference's own L1 Python wrappers (autograd Functions + nn.Modules above the pybind11 ops).  They are staged -- byte
+# for byte, as build OUTPUT next to the compiled extensions, git-ignored like them -- so that the GPU box (which has no
+# /root/reference) can run them on top of this repository's backend.py shims (tests/test_reference_wrappers.py): the one
+# place where forward_buffer, the [L,B,C] layout and fp16 grad_weights are passed exactly the way the reference passes them.
+WRAPPERS = {
+    "gridencoder": ["gridencoder/grid.py"],
+    "raymarching": ["raymarching/raymarching.py"],
+    "ffmlp": ["ffmlp/ffmlp.py"],
+    "shencoder": ["shencoder/sphere_harmonics.py"],
+}
+
+
+def stage_wrappers():
+    """-> list of staged paths under oracle/_ref/py/ (empty when /root/reference is absent)."""
+    import shutil
+    if not os.path.isdir(REF):
+        return []
+    out = []
+    for pkg, files in WRAPPERS.items():
+        dst_dir = os.path.join(OUT, "py", pkg)
+        os.makedirs(dst_dir, exist_ok=True)
+        for f in files:
+            dst = os.path.join(dst_dir, os.path.basename(f))
+            shutil.copyfile(os.path.join(REF, f), dst)
+            out.append(dst)
+    print(f"[ref-ext] staged {len(out)} reference wrapper modules under {os.path.join(OUT, 'py')}", flush=True)
+    return out
+
+
 def build_all(keys=None, jobs=None):
     """The extensions side by side: the wall clock is the slowest one (ffmlp with its CUTLASS headers, ~8 min on 8 cores)
     instead of the sum (~25 min).  Returns {key: path or exception}."""
     import concurrent.futures as cf
     keys = list(keys or EXTS)
+    try:
+        stage_wrappers()
+    except OSError as e:  # the checker's convenience must not fail the build
+        print(f"[ref-ext] could not stage the reference wrappers: {e}", flush=True)
     out = {}
     with cf.ThreadPoolExecutor(max_workers=jobs or len(keys)) as ex:
         futs = {ex.submit(build_one, k): k for k in keys}

@@ -225,6 +225,24 @@ def packbits(grid, thresh):
     return out
 
 
+def density_grid_update(density_grid, tmp_grid, decay=0.95, density_thresh=10.0):
+    """The tail of NeRFRenderer.update_extra_state, /root/reference/nerf/renderer.py:582-590, on given grids:
+        valid = (grid >= 0) & (tmp >= 0)                         :582
+        grid[valid] = maximum(grid[valid] * decay, tmp[valid])   :583   (fp32, like the torch tensors)
+        mean_density = mean(clamp(grid, min=0))                  :584   (-1 cells count as 0)
+        thresh = min(mean_density, density_thresh)               :589
+        bitfield = packbits(grid, thresh)                        :590   (strict `>`, raymarching.cu:292-313)
+    -> (new grid [C, H^3] f32, mean_density (python float of the fp32 mean), bitfield uint8 [C * H^3 / 8]).
+    The mean is accumulated in float64 and rounded to fp32 once: the tie-breaker for fp32 reductions in any order."""
+    grid = np.array(density_grid, np.float32, copy=True)
+    tmp = np.asarray(tmp_grid, np.float32)
+    valid = (grid >= 0) & (tmp >= 0)
+    grid[valid] = np.maximum(grid[valid] * np.float32(decay), tmp[valid])
+    mean = float(np.float32(np.clip(grid, 0, None).astype(np.float64).mean()))
+    thresh = min(mean, float(density_thresh))
+    return grid, mean, packbits(grid, thresh)
+
+
 def march_rays_train(rays_o, rays_d, bound, density_bitfield, C, H, nears, fars, M, noises=None, dt_gamma=0.0,
                      max_steps=1024, counter=None):
     """Raw kernel semantics (no Python-side trimming).  -> xyzs[M,3], dirs[M,3], deltas[M,2], rays[N,3], counter[2]."""

@@ -62,6 +62,28 @@ def grid():
              outputs=out.float(), dy_dx=dy.float(), grad_embeddings=ge.float(), grad_inputs=gi.float())
 
 
+def grid_tv():
+    """grad_total_variation (gridencoder.cu:503-642): `inputs` in the table dtype (:505), grad accumulated into.  fp32 only: the
+    reference's half path is a no-op (its atomicAdd(at::Half*) is an empty stub, :21-26; the module always calls it in fp32)."""
+    ref = ref_ext.load("_gridencoder")
+    offsets, pls = cpu_ref.make_offsets(num_levels=8, log2_hashmap_size=12, base_resolution=8, desired_resolution=256)
+    L, C, D, H, S = 8, 2, 3, 8, float(np.log2(pls))
+    B, weight = 2048, 0.37
+    rng = np.random.default_rng(4)
+    x = rng.random((B, D)).astype(np.float32)
+    x[:4] = [[0, 0, 0], [1, 1, 1], [0.5, 0.5, 0.5], [-0.25, 0.5, 0.5]]
+    emb = rng.standard_normal((int(offsets[-1]), C)).astype(np.float32)
+    lv2 = torch.exp2(torch.arange(L, device=DEV, dtype=torch.float32) * torch.tensor(S, dtype=torch.float32, device=DEV))
+    out = {}
+    for dt, tag in ((torch.float32, "f32"),):
+        e, xi = T(emb).to(dt), T(x).to(dt)
+        g = torch.zeros_like(e)
+        ref.grad_total_variation(xi, e, g, T(offsets), weight, B, D, C, L, S, H, 0, False)
+        torch.cuda.synchronize()
+        out.update({f"x_{tag}": xi.float(), f"embeddings_{tag}": e.float(), f"grad_{tag}": g.float()})
+    save("grid_tv", level_exp2=lv2, offsets=offsets, per_level_scale=pls, base_resolution=H, weight=weight, **out)
+
+
 def raymarching():
     ref = ref_ext.load("_raymarching")
     H, C, bound = 32, 2, 2.0
@@ -175,7 +197,13 @@ def shenc():
 
 if __name__ == "__main__":
     cpu_ref.build()
+    only = sys.argv[1:]
+    if only:  # e.g. `make_golden.py grid_tv`: (re)generate the named fixtures only
+        for name in only:
+            globals()[name]()
+        sys.exit(0)
     grid()
+    grid_tv()
     raymarching()
     ffmlp()
     shenc()

@@ -106,6 +106,21 @@ def test_oracle_sh_vs_golden(oracle):
     assert np.allclose(oracle.sh_encode(g["dirs"], 4), g["outputs"], rtol=1e-6, atol=1e-6)
 
 
+def test_oracle_grid_tv_vs_golden(oracle):
+    """R4 pinned without a GPU: oracle.grad_total_variation against the reference extension's output (fp32; its half path is a
+    no-op, see tests/golden/make_golden.py::grid_tv)."""
+    g = load("grid_tv")
+    oracle.set_level_exp2(g["level_exp2"])
+    try:
+        grad = np.zeros_like(g["embeddings_f32"])
+        oracle.grad_total_variation(g["x_f32"], g["embeddings_f32"], grad, g["offsets"], float(g["weight"]), float(g["per_level_scale"]),
+                                    int(g["base_resolution"]))
+    finally:
+        oracle.set_level_exp2(None)
+    assert np.abs(g["grad_f32"]).max() > 0
+    assert rel(grad, g["grad_f32"]) < 1e-5
+
+
 # ---------------------------------------------------------------------------------------------- kernels vs golden (GPU)
 def _T(a):
     import torch

@@ -1,0 +1,112 @@
+"""No process-wide state behind the C ABI: two NGPTrainers with DIFFERENT bounds (so different
+ngp_call_opts.input_bound / batch_limit per call), a bare GridEncoder and an FFMLP module run at the same time, each on its own
+host thread and CUDA stream, and each has to produce what it produces when run alone.  With the round-1 library (ngp_set_batch_limit
+/ ngp_set_input_bound as process-wide atomics, one FFMLP dW workspace per device) the encoder thread got remapped inputs and
+truncated batches and the two backward passes shared one accumulator."""
+import threading
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+def _trainer(bound, seed):
+    import nerf
+    from nerf import synthetic
+    tr = nerf.NGPTrainer(bound=bound, num_rays=1024, use_graph=False, log2_hashmap_size=15, perturb=False, update_interval=0, seed=seed)
+    o, d, gt = synthetic.make_pool(16, 1024, DEV, seed=seed)
+    tr.set_pool(o, d, gt)
+    torch.manual_seed(seed)
+    tr.update_extra_state()  # the only consumer of torch's global RNG: done before the threads start
+    return tr
+
+
+def _run_trainer(tr, steps, out):
+    counts, losses = [], []
+    for _ in range(steps):
+        tr.next_pool_batch()
+        tr.train_step()
+        counts.append(int(tr.step_counter[0, 0].item()))
+        losses.append(tr.loss())
+    out["counts"], out["losses"], out["params"] = counts, losses, tr.params.clone()
+
+
+def _encoder_job(steps, out):
+    import gridencoder
+    import ffmlp
+    torch.manual_seed(7)
+    enc = gridencoder.GridEncoder(num_levels=16, desired_resolution=2048, log2_hashmap_size=17).to(DEV)
+    net = ffmlp.FFMLP(32, 16, 64, 2).to(DEV)
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    with torch.no_grad():
+        enc.embeddings.copy_(torch.rand(enc.embeddings.shape, device=DEV, generator=gen) * 2 - 1)
+    ys, ges, gws = [], [], []
+    for i in range(steps):
+        x = torch.rand(40000 + 17 * i, 3, device=DEV, generator=gen) * 2 - 1
+        g = torch.randn(x.shape[0], 16, device=DEV, generator=gen)
+        enc.embeddings.grad = net.weights.grad = None
+        feat = enc(x, bound=1)                      # fp32 table, no options: inputs in [-1, 1]
+        with torch.autocast("cuda", dtype=torch.half):
+            y = net(feat)
+        y.float().backward(g)
+        ys.append(y.detach().clone()); ges.append(enc.embeddings.grad.clone()); gws.append(net.weights.grad.clone())
+    out["y"], out["ge"], out["gw"] = ys, ges, gws
+
+
+def _in_thread(fn, *args):
+    """run fn on its own host thread and its own CUDA stream"""
+    err = []
+
+    def body():
+        try:
+            torch.cuda.set_device(0)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                fn(*args)
+            s.synchronize()
+        except BaseException as e:  # noqa: BLE001 -- re-raised in the test thread
+            err.append(e)
+    t = threading.Thread(target=body)
+    t.err = err
+    return t
+
+
+def test_two_trainers_and_bare_modules_run_concurrently():
+    steps = 12
+    # ---- each job alone ----
+    alone = [dict(), dict(), dict()]
+    _run_trainer(_trainer(1.0, 1), steps, alone[0])
+    _run_trainer(_trainer(2.0, 2), steps, alone[1])
+    _encoder_job(steps, alone[2])
+    torch.cuda.synchronize()
+    # ---- the same three jobs at the same time ----
+    tr1, tr2 = _trainer(1.0, 1), _trainer(2.0, 2)
+    torch.cuda.synchronize()
+    together = [dict(), dict(), dict()]
+    threads = [_in_thread(_run_trainer, tr1, steps, together[0]), _in_thread(_run_trainer, tr2, steps, together[1]),
+               _in_thread(_encoder_job, steps, together[2])]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    torch.cuda.synchronize()
+    for t in threads:
+        if t.err:
+            raise t.err[0]
+    for k in (0, 1):
+        # marching is deterministic given the occupancy grid: the sample counts of the first steps are exact; later ones follow the
+        # (fp16-atomic-noisy) parameters only through the loss, never through the grid (update_interval = 0)
+        assert together[k]["counts"] == alone[k]["counts"], k
+        assert all(abs(a - b) <= 2e-2 * abs(b) + 1e-6 for a, b in zip(together[k]["losses"], alone[k]["losses"])), (together[k]["losses"], alone[k]["losses"])
+        assert _rel(together[k]["params"][-2000:], alone[k]["params"][-2000:]) < 5e-2  # MLP weights after 12 Adam steps
+    assert alone[0]["counts"] != alone[1]["counts"]  # the two trainers really do different work
+    for i in range(steps):
+        assert torch.equal(together[2]["y"][i], alone[2]["y"][i]), i                      # forward: bit-exact
+        assert _rel(together[2]["ge"][i], alone[2]["ge"][i]) < 1e-5, i                    # fp32 atomics, order only
+        assert _rel(together[2]["gw"][i], alone[2]["gw"][i]) < 1e-5, i

@@ -168,16 +168,20 @@ def test_module_matches_torch_twin_and_reference_init():
     assert torch.equal(y2, y.detach())
 
 
-def test_vs_reference_extension():
-    """The reference's own _ffmlp kernels (fp16 accumulate) on identical tensors; both against the fp32 twin."""
+@pytest.mark.parametrize("nl,B", [(2, 4096), (2, 1 << 20), (3, 1 << 20)])
+def test_vs_reference_extension(nl, B):
+    """The reference's own _ffmlp kernels (fp16 accumulate) on identical tensors; both against the fp64 twin.  Sizes: the small
+    case, and BASELINE.json's 2^20 rows for both nets of the path (32 -> 64 x 2 -> 16 sigma net, 32 -> 64 x 3 -> 16 colour / SDF
+    net).  The upstream gradient is scaled like a mean loss (1 / sqrt(B / 4096)) so that fp16 weight gradients stay in range at
+    K = 2^20 rows."""
     from oracle import ref_ext, cpu_ref
     ref = ref_ext.load("_ffmlp")
     if ref is None:
         pytest.skip("oracle/_ref/_ffmlp.so not built")
-    in_dim, out_dim, hid, nl, B = 32, 16, 64, 2, 4096
+    in_dim, out_dim, hid = 32, 16, 64
     torch.manual_seed(5)
     x = (torch.randn(B, in_dim, device=DEV) * 0.5).half()
-    g = (torch.randn(B, out_dim, device=DEV) * 0.1).half()
+    g = (torch.randn(B, out_dim, device=DEV) * (0.1 / (B / 4096) ** 0.5)).half()
     w = _weights(in_dim, out_dim, hid, nl, seed=4, dtype=torch.float16)
     ref.allocate_splitk(nl + 1)
     y_ref = torch.empty(B, out_dim, device=DEV, dtype=torch.half)
@@ -207,8 +211,9 @@ def test_vs_reference_extension():
     print(f"backward distance to the twin (rel. Frobenius): dx tcgen05 {ex_new:.2e} ref {ex_ref:.2e}; dW tcgen05 {ew_new:.2e} ref {ew_ref:.2e}")
     assert ex_new < 5e-3 and ew_new < 5e-3
     assert ex_new <= ex_ref + 1e-3 and ew_new <= ew_ref + 1e-3
-    assert rel(gx.float().cpu().numpy(), gx_ref.float().cpu().numpy()) < 5e-2
-    assert rel(gw.float().cpu().numpy(), gw_ref.float().cpu().numpy()) < 5e-2
+    # against each other: bounded by the reference's own distance from the twin (it sums K = B products in half precision)
+    assert rel(gx.float().cpu().numpy(), gx_ref.float().cpu().numpy()) < max(5e-2, 2 * ex_ref)
+    assert rel(gw.float().cpu().numpy(), gw_ref.float().cpu().numpy()) < max(5e-2, 2 * ew_ref)
 
 
 ACTS = {"relu": 0, "exponential": 1, "sine": 2, "sigmoid": 3, "squareplus": 4, "softplus": 5, "none": 6}

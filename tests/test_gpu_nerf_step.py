@@ -370,13 +370,20 @@ def test_checkpoint_round_trip_in_the_reference_layout(tmp_path):
     path = str(tmp_path / "ngp.pth")
     tr.save_checkpoint(path)
     ck = torch.load(path)
-    assert {"model", "mean_count", "mean_density", "global_step"} <= set(ck)
+    assert {"model", "mean_count", "mean_density", "global_step", "epoch", "stats"} <= set(ck)
+    # what the reference's Trainer.load_checkpoint reads from the file (nerf/utils.py:1254-1272), transcribed: every access succeeds
+    ref_loader = dict(model=ck["model"], mean_count=ck["mean_count"], mean_density=ck["mean_density"], stats=ck["stats"], epoch=ck["epoch"],
+                      global_step=ck["global_step"])
+    assert isinstance(ref_loader["stats"], dict) and {"loss", "valid_loss", "results", "checkpoints", "best_result"} <= set(ref_loader["stats"])
+    assert isinstance(ref_loader["epoch"], int) and ref_loader["global_step"] == 3 and ref_loader["mean_density"] > 0
     assert {"encoder.embeddings", "encoder.offsets", "sigma_net.weights", "color_net.weights", "density_grid", "density_bitfield",
             "step_counter", "aabb_train", "aabb_infer"} == set(ck["model"])
     tr2 = _make(num_rays=1024, graph=False, perturb=False, update_interval=0)
     tr2.load_checkpoint(path)
     assert torch.equal(tr2.params, tr.params) and torch.equal(tr2.table16, tr.table16) and torch.equal(tr2.exp_avg, tr.exp_avg)
     assert torch.equal(tr2.density_bitfield, tr.density_bitfield) and torch.equal(tr2.state, tr.state) and tr2.global_step == tr.global_step
+    assert abs(tr2.mean_density() - tr.mean_density()) <= 1e-6 * tr.mean_density()  # restored, not 0
+    assert torch.equal(tr2.count_sum, tr.count_sum) and tr2.local_step == tr.local_step
     # the twin module of the reference topology loads the same state dict
     net = nerf.NeRFNetwork(bound=tr.bound, log2_hashmap_size=17).cuda()
     missing, unexpected = net.load_state_dict({k: v for k, v in ck["model"].items()}, strict=False)

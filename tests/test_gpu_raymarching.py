@@ -271,3 +271,151 @@ def test_mark_untrained_grid_matches_oracle_and_stays_unoccupied():
     bits = tr.density_bitfield.cpu().numpy()
     occ = np.unpackbits(bits, bitorder="little").astype(bool)
     assert not occ[marked.view(-1).cpu().numpy()].any()
+
+
+def _transcribed_update(grid, tmp, decay, density_thresh, packbits):
+    """nerf/renderer.py:582-590 with torch ops, as the reference executes them; packbits = the op to end with."""
+    grid = grid.clone()
+    valid_mask = (grid >= 0) & (tmp >= 0)
+    grid[valid_mask] = torch.maximum(grid[valid_mask] * decay, tmp[valid_mask])
+    mean_density = torch.mean(grid.clamp(min=0)).item()
+    return grid, mean_density, packbits(grid, min(mean_density, density_thresh))
+
+
+@pytest.mark.parametrize("cascade,H,density_thresh", [(1, 128, 10.0), (3, 64, 10.0), (2, 64, 0.2)])
+def test_density_grid_update_kernels_vs_transcription(oracle, cascade, H, density_thresh):
+    """R10: ngp_density_ema + ngp_packbits_mean (mean and threshold stay on the device) against (a) the torch transcription of
+    renderer.py:582-590 ending in the REFERENCE extension's packbits when it is built (else this library's, itself pinned
+    bit-exact to it), (b) the oracle twin.  Grid bit-exact.  Mean: the kernel carries the sum in double, so its fp32 mean is the
+    correctly rounded one (== the oracle's float64 evaluation); torch.mean's fp32 tree sum may sit a few ulp away (2e-7).
+    Bitfield bit-exact on every cell that is not inside that ulp-wide window around the threshold (at most a handful of 2 M)."""
+    import ngp_abi as abi
+    import raymarching
+    from oracle import ref_ext
+    ref = ref_ext.load("_raymarching")
+
+    def pack(grid, thresh):
+        bits = torch.empty(grid.numel() // 8, dtype=torch.uint8, device=DEV)
+        if ref is not None:
+            ref.packbits(grid.contiguous(), grid.numel() // 8, thresh, bits)
+            return bits
+        return raymarching.packbits(grid, thresh)
+
+    torch.manual_seed(cascade * 1000 + H)
+    n = H ** 3
+    grid = torch.rand(cascade, n, device=DEV) ** 4 * 30
+    grid[torch.rand(cascade, n, device=DEV) < 0.2] = -1.0   # untrained cells (mark_untrained_grid)
+    grid[torch.rand(cascade, n, device=DEV) < 0.1] = 0.0
+    tmp = torch.rand(cascade, n, device=DEV) ** 4 * 30
+    tmp[torch.rand(cascade, n, device=DEV) < 0.5] = -1.0    # cells the partial update did not probe
+    tmp[torch.rand(cascade, n, device=DEV) < 0.05] = 0.0
+    for it in range(3):  # the EMA is stateful: a few rounds
+        g_ref, mean_ref, bits_ref = _transcribed_update(grid, tmp, 0.95, density_thresh, pack)
+        g_orc, mean_orc, bits_orc = oracle.density_grid_update(grid.cpu().numpy(), tmp.cpu().numpy(), 0.95, density_thresh)
+        g = grid.clone()
+        msum = torch.zeros(1, dtype=torch.float64, device=DEV)
+        bits = torch.zeros(cascade * n // 8, dtype=torch.uint8, device=DEV)
+        abi.check(abi.lib.ngp_density_ema(g.data_ptr(), tmp.data_ptr(), 0.95, g.numel(), msum.data_ptr(), abi.stream()))
+        abi.check(abi.lib.ngp_packbits_mean(g.data_ptr(), g.numel() // 8, msum.data_ptr(), 1.0 / g.numel(), density_thresh, bits.data_ptr(), abi.stream()))
+        mean = float(np.float32(float(msum.item()) / g.numel()))
+        assert torch.equal(g, g_ref) and np.array_equal(g.cpu().numpy(), g_orc)
+        assert mean == mean_orc                          # correctly rounded fp32 mean, whatever the addition order
+        assert abs(mean - mean_ref) <= 3e-7 * mean_ref   # torch.mean's own fp32 reduction
+        assert np.array_equal(bits.cpu().numpy(), bits_orc)  # same mean -> same threshold -> bit-exact
+        thr = min(mean_ref, density_thresh)
+        far = ((g - thr).abs() > 1e-6 * thr).view(-1).cpu().numpy()   # cells torch.mean's last bits cannot flip
+        assert (~far).sum() <= 8
+        occ = np.unpackbits(bits.cpu().numpy(), bitorder="little").astype(bool)
+        assert np.array_equal(occ[far], np.unpackbits(bits_ref.cpu().numpy(), bitorder="little").astype(bool)[far])
+        assert not occ[(g < 0).view(-1).cpu().numpy()].any() and 0 < occ.sum() < occ.size
+        grid = g
+        tmp = torch.where(torch.rand_like(tmp) < 0.5, torch.rand_like(tmp) * 20, torch.full_like(tmp, -1.0))
+
+
+@pytest.mark.parametrize("bound", [1.0, 2.0])
+def test_update_extra_state_vs_transcription(bound):
+    """NGPTrainer.update_extra_state against a transcription of nerf/renderer.py:498-598 that draws the same torch random
+    numbers in the same order and queries the same density function, for the full sweep (iter_density < 16) and the partial
+    update (>= 16), 1 and 2 cascades.  Full sweep: every cell is written once -> density grid bit-exact.  Partial update: the
+    reference draws cells WITH duplicates (:554 "allow for duplication") and `tmp_grid[cas, indices] = sigmas` lets an
+    arbitrary one of them win, in the reference as here; cells probed once are bit-exact, cells probed several times must
+    hold one of their candidates' results (checked as min <= value <= max over the candidates).  The bitfield is the
+    reference packbits of the resulting grid at min(mean, density_thresh)."""
+    import nerf
+    import raymarching
+    import ngp_abi as abi
+    H = 32
+    tr = nerf.NGPTrainer(bound=bound, num_rays=256, use_graph=False, log2_hashmap_size=14, grid_size=H, density_thresh=0.9)
+    with torch.no_grad():  # a table with structure, so that densities spread around the threshold
+        tr.embeddings.copy_(torch.randn_like(tr.embeddings) * 0.5)
+        abi.check(abi.lib.ngp_cast_f16(tr.params.data_ptr(), tr.table16.data_ptr(), tr.n16, abi.stream()))
+
+    def reference_probes(density_grid, iter_density):
+        """renderer.py:506-574 -> per cascade (indices, sigmas) in the order the reference assigns them"""
+        probes = []
+        if iter_density < 16:
+            X = torch.arange(H, dtype=torch.int32, device=DEV).split(128)
+            for xs in X:
+                for ys in X:
+                    for zs in X:
+                        xx, yy, zz = torch.meshgrid(xs, ys, zs, indexing="ij")
+                        coords = torch.cat([xx.reshape(-1, 1), yy.reshape(-1, 1), zz.reshape(-1, 1)], dim=-1)
+                        indices = raymarching.morton3D(coords).long()
+                        xyzs = 2 * coords.float() / (H - 1) - 1
+                        for cas in range(tr.cascade):
+                            b = min(2 ** cas, tr.bound)
+                            half_grid_size = b / H
+                            cas_xyzs = xyzs * (b - half_grid_size)
+                            cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * half_grid_size
+                            probes.append((cas, indices, tr.density(cas_xyzs)))
+        else:
+            N = H ** 3 // 4
+            for cas in range(tr.cascade):
+                coords = torch.randint(0, H, (N, 3), device=DEV)
+                indices = raymarching.morton3D(coords).long()
+                occ_indices = torch.nonzero(density_grid[cas] > 0).squeeze(-1)
+                rand_mask = torch.randint(0, occ_indices.shape[0], [N], dtype=torch.long, device=DEV)
+                occ_indices = occ_indices[rand_mask]
+                occ_coords = raymarching.morton3D_invert(occ_indices)
+                indices = torch.cat([indices, occ_indices], dim=0)
+                coords = torch.cat([coords, occ_coords], dim=0)
+                xyzs = 2 * coords.float() / (H - 1) - 1
+                b = min(2 ** cas, tr.bound)
+                half_grid_size = b / H
+                cas_xyzs = xyzs * (b - half_grid_size)
+                cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * half_grid_size
+                probes.append((cas, indices, tr.density(cas_xyzs)))
+        return probes
+
+    for iter_density in (0, 1, 16, 17):
+        tr.iter_density = iter_density
+        before = tr.density_grid.clone()
+        torch.manual_seed(100 + iter_density)
+        probes = reference_probes(before, iter_density)
+        torch.manual_seed(100 + iter_density)
+        tr.update_extra_state()
+        assert tr.iter_density == iter_density + 1
+        # renderer.py:582-583 per candidate: a probed cell ends as max(old * decay, sigma) (old >= 0, sigma >= 0), else unchanged
+        assert len(probes) == tr.cascade  # H = 32 < S = 128: one block, one probe batch per cascade
+        lo, hi, cnt = before.clone(), before.clone(), torch.zeros_like(before)
+        for cas, idx, sig in probes:
+            old = before[cas, idx]
+            res = torch.where((old >= 0) & (sig >= 0), torch.maximum(old * 0.95, sig), old)
+            cnt[cas].index_add_(0, idx, torch.ones_like(sig))
+            hi[cas].scatter_reduce_(0, idx, res, "amax", include_self=False)  # untouched cells keep `before`
+            lo[cas].scatter_reduce_(0, idx, res, "amin", include_self=False)
+        g = tr.density_grid
+        once = cnt <= 1
+        assert torch.equal(g[once], lo[once]) and torch.equal(lo[once], hi[once]), iter_density      # bit-exact where defined
+        assert bool(((g >= lo) & (g <= hi)).all()), iter_density                                    # one of the candidates elsewhere
+        if iter_density < 16:
+            assert bool(once.all())
+        else:
+            assert 0.02 < float((~once).float().mean()) < 0.9
+        # renderer.py:584-590 on the grid that resulted
+        mean = float(np.float32(g.double().clamp(min=0).mean().item()))
+        assert tr.mean_density() == mean
+        bits_ref = raymarching.packbits(g, min(mean, tr.density_thresh))
+        assert torch.equal(tr.density_bitfield, bits_ref)
+        occ = np.unpackbits(bits_ref.cpu().numpy(), bitorder="little")
+        assert 0 < occ.sum() < occ.size

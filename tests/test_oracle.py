@@ -384,3 +384,17 @@ def test_mark_untrained_grid_oracle_follows_the_reference_loops():
     # the batched matmul may sum the 3-term products in another order: a cell exactly on a frustum face can flip
     assert (got != ref).mean() < 1e-4, float((got != ref).mean())
     assert 0 < (got == 0).sum() < got.size and got.max() <= 37
+
+
+def test_density_grid_update_twin(oracle):
+    """oracle.density_grid_update restates nerf/renderer.py:582-590: cells marked -1 (untrained) or not probed (tmp = -1) are
+    left alone, probed ones take max(decayed, new), the mean counts -1 as 0, the threshold is min(mean, density_thresh)."""
+    grid = np.array([[-1.0, 0.0, 4.0, 2.0, 0.5, -1.0, 8.0, 1.0]], np.float32)
+    tmp = np.array([[3.0, -1.0, 1.0, 5.0, 0.0, -1.0, -1.0, 0.96]], np.float32)
+    g, mean, bits = oracle.density_grid_update(grid, tmp, decay=0.95, density_thresh=10.0)
+    assert np.array_equal(g, np.array([[-1.0, 0.0, np.float32(4.0) * np.float32(0.95), 5.0, np.float32(0.5) * np.float32(0.95), -1.0, 8.0, 0.96]], np.float32))
+    assert np.isclose(mean, np.clip(g, 0, None).mean())
+    assert bits.tolist() == [int(sum(1 << i for i in range(8) if g[0, i] > mean))]
+    g2, mean2, bits2 = oracle.density_grid_update(grid, tmp, decay=0.95, density_thresh=0.9)  # the fixed threshold wins
+    assert bits2.tolist() == [int(sum(1 << i for i in range(8) if g[0, i] > 0.9))]
+    assert np.array_equal(grid[0, :2], [-1.0, 0.0])  # the input is not modified

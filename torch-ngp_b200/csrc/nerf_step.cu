@@ -297,10 +297,14 @@ __global__ void __launch_bounds__(256) k_get_rays(const float *__restrict__ pose
 }
 
 // ---- density grid maintenance (nerf/renderer.py:498-598) ----------------------------------------------------
-// grid = max(grid * decay, tmp) where both >= 0 ; partial sums of clamp(grid, 0) -> mean density
+// grid = max(grid * decay, tmp) where both >= 0 ; sum of clamp(grid, 0) -> mean density.
+// The sum is carried in DOUBLE (per thread, per warp, and in the one global accumulator): the reference takes
+// torch.mean of 2 M+ cells (renderer.py:584) and thresholds the grid with it (:589), so the mean has to be the
+// correctly rounded fp32 mean whatever the order of the additions -- a chain of fp32 atomics onto a ~1e7 running sum
+// was off by 2.5e-6 relative (measured), enough to flip cells that sit next to the threshold.
 __global__ void __launch_bounds__(256) k_density_ema(float *__restrict__ grid, const float *__restrict__ tmp, float decay, uint32_t n,
-                                                     float *__restrict__ sum_out) {
-    float s = 0.f;
+                                                     double *__restrict__ sum_out) {
+    double s = 0.0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         float g = grid[i];
         const float t = tmp[i];
@@ -308,18 +312,26 @@ __global__ void __launch_bounds__(256) k_density_ema(float *__restrict__ grid, c
             g = fmaxf(g * decay, t);
             grid[i] = g;
         }
-        s += fmaxf(g, 0.f);
+        s += (double)fmaxf(g, 0.f);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if ((threadIdx.x & 31) == 0) atomicAdd(sum_out, s);
+    __shared__ double s_part[8];
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += s_part[w];
+        atomicAdd(sum_out, t);
+    }
 }
 // packbits with a device-resident threshold: thresh = min(sum / n, density_thresh)  (renderer.py:584-590)
-__global__ void __launch_bounds__(256) k_packbits_mean(const float4 *__restrict__ grid4, uint32_t N4, const float *__restrict__ sum, float inv_n,
+__global__ void __launch_bounds__(256) k_packbits_mean(const float4 *__restrict__ grid4, uint32_t N4, const double *__restrict__ sum, double inv_n,
                                                        float density_thresh, uint32_t *__restrict__ bitfield32) {
     const uint32_t n = threadIdx.x + blockIdx.x * blockDim.x;
     if (n >= N4) return;
-    const float thresh = fminf(*sum * inv_n, density_thresh);
+    const float thresh = fminf((float)(*sum * inv_n), density_thresh);  // the fp32 mean, rounded once
     uint32_t bits = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -488,7 +500,7 @@ int ngp_get_rays(const float *poses, uint32_t B, float fx, float fy, float cx, f
     return NGP_OK;
 }
 
-int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, float *sum_out, void *stream) {
+int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, double *sum_out, void *stream) {
     using namespace ngp;
     if (n == 0) return NGP_OK;
     NGP_CHECK_ARG(grid && tmp && sum_out, "density_ema: null pointer argument");
@@ -496,13 +508,13 @@ int ngp_density_ema(float *grid, const float *tmp, float decay, uint32_t n, floa
     uint32_t g = div_round_up(n, 256u);
     const uint32_t cap = (uint32_t)sm_count() * 16;
     if (g > cap) g = cap;
-    NGP_CHECK_CUDA(cudaMemsetAsync(sum_out, 0, sizeof(float), st));
+    NGP_CHECK_CUDA(cudaMemsetAsync(sum_out, 0, sizeof(double), st));
     { NGP_PROF("k_density_ema", st); k_density_ema<<<g, 256, 0, st>>>(grid, tmp, decay, n, sum_out); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
 }
 
-int ngp_packbits_mean(const float *grid, uint32_t N, const float *sum, float inv_count, float density_thresh, uint8_t *bitfield, void *stream) {
+int ngp_packbits_mean(const float *grid, uint32_t N, const double *sum, double inv_count, float density_thresh, uint8_t *bitfield, void *stream) {
     using namespace ngp;
     if (N == 0) return NGP_OK;
     NGP_CHECK_ARG(grid && sum && bitfield && N % 4 == 0, "packbits_mean: null pointer argument or N not a multiple of 4");

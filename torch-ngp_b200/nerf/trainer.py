@@ -96,7 +96,7 @@ class NGPTrainer:
         self.density_bitfield = torch.zeros(self.cascade * self.H ** 3 // 8, dtype=torch.uint8, device=dev)
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=dev)
         self.count_sum = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.mean_sum = torch.zeros(1, device=dev)
+        self.mean_sum = torch.zeros(1, dtype=torch.float64, device=dev)  # sum of clamp(density_grid, 0), carried in double on the device
         self.mean_count, self.iter_density, self.local_step, self.global_step = -1, 0, 0, 0
 
         # ---- step state ----
@@ -393,42 +393,44 @@ class NGPTrainer:
 
     @torch.no_grad()
     def update_extra_state(self, decay=0.95):
+        """nerf/renderer.py:498-598.  Cell sampling follows the reference call for call (same torch RNG calls in the same
+        order, so a seeded run probes the same points): full sweep of all H^3 cells for the first 16 updates (:510-538, one
+        S = H block), then per cascade H^3/4 uniform cells + H^3/4 cells re-drawn from the occupied ones (:546-574).  The
+        EMA (:583), mean of clamp(min=0) (:584), min(mean, thresh) (:589) and packbits (:590) are two kernels with the mean
+        kept on the device; step-counter bookkeeping (:593-596) uses a device-side running sum."""
         self.flush()
         H, dev = self.H, self.dev
         tmp = -torch.ones_like(self.density_grid)
-        if self.iter_density < 16:  # full sweep
-            if not hasattr(self, "_all_coords"):
-                r = torch.arange(H, dtype=torch.int32, device=dev)
-                xx, yy, zz = torch.meshgrid(r, r, r, indexing="ij")
-                self._all_coords = torch.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], -1).contiguous()
-                self._all_indices = _raymarching.morton3D(self._all_coords).long()
-            coords_l, indices_l = [self._all_coords] * self.cascade, [self._all_indices] * self.cascade
-        else:  # partial: H^3/4 uniform cells + H^3/4 cells resampled from the occupied ones, per cascade
-            n = H ** 3 // 4
-            coords_l, indices_l = [], []
-            for cas in range(self.cascade):
-                coords = torch.randint(0, H, (n, 3), device=dev, dtype=torch.int32)
-                indices = _raymarching.morton3D(coords).long()
-                occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
-                if occ.shape[0] > 0:
-                    occ = occ[torch.randint(0, occ.shape[0], [n], dtype=torch.long, device=dev)]
-                    occ_coords = _raymarching.morton3D_invert(occ.int())
-                    indices = torch.cat([indices, occ])
-                    coords = torch.cat([coords, occ_coords])
-                coords_l.append(coords)
-                indices_l.append(indices)
-        for cas in range(self.cascade):
-            coords, indices = coords_l[cas], indices_l[cas]
+
+        def probe(cas, coords, indices):
             xyzs = 2 * coords.float() / (H - 1) - 1
             bound = min(2 ** cas, self.bound)
             hgs = bound / H
             cas_xyzs = xyzs * (bound - hgs)
             cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * hgs
             tmp[cas, indices] = self.density(cas_xyzs)
-        n_cells = self.density_grid.numel()
-        _ck(abi.lib.ngp_density_ema(self.density_grid.data_ptr(), tmp.data_ptr(), decay, n_cells, self.mean_sum.data_ptr(), abi.stream()))
-        _ck(abi.lib.ngp_packbits_mean(self.density_grid.data_ptr(), n_cells // 8, self.mean_sum.data_ptr(), 1.0 / n_cells, self.density_thresh,
-                                      self.density_bitfield.data_ptr(), abi.stream()))
+
+        if self.iter_density < 16:  # full sweep
+            if not hasattr(self, "_all_coords"):
+                r = torch.arange(H, dtype=torch.int32, device=dev)
+                xx, yy, zz = torch.meshgrid(r, r, r, indexing="ij")
+                self._all_coords = torch.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], -1).contiguous()
+                self._all_indices = _raymarching.morton3D(self._all_coords).long()
+            for cas in range(self.cascade):
+                probe(cas, self._all_coords, self._all_indices)
+        else:  # partial: H^3/4 uniform cells + H^3/4 cells resampled from the occupied ones, per cascade
+            n = H ** 3 // 4
+            for cas in range(self.cascade):
+                coords = torch.randint(0, H, (n, 3), device=dev)  # int64 like the reference's call (:549); morton3D takes .int()
+                indices = _raymarching.morton3D(coords.int()).long()
+                occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
+                if occ.shape[0] > 0:  # (the reference's randint(0, 0) raises on an empty grid)
+                    occ = occ[torch.randint(0, occ.shape[0], [n], dtype=torch.long, device=dev)]
+                    occ_coords = _raymarching.morton3D_invert(occ.int())
+                    indices = torch.cat([indices, occ])
+                    coords = torch.cat([coords, occ_coords])
+                probe(cas, coords, indices)
+        self._density_ema_packbits(tmp, decay)
         self.iter_density += 1
         # sample budget for the next interval (the one host read of the schedule, nerf/renderer.py:593-596)
         if self.local_step > 0:
@@ -439,6 +441,14 @@ class NGPTrainer:
         self.count_sum.zero_()
         self.local_step = 0
 
+    def _density_ema_packbits(self, tmp, decay):
+        """renderer.py:582-590 on the device: grid = max(grid * decay, tmp) where both >= 0; mean of clamp(grid, 0);
+        bitfield = grid > min(mean, density_thresh)."""
+        n_cells = self.density_grid.numel()
+        _ck(abi.lib.ngp_density_ema(self.density_grid.data_ptr(), tmp.data_ptr(), decay, n_cells, self.mean_sum.data_ptr(), abi.stream()))
+        _ck(abi.lib.ngp_packbits_mean(self.density_grid.data_ptr(), n_cells // 8, self.mean_sum.data_ptr(), 1.0 / n_cells, self.density_thresh,
+                                      self.density_bitfield.data_ptr(), abi.stream()))
+
     @torch.no_grad()
     def mark_untrained_grid(self, poses, intrinsic):
         """nerf/renderer.py:433-496: cells outside every training camera's frustum are set to -1 and stay unoccupied.
@@ -448,7 +458,8 @@ class NGPTrainer:
         return int((count == 0).sum().item())
 
     def mean_density(self):
-        return float(self.mean_sum.item()) / self.density_grid.numel()
+        """mean(clamp(density_grid, 0)) of the last update as the fp32 value the bitfield threshold used (renderer.py:584)."""
+        return float(np.float32(float(self.mean_sum.item()) / self.density_grid.numel()))
 
     # ---- checkpoints in the reference's layout (nerf/utils.py:1175-1311, state-dict names of network_ff.NeRFNetwork) ----
     def state_dict(self):
@@ -486,12 +497,17 @@ class NGPTrainer:
         return missing, unexpected
 
     def save_checkpoint(self, path, full=True):
-        """{'model', 'mean_count', 'mean_density', 'global_step'} as Trainer.save_checkpoint writes them (utils.py:1180-1199);
-        full adds this trainer's optimizer state (Adam moments, step / loss-scale state) under 'optimizer_b200'."""
-        state = {"global_step": self.global_step, "mean_count": self.mean_count, "mean_density": self.mean_density(), "model": self.state_dict()}
+        """{'epoch', 'global_step', 'stats', 'mean_count', 'mean_density', 'model'} as Trainer.save_checkpoint writes them
+        (utils.py:1180-1199; its load_checkpoint indexes 'stats', 'epoch' and 'global_step' unconditionally, :1270-1272, so
+        they are always present: the epoch counter and the stats lists are the reference Trainer's bookkeeping, kept here
+        only so that its loader accepts the file); full adds this trainer's optimizer state (Adam moments, step / loss-scale
+        state) under 'optimizer_b200'."""
+        state = {"epoch": getattr(self, "epoch", 0), "global_step": self.global_step,
+                 "stats": getattr(self, "stats", {"loss": [], "valid_loss": [], "results": [], "checkpoints": [], "best_result": None}),
+                 "mean_count": self.mean_count, "mean_density": self.mean_density(), "model": self.state_dict()}
         if full:
             state["optimizer_b200"] = {"exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(), "state": self.state.clone(),
-                                       "iter_density": self.iter_density, "local_step": self.local_step}
+                                       "iter_density": self.iter_density, "local_step": self.local_step, "count_sum": self.count_sum.clone()}
         torch.save(state, path)
 
     def load_checkpoint(self, path, model_only=False):
@@ -502,11 +518,21 @@ class NGPTrainer:
         self.load_state_dict(ck["model"], strict=False)
         if "mean_count" in ck:
             self.mean_count = ck["mean_count"]
+        if "mean_density" in ck:  # utils.py:1259-1260; kept as the running sum the device-side threshold reads
+            self.mean_sum.fill_(float(ck["mean_density"]) * self.density_grid.numel())
+        else:
+            self.mean_sum.copy_(self.density_grid.double().clamp(min=0).sum().view(1))
+        self.count_sum.zero_()  # sample counts of the interval that was running when the file was written are not in it
+        self.local_step = 0
         self.global_step = ck.get("global_step", self.global_step)
+        self.epoch, self.stats = ck.get("epoch", 0), ck.get("stats", getattr(self, "stats", None) or {})
         if not model_only and "optimizer_b200" in ck:
             o = ck["optimizer_b200"]
             self.exp_avg.copy_(o["exp_avg"]); self.exp_avg_sq.copy_(o["exp_avg_sq"]); self.state.copy_(o["state"])
-            self.iter_density, self.local_step = o["iter_density"], o["local_step"]
+            self.iter_density = o["iter_density"]
+            if "count_sum" in o:  # the running sample count and the number of steps it covers travel together
+                self.count_sum.copy_(o["count_sum"])
+                self.local_step = o["local_step"]
 
     # ---- inference rendering (nerf/renderer.py:346-431, the `not self.training` branch of run_cuda) ----------------
     def _render_state(self, N, rows):

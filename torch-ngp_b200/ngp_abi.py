@@ -85,7 +85,7 @@ SIGNATURES = {
     "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _op]),
     "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
     "ngp_density_ema": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
-    "ngp_packbits_mean": (_int, [_vp, _u32, _vp, _f32, _f32, _vp, _vp]),
+    "ngp_packbits_mean": (_int, [_vp, _u32, _vp, ctypes.c_double, _f32, _vp, _vp]),
     "ngp_umma_selftest": (_int, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp]),
 }
 
