@@ -381,7 +381,9 @@ def ffmlp_backward(grad, inputs, weights, input_dim, output_dim_padded, hidden_d
 
 
 # ------------------------------------------------------------------------------------------------
-# SH direction encoding, degree <= 4 (shencoder.cu:27-120 polynomial form)
+# SH direction encoding, degree <= 8 (shencoder.cu:27-120): bands l < 4 in the reference's polynomial form, bands 4..7
+# from the closed form the reference's table was generated from (its own comments give each entry in closed form,
+# e.g. :72 `3*sqrt(35)*xy*(x2 - y2)/(4*sqrt(pi))`): Y_l^{+-m} = N_l^m Q_l^m(z) {Re|Im}(x+iy)^m, Q_l^m = (-1)^m d^m P_l/dz^m
 # ------------------------------------------------------------------------------------------------
 def sh_encode(dirs, degree=4):
     d = np.asarray(dirs, dtype=np.float64)
@@ -407,4 +409,25 @@ def sh_encode(dirs, degree=4):
         out[:, 13] = 0.45704579946446572 * x * (1.0 - 5.0 * z2)
         out[:, 14] = 1.4453057213202769 * z * (x2 - y2)
         out[:, 15] = 0.59004358992664352 * x * (-x2 + 3.0 * y2)
+    if degree > 4:
+        from math import factorial, pi, sqrt
+        w = x + 1j * y
+        for m in range(degree):
+            wm = w ** m
+            qmm = (-1.0) ** m * float(np.prod(np.arange(2 * m - 1, 0, -2))) if m else 1.0
+            q2, q1 = None, np.full_like(z, qmm)
+            for l in range(m, degree):
+                if l == m:
+                    q = q1
+                elif l == m + 1:
+                    q = (2 * m + 1) * z * q1
+                else:
+                    q = ((2 * l - 1) * z * q1 - (l + m - 1) * q2) / (l - m)
+                if l > m:
+                    q2, q1 = q1, q
+                if l >= 4:
+                    n = sqrt((2 * l + 1) / (4 * pi) * factorial(l - m) / factorial(l + m)) * (sqrt(2) if m else 1.0)
+                    out[:, l * l + l + m] = n * q * wm.real
+                    if m:
+                        out[:, l * l + l - m] = n * q * wm.imag
     return out

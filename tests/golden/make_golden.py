@@ -193,6 +193,13 @@ def shenc():
     ref.sh_encode_forward(T(d), out, 256, 3, 4, None)
     torch.cuda.synchronize()
     save("shencoder_deg4", dirs=d, outputs=out)
+    # degree 8 (all 64 coefficients) with the reference's dy_dx table, on unit directions and on unnormalised points
+    d8 = np.concatenate([d, rng.standard_normal((256, 3)).astype(np.float32) * 0.7])
+    out8 = torch.empty(512, 64, device=DEV)
+    dy_dx = torch.empty(512, 64 * 3, device=DEV)
+    ref.sh_encode_forward(T(d8), out8, 512, 3, 8, dy_dx)
+    torch.cuda.synchronize()
+    save("shencoder_deg8", dirs=d8, outputs=out8, dy_dx=dy_dx)
 
 
 if __name__ == "__main__":

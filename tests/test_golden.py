@@ -104,6 +104,10 @@ def test_oracle_ffmlp_vs_golden(oracle, name):
 def test_oracle_sh_vs_golden(oracle):
     g = load("shencoder_deg4")
     assert np.allclose(oracle.sh_encode(g["dirs"], 4), g["outputs"], rtol=1e-6, atol=1e-6)
+    g = load("shencoder_deg8")  # bands 4..7: the reference evaluates expanded fp32 polynomials with coefficients up to ~700
+    o = oracle.sh_encode(g["dirs"], 8)
+    assert np.allclose(o[:, :16], g["outputs"][:, :16], rtol=1e-6, atol=1e-6)
+    assert np.abs(o - g["outputs"]).max() <= 1e-5 * max(1.0, np.abs(o).max())
 
 
 def test_oracle_grid_tv_vs_golden(oracle):

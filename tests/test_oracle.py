@@ -293,6 +293,34 @@ def test_sh_encode_orthonormal(oracle):
     y = oracle.sh_encode(d, 4)
     gram = 4 * np.pi * (y.T @ y) / d.shape[0]  # Monte-Carlo <Y_i, Y_j> over the sphere
     assert np.allclose(gram, np.eye(16), atol=0.03)
+    y = oracle.sh_encode(d, 8)
+    gram = 4 * np.pi * (y.T @ y) / d.shape[0]
+    assert np.allclose(gram, np.eye(64), atol=0.03)
+
+
+def test_sh_encode_high_bands_closed_forms(oracle):
+    """Bands 4..7 of the oracle against the closed forms the reference's table quotes in its comments (shencoder.cu:72-119),
+    on UNNORMALISED points: the entries are polynomials in (x, y, z), not only functions on the sphere."""
+    from math import pi, sqrt
+    rng = np.random.default_rng(1)
+    d = rng.standard_normal((2000, 3))
+    x, y, z = d.T
+    x2, y2, z2 = x * x, y * y, z * z
+    x4, y4, z4 = x2 * x2, y2 * y2, z2 * z2
+    x6, y6, z6 = x4 * x2, y4 * y2, z4 * z2
+    o = oracle.sh_encode(d, 8)
+    forms = {16: 3 * sqrt(35) * x * y * (x2 - y2) / (4 * sqrt(pi)),                                         # :72
+             20: 3 * (-30 * z2 + 35 * z4 + 3) / (16 * sqrt(pi)),                                            # :76
+             30: sqrt(11) * z * (-70 * z2 + 63 * z4 + 15) / (16 * sqrt(pi)),                                 # :87
+             37: 3 * sqrt(2002) * y * z * (10 * x2 * y2 - 5 * x4 - y4) / (32 * sqrt(pi)),                    # :95
+             42: sqrt(13) * (105 * z2 - 315 * z4 + 231 * z6 - 5) / (32 * sqrt(pi)),                          # :100
+             48: sqrt(6006) * (15 * x2 * y4 - 15 * x4 * y2 + x6 - y6) / (64 * sqrt(pi)),                     # :106
+             53: -3 * sqrt(35) * y * (3 * x2 - y2) * (13 * z2 * (11 * z2 - 3) - 27 * z2 + 3) / (64 * sqrt(pi)),  # :112
+             58: sqrt(70) * z * (x2 - y2) * (143 * z2 * (3 * z2 - 1) - 187 * z2 + 45) / (64 * sqrt(pi)),     # :117
+             63: 3 * sqrt(715) * x * (-35 * x2 * y4 + 21 * x4 * y2 - x6 + 7 * y6) / (64 * sqrt(pi))}         # :122
+    for k, v in forms.items():
+        assert np.abs(o[:, k] - v).max() <= 1e-12 * np.abs(v).max(), k
+    assert np.array_equal(o[:, :16], oracle.sh_encode(d, 4))
 
 
 def test_constant_step_t_sequence_closed_form():

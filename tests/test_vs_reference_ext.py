@@ -164,10 +164,12 @@ def test_grad_total_variation_vs_reference(oracle, dtype):
             assert float(g_r.float().abs().max()) == 0.0  # the reference's half path adds nothing (stubbed atomicAdd)
             g64 = np.zeros((int(offsets[-1]), C), np.float64)
             oracle.grad_total_variation(x.double().cpu().numpy(), emb.double().cpu().numpy(), g64, offsets, 0.37, pls, H, gridtype, ac)
-            # half atomics: a cell visited k times accumulates k half additions (k ~ 53 per coarse cell at 2^18 points: measured
-            # 1.0e-2 of the largest entry), so the bound is that of k roundings, not of one
+            # half atomics: a cell visited k times accumulates k half additions (k ~ 53 per coarse cell at 2^18 points and
+            # k ~ 60 for 3000 points on the 7 x 7 coarsest level of the 2-D case: measured 1.0e-2 / 1.3e-2 of the largest entry),
+            # so the bound is that of k roundings, not of one
+            k = B / float(offsets[1] - offsets[0])
             e_new = np.abs(g.double().cpu().numpy() - g64).max() / np.abs(g64).max()
-            assert e_new <= (2e-2 if B > 100000 else 4e-3), (D, C, L, e_new)
+            assert e_new <= (2.5e-2 if k > 8 else 4e-3), (D, C, L, k, e_new)
 
 
 # ------------------------------------------------------------------------------------------ marching
@@ -309,15 +311,21 @@ def test_inference_pair_vs_reference(scene):
 def test_sh_encoder_vs_reference():
     ref = _ref("_shencoder")
     import ngp_abi as abi
+    from oracle import cpu_ref
     torch.manual_seed(0)
     B = 10000
     d = torch.nn.functional.normalize(torch.randn(B, 3, device=DEV), dim=-1).contiguous()
-    for degree in (1, 2, 3, 4):
+    for degree in range(1, 9):
+        hi = degree > 4  # bands 4..7: closed form here, expanded fp32 polynomials (coefficients up to ~700) in the reference
         out_r = torch.empty(B, degree ** 2, device=DEV)
         ref.sh_encode_forward(d, out_r, B, 3, degree, None)
         out = torch.empty(B, degree ** 2, device=DEV)
         abi.check(abi.lib.ngp_sh_encode_forward(d.data_ptr(), out.data_ptr(), B, degree, degree ** 2, abi.DTYPE_F32, abi.stream()))
-        assert torch.allclose(out, out_r, rtol=1e-6, atol=1e-7)
+        assert torch.allclose(out[:, :16], out_r[:, :16], rtol=1e-6, atol=1e-7)
+        assert torch.allclose(out, out_r, rtol=1e-5, atol=1e-5), (degree, float((out - out_r).abs().max()))
+        if hi:  # tie-breaker: both against the fp64 oracle
+            o64 = torch.from_numpy(cpu_ref.sh_encode(d.cpu().numpy(), degree)).to(DEV)
+            assert float((out.double() - o64).abs().max()) <= 1e-5 and float((out_r.double() - o64).abs().max()) <= 1e-5
         # gradients w.r.t. the directions: the reference's dy_dx + kernel_sh_backward vs the fused backward
         dy_dx = torch.empty(B, degree ** 2 * 3, device=DEV)
         ref.sh_encode_forward(d, out_r, B, 3, degree, dy_dx)
@@ -326,7 +334,8 @@ def test_sh_encoder_vs_reference():
         ref.sh_encode_backward(g, d, B, 3, degree, dy_dx, gi_r)
         gi = torch.empty_like(d)
         abi.check(abi.lib.ngp_sh_encode_backward(g.data_ptr(), d.data_ptr(), gi.data_ptr(), B, degree, degree ** 2, abi.stream()))
-        assert torch.allclose(gi, gi_r, rtol=1e-5, atol=1e-5), (degree, float((gi - gi_r).abs().max()))
+        tol = 1e-5 * max(1.0, float(gi_r.abs().max()))  # 1e-5 of the gradient's scale (degree 8: |dY/dx| reaches ~30)
+        assert float((gi - gi_r).abs().max()) <= tol, (degree, float((gi - gi_r).abs().max()), tol)
     # module level: autograd through SHEncoder against autograd through the polynomial written in torch
     import shencoder
     dd = d[:512].clone().requires_grad_(True)

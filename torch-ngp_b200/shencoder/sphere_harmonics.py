@@ -1,4 +1,4 @@
-"""shencoder.SHEncoder -- same public API as /root/reference/shencoder/sphere_harmonics.py (:13-87), degree 1..4.
+"""shencoder.SHEncoder -- same public API as /root/reference/shencoder/sphere_harmonics.py (:13-87), degree 1..8.
 Gradients w.r.t. the directions (only when the input requires grad, as in the reference) come from one fused kernel that
 contracts the upstream gradient with the analytic derivatives -- no [B, degree^2 * 3] dy_dx buffer."""
 import torch
@@ -44,7 +44,7 @@ class SHEncoder(nn.Module):
     def __init__(self, input_dim=3, degree=4):
         super().__init__()
         assert input_dim == 3, "SH encoder only support input dim == 3"
-        assert 1 <= degree <= 4, "this build carries SH degrees 1..4"
+        assert 1 <= degree <= 8, "SH encoder only supports degree in [1, 8]"
         self.input_dim, self.degree, self.output_dim = input_dim, degree, degree ** 2
 
     def __repr__(self):
