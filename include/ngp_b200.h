@@ -183,13 +183,17 @@ NGP_API int ngp_compact_alive_static(const int *in, uint32_t n, const int *n_dev
  * Row-major [B, dim] activations (== the reference's "col-major [dim, B]"), weights flat, each layer
  * row-major [out, in] (ffmlp.cu:631-634), fp16 or fp32 (`weights_dtype`; fp32 is rounded to fp16 while
  * staged into shared memory).  Any B >= 0 (the ragged tail tile is masked; FFMLP.forward's padding copy,
- * ffmlp.py:157-159, is not needed).  hidden_dim in {16,32,64,128}, input_dim % 16 == 0 (<= 128),
- * output_dim % 16 == 0 (<= 128), num_layers >= 2 (num_layers + 1 matmuls), activation = any of the reference's
+ * ffmlp.py:157-159, is not needed).  hidden_dim in {16,32,64,128,256} (ffmlp.cu:651-658), input_dim % 16 == 0
+ * (<= 128; <= 256 at hidden_dim 256), output_dim % 16 == 0 (<= 128), num_layers >= 2 (num_layers + 1 matmuls), activation = any of the reference's
  * codes 0..6 (ffmlp.cu:22-32: ReLU, Exponential, Sine, Sigmoid, Squareplus, Softplus, None; Sine has no backward, as
  * in the reference, utils.h:552-556), output_activation 6 = None (all that FFMLP ever passes, ffmlp.py:107-108);
  * anything else -> NGP_EUNSUPPORTED.
- * forward_buffer / inference_buffer / backward_buffer are accepted for signature compatibility and may be
- * NULL: they are never written (activations live in shared memory; the backward recomputes the forward).
+ * hidden_dim <= 128: forward_buffer / inference_buffer / backward_buffer are accepted for signature compatibility
+ * and may be NULL: they are never written (activations live in shared memory; the backward recomputes the forward).
+ * hidden_dim 256 (neither the weights nor the weight-gradient accumulators fit on the SM next to a batch tile): the
+ * reference's own two-phase flow (ffmlp.cu:749-895) and buffers -- ngp_ffmlp_forward writes forward_buffer
+ * [num_layers, B, 256] when it is not NULL, ngp_ffmlp_backward REQUIRES that forward_buffer and a backward_buffer of
+ * the same shape (scratch; any contents), NGP_EINVAL otherwise; inference_buffer stays unused.
  * ------------------------------------------------------------------------------------------- */
 NGP_API int ngp_ffmlp_forward(const void *inputs, const void *weights, int weights_dtype, uint32_t B, uint32_t input_dim,
                       uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,

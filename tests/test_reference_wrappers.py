@@ -70,7 +70,7 @@ def test_reference_grid_encoder_module_on_shim():
     assert torch.allclose(a.embeddings.grad, b.embeddings.grad, rtol=1e-4, atol=1e-6 * a.embeddings.grad.abs().max().item())
 
 
-@pytest.mark.parametrize("cfg", [(32, 16, 64, 2), (32, 3, 64, 3), (16, 1, 32, 2)])
+@pytest.mark.parametrize("cfg", [(32, 16, 64, 2), (32, 3, 64, 3), (16, 1, 32, 2), (32, 3, 256, 2)])
 def test_reference_ffmlp_module_on_shim(cfg):
     import ffmlp
     ref = _wrapper("ffmlp")

@@ -3,8 +3,10 @@ names and the same positional arguments, forwarding to the C ABI of libngp_b200.
 
 Differences below the API (include/ngp_b200.h): `weights` may be fp32 (converted to fp16 while staged
 into shared memory, so no per-call cast kernel) or fp16; `forward_buffer` / `backward_buffer` /
-`inference_buffer` may be None -- the tcgen05 kernels keep every activation in shared memory / TMEM and
-recompute the forward inside the backward instead of round-tripping [num_layers, B, hidden] through HBM;
+`inference_buffer` may be None for hidden_dim <= 128 -- the tcgen05 kernels keep every activation in shared memory /
+TMEM and recompute the forward inside the backward instead of round-tripping [num_layers, B, hidden] through HBM
+(hidden_dim 256 uses both buffers in the reference's layout: neither its weights nor its weight-gradient accumulators
+fit on the SM next to a batch tile);
 `grad_weights` may be fp32 (no K = B reduction in half precision)."""
 import torch
 
@@ -79,9 +81,16 @@ def ffmlp_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_d
         abi.check_tensor(grad_inputs, "grad_inputs", _f16, "a half", B * input_dim)
     nbytes = abi.lib.ngp_ffmlp_backward_workspace_bytes(input_dim, output_dim, hidden_dim, num_layers)
     ws = _workspace(grad.device, nbytes)
+    fb = bb = None
+    if hidden_dim == 256:  # the one width that reads them (two-phase backward, csrc/ffmlp_wide.cu); narrower nets recompute on the SM
+        if forward_buffer is None or backward_buffer is None:
+            raise RuntimeError("ffmlp_backward: hidden_dim 256 needs forward_buffer and backward_buffer ([num_layers, B, 256] half)")
+        abi.check_tensor(forward_buffer, "forward_buffer", _f16, "a half", num_layers * B * hidden_dim)
+        abi.check_tensor(backward_buffer, "backward_buffer", _f16, "a half", num_layers * B * hidden_dim)
+        fb, bb = forward_buffer.data_ptr(), backward_buffer.data_ptr()
     abi.check(abi.lib.ngp_ffmlp_backward(
-        grad.data_ptr(), inputs.data_ptr(), weights.data_ptr(), _wdtype(weights), None, B, input_dim, output_dim, hidden_dim, num_layers,
-        activation, output_activation, int(bool(calc_grad_inputs)), None, grad_inputs.data_ptr() if calc_grad_inputs else None,
+        grad.data_ptr(), inputs.data_ptr(), weights.data_ptr(), _wdtype(weights), fb, B, input_dim, output_dim, hidden_dim, num_layers,
+        activation, output_activation, int(bool(calc_grad_inputs)), bb, grad_inputs.data_ptr() if calc_grad_inputs else None,
         grad_weights.data_ptr(), abi.dtype_code(grad_weights, "grad_weights"), ws.data_ptr(), ws.numel(), abi.stream(), opts))
 
 

@@ -5,8 +5,9 @@ Same constraints, parameter layout and seeded initialisation as the reference (o
 Parameter: layer 0 [hidden, in], num_layers-1 x [hidden, hidden], last [16, hidden], each row-major
 [out, in]; manual_seed(42), U(+-sqrt(3/hidden))).  Differences, all below the API:
   * no batch padding copy (ffmlp.py:157-159 cats up to 128 zero rows): the kernels mask the ragged tail;
-  * no forward_buffer / backward_buffer: activations stay in shared memory / TMEM and the backward
-    recomputes the forward (480 -> 96 B/point forward, ~2100 -> 160 B/point backward);
+  * no forward_buffer / backward_buffer for hidden_dim <= 128: activations stay in shared memory / TMEM and the
+    backward recomputes the forward (480 -> 96 B/point forward, ~2100 -> 160 B/point backward); hidden_dim 256
+    keeps both buffers in the reference's layout (csrc/ffmlp_wide.cu);
   * fp32 accumulation (TMEM) and fp32 weight gradients; weights are read as fp32 and rounded to fp16 while
     staged into shared memory, so there is no per-call cast of the parameter vector.
 """
@@ -37,9 +38,11 @@ class _ffmlp_forward(Function):
         outputs = torch.empty(B, output_dim, device=inputs.device, dtype=inputs.dtype)
         with torch.amp.autocast("cuda", enabled=False):
             if not inference:
+                # hidden_dim 256 keeps the reference's forward_buffer (ffmlp.py:33); narrower nets recompute in the backward
+                fb = torch.empty(num_layers, B, hidden_dim, device=inputs.device, dtype=inputs.dtype) if hidden_dim == 256 else None
                 _backend.ffmlp_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation,
-                                       output_activation, None, outputs)
-                ctx.save_for_backward(inputs, weights)
+                                       output_activation, fb, outputs)
+                ctx.save_for_backward(inputs, weights, *([fb] if fb is not None else []))
                 ctx.dims = (input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs)
             else:
                 _backend.ffmlp_inference(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation,
@@ -50,12 +53,14 @@ class _ffmlp_forward(Function):
     def backward(ctx, grad):
         B = grad.shape[0]
         grad = grad.to(torch.half).contiguous()
-        inputs, weights = ctx.saved_tensors
+        inputs, weights, *rest = ctx.saved_tensors
         input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs = ctx.dims
         grad_inputs = torch.empty_like(inputs) if calc_grad_inputs else None
         grad_weights = torch.empty_like(weights)  # fp32 for the fp32 Parameter; overwritten by the kernel
-        _backend.ffmlp_backward(grad, inputs, weights, None, B, input_dim, output_dim, hidden_dim, num_layers, activation,
-                                output_activation, calc_grad_inputs, None, grad_inputs, grad_weights)
+        fb = rest[0] if rest else None
+        bb = torch.empty_like(fb) if fb is not None else None  # ffmlp.py:70 (every row in use is written before it is read)
+        _backend.ffmlp_backward(grad, inputs, weights, fb, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                                output_activation, calc_grad_inputs, bb, grad_inputs, grad_weights)
         return grad_inputs, grad_weights, None, None, None, None, None, None, None, None
 
 

@@ -37,7 +37,7 @@ class NGPTrainer:
     def __init__(self, bound=1.0, num_rays=4096, device="cuda", lr=1e-2, grid_size=128, density_thresh=10.0, density_scale=1.0,
                  min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=128.0,
                  growth_interval=2000, decay_steps=30000, world_size=1, seed=0, use_graph=True, update_interval=16,
-                 num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False):
+                 num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False, init_samples_per_ray=512):
         """overlap_optimizer: defer the optimizer of step n to the start of step n+1 and run it on a second stream next to
         the ray marching of step n+1 (the marcher reads rays and the occupancy bitfield, never the parameters; Adam is
         HBM-bound, the marcher instruction-bound).  Same arithmetic in the same order; the parameters a caller reads
@@ -122,8 +122,9 @@ class NGPTrainer:
         self._graph = None
         # until the first density-grid interval has measured the sample count: room for 512 samples per ray (the reference
         # allocates N * max_steps and trims after a host read, raymarching.py:196-231); rays that do not fit are dropped
-        self._alloc_samples(N * 512)
+        self._alloc_samples(N * int(init_samples_per_ray))
         self._pool = None
+        self.overlap_events = None  # set to [] to collect (side start, after all-reduce, after optimizer, after march) CUDA events per step
 
     # ------------------------------------------------------------------------------------------------------
     def _alloc_samples(self, M):
@@ -279,11 +280,21 @@ class NGPTrainer:
             if self._side is None:
                 self._side = torch.cuda.Stream()
             self._side.wait_stream(main)  # the gradients of the previous step
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if self.overlap_events is not None else None
             self._run("march")          # submitted first: its blocks take their share of every SM before Adam's do
+            if ev:
+                ev[3].record(main)
             with torch.cuda.stream(self._side):
+                if ev:
+                    ev[0].record(self._side)
                 if self.world > 1:
                     self._allreduce()
+                if ev:
+                    ev[1].record(self._side)
                 self._run("opt")
+                if ev:
+                    ev[2].record(self._side)
+                    self.overlap_events.append(ev)
             self._pending = False
             main.wait_stream(self._side)
         else:
@@ -551,13 +562,14 @@ class NGPTrainer:
             rays_o=torch.empty(N, 3, **f32), rays_d=torch.empty(N, 3, **f32), nears=torch.empty(N, **f32), fars=torch.empty(N, **f32),
             ws=torch.empty(N, **f32), depth=torch.empty(N, **f32), image=torch.empty(N, 3, **f32), rays_t=torch.empty(N, **f32),
             alive=[torch.empty(N, dtype=torch.int32, device=dev), torch.empty(N, dtype=torch.int32, device=dev)],
-            iota=torch.arange(N, dtype=torch.int32, device=dev), n_dev=torch.zeros(1, dtype=torch.int32, device=dev),
-            rows_dev=torch.zeros(1, dtype=torch.int32, device=dev),
+            iota=torch.arange(N, dtype=torch.int32, device=dev), cnt2=torch.zeros(2, dtype=torch.int32, device=dev),
+            work=torch.zeros(2, dtype=torch.int64, device=dev),
             xyzs=torch.zeros(cap, 3, **f32), dirs=torch.zeros(cap, 3, **f32), deltas=torch.zeros(cap, 2, **f32), x01=torch.empty(cap, 3, **f32),
             enc=torch.empty(cap, 32, **f16), h=torch.empty(cap, 16, **f16), cin=torch.empty(cap, 32, **f16), c=torch.empty(cap, 16, **f16),
             sigmas=torch.empty(cap, **f32), rgbs=torch.empty(cap, 3, **f32),
             cws=torch.empty(max(1 << 16, lib.ngp_compact_alive_workspace_bytes(N)), dtype=torch.uint8, device=dev),
             noises=torch.zeros(N, **f32), zeros_n=torch.zeros(N, **f32), graphs={}, table=None)
+        rs["rows_dev"], rs["n_dev"] = rs["cnt2"][0:1], rs["cnt2"][1:2]  # two views of one buffer: one add keeps the frame totals
         cache[(N, rows)] = rs
         return rs
 
@@ -568,6 +580,7 @@ class NGPTrainer:
         n_dev = rs["n_dev"]
         rs["deltas"][:M].zero_()  # a zero delta ends a ray's samples in composite_rays (the reference allocates zeroed buffers every iteration)
         torch.mul(n_dev, n_step, out=rs["rows_dev"])  # sample rows really in use: bounds the shading kernels on the device
+        rs["work"].add_(rs["cnt2"])  # running totals of the frame: sample rows shaded, ray-iterations marched (for the roofline)
         _ck(lib.ngp_march_rays(n_alive, n_dev.data_ptr(), n_step, rs["alive"][cur].data_ptr(), rs["rays_t"].data_ptr(), rs["rays_o"].data_ptr(),
                                rs["rays_d"].data_ptr(), self.bound, self.dt_gamma, self.max_steps, self.cascade, self.H,
                                self.density_bitfield.data_ptr(), rs["nears"].data_ptr(), rs["fars"].data_ptr(), rs["xyzs"].data_ptr(),
@@ -618,7 +631,7 @@ class NGPTrainer:
         nears, fars = rs["nears"], rs["fars"]
         _ck(lib.ngp_near_far_from_aabb(rs["rays_o"].data_ptr(), rs["rays_d"].data_ptr(), self.aabb.data_ptr(), N, self.min_near, nears.data_ptr(),
                                        fars.data_ptr(), s))
-        rs["ws"].zero_(); rs["depth"].zero_(); rs["image"].zero_()
+        rs["ws"].zero_(); rs["depth"].zero_(); rs["image"].zero_(); rs["work"].zero_()
         rs["alive"][0].copy_(rs["iota"])
         rs["n_dev"].fill_(N)
         rs["rays_t"].copy_(nears)
@@ -665,4 +678,5 @@ class NGPTrainer:
         image = rs["image"] + (1 - rs["ws"]).unsqueeze(-1) * self.bg_color
         depth = torch.clamp(rs["depth"] - nears, min=0) / (fars - nears)
         self.last_render_iters = it
+        self.last_render_work = rs["work"]  # device tensor [sample rows shaded, ray-iterations marched] of this frame
         return image, depth
