@@ -41,6 +41,22 @@ def load_peaks():
         return {"hbm_gbs": 6650.0, "tflops": 1400.0, "tflops_burst": 1590.0, "source": "fallback"}
 
 
+# Tensor-pipe utilisation of the FFMLP kernels is a profiler counter, not something a timed run can read: the committed
+# `ncu --set full` capture (profiles/r2_ffmlp_ncu_summary.json) holds sm__pipe_tensor_cycles_active and
+# sm__ops_path_tensor_src_fp16_dst_fp32 (the tcgen05-era counters; the hmma ones read n/a on UTCHMMA kernels).
+def _tensor_pipe_note():
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_ffmlp_ncu_summary.json")) as f:
+            cap = json.load(f)
+        return {k: {"pipe_tensor_cycles_active_pct": v[0].get("tensor_pipe_active_pct"), "tensor_ops_pct_of_peak": v[0].get("tensor_ops_pct_of_peak"),
+                    "us_under_ncu": v[0].get("us")} for k, v in cap["kernels"].items() if k.startswith("k_ffmlp")} | {"source": "profiles/r2_ffmlp_ncu_summary.json"}
+    except Exception:
+        return None
+
+
+TENSOR_PIPE_NOTE = _tensor_pipe_note()
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons of one GPU during the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -235,6 +251,41 @@ class HashGridWorkload:
         s = 4
         return self.B * (4 * 3 + 8 * self.L * self.C * s + self.L * self.C * s) * 2 + self.T * self.C * s
 
+    def reference_ext(self):
+        """The reference's own CUDA extension (oracle/_ref/_gridencoder.so: gridencoder.cu compiled unmodified for sm_100a) on
+        the SAME tensors, outside every timed region of this repository's path -- a reported baseline beside cpu_baseline."""
+        try:
+            from oracle import ref_ext
+            ref = ref_ext.load("_gridencoder")
+        except Exception as e:  # the checker is absent: say so, measure nothing
+            return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+        if ref is None:
+            return {"unavailable": "oracle/_ref/_gridencoder.so not built"}
+        torch = self.torch
+        e, emb = self.enc, self.enc.embeddings.data
+        out = torch.empty(self.L, self.B, self.C, device=self.dev)
+        grad = self.grad.view(self.B, self.L, self.C).permute(1, 0, 2).contiguous()
+        g_emb = torch.zeros_like(emb)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
+        offs = e.offsets.to(self.dev)
+
+        def step():
+            ref.grid_encode_forward(self.x01, emb, offs, out, self.B, 3, 2, self.L, self.S, self.H, None, 0, False, 0)
+            g_emb.zero_()
+            ref.grid_encode_backward(grad, self.x01, emb, offs, g_emb, self.B, 3, 2, self.L, self.S, self.H, None, None, 0, False, 0)
+        for _ in range(3):
+            step()
+        ts = []
+        for _ in range(10):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); step(); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ms = float(np.median(ts))
+        return {"value": self.B / (ms * 1e-3) / 1e6, "unit": self.unit, "ms_per_step": ms, "kind": "reference CUDA extension, unmodified, sm_100a build",
+                "sample": "10 x fwd + table clear + bwd on the same 2^18 points and table, L2 flushed between steps, median"}
+
     # ---- CPU baseline: the oracle port (C + OpenMP), all host cores, bounded sample -------------
     def cpu_baseline(self, budget_s=15.0):
         from oracle import cpu_ref
@@ -330,6 +381,63 @@ class NerfTrainWorkload:
         self.tr.train_step(o[sl], d[sl], g[sl])
         return self.tr.loss()
 
+    def extras(self, steps, world):
+        """N > 1: where the collective sits.  CUDA events on the two streams of `steps` more steps: the all-reduce and the optimizer
+        run on the side stream beside march(n+1) on the main stream; `exposed` is what of them outlasts the march."""
+        if world == 1 or not self._overlap:
+            return {}
+        torch, tr = self.torch, self.tr
+        tr.overlap_events = []
+        for _ in range(steps):
+            self.step_device()
+        torch.cuda.synchronize()
+        ev, tr.overlap_events = tr.overlap_events, None
+        if not ev:
+            return {}
+        ar = [e[0].elapsed_time(e[1]) * 1e3 for e in ev]
+        opt = [e[1].elapsed_time(e[2]) * 1e3 for e in ev]
+        exposed = [max(0.0, e[3].elapsed_time(e[2]) * 1e3) for e in ev]  # march end -> optimizer end (negative: fully hidden)
+        loc = {"allreduce_us": float(np.mean(ar)), "optimizer_us": float(np.mean(opt)), "allreduce_plus_optimizer_exposed_us": float(np.mean(exposed))}
+        return {"collective": {k: max_over_ranks(v, world) for k, v in loc.items()} |
+                {"note": "CUDA events on the side stream (all-reduce, optimizer) and the main stream (march of the next step), max over ranks of the per-rank means; "
+                         "exposed = side-stream end minus march end, clamped at 0"}}
+
+    def single_gpu_same_global_batch(self, rank, world, steps, warmup):
+        """SURVEY.md 8(d) config 3's scaling denominator: rank 0 ALONE runs the global batch (2^18 rays/step) on one GPU with the
+        model state (parameters, occupancy grid) the group has just trained, while the other ranks wait at a barrier."""
+        import torch
+        import nerf
+        from nerf import synthetic
+        out = None
+        if rank == 0:
+            Ng = self.N * world
+            spr = max(8.0, self.tr.mean_count / self.N) if self.tr.mean_count > 0 else 256.0
+            tr = nerf.NGPTrainer(bound=1.0, num_rays=Ng, device=self.dev, world_size=1, seed=0, use_graph=not self.args.no_graph,
+                                 overlap_optimizer=not self.args.no_overlap, init_samples_per_ray=int(spr * 1.3) + 8)
+            tr.adam_blocks_per_sm = self.args.adam_blocks
+            tr.load_state_dict(self.tr.state_dict())
+            tr.exp_avg.copy_(self.tr.exp_avg); tr.exp_avg_sq.copy_(self.tr.exp_avg_sq); tr.state.copy_(self.tr.state)
+            tr.mean_sum.copy_(self.tr.mean_sum)
+            tr.iter_density, tr.update_interval = self.tr.iter_density, 0  # the group's grid as it is: identical occupancy, so identical samples per ray
+            views = max(16, 4 * Ng // 4096)
+            o, d, gt = synthetic.make_pool(views, 4 * Ng // views, self.dev, seed=1000)
+            tr.set_pool(o, d, gt)
+            for _ in range(max(3, warmup)):
+                tr.next_pool_batch(); tr.train_step()
+            torch.cuda.synchronize()
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            for a, b in ev:
+                a.record(); tr.next_pool_batch(); tr.train_step(); b.record()
+            torch.cuda.synchronize()
+            ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+            cnt = int(tr.step_counter[0, 0].item())
+            out = {"value": Ng / (ms * 1e-3), "unit": self.unit, "ms_per_step": ms, "rays_per_step": Ng, "n_gpus": 1, "steps": steps,
+                   "samples_per_step": cnt, "note": "rank 0 alone, same parameters and occupancy grid as the group run, density-grid update off during the timed steps"}
+            del tr
+            torch.cuda.empty_cache()
+        barrier_sync(world)
+        return out
+
     def profile_mode(self, on):
         """per-launch CUDA events cannot be recorded inside a graph replay: the profile pass runs the same launches eagerly."""
         self._saved = getattr(self, "_saved", self.tr.use_graph)
@@ -352,19 +460,22 @@ class NerfTrainWorkload:
         return n
 
     def roofline(self, prof, peaks, steps):
-        """Dominant kernel (largest share of the step) against the roofline that bounds it.  Algorithmic work per launch,
-        S = samples actually marched per step (not the padded capacity), s = 2 B (fp16 table / activations):
-          k_grid_fwd / k_grid_bwd  S * (12 + 8*L*C*s + L*C*s) bytes          
+        """Dominant kernel (largest share of the step) against the roofline that bounds it.  ALGORITHMIC work per launch
+        (SURVEY.md 8d), S = samples actually marched per step (not the padded capacity), s = 2 B (fp16 table / activations):
+          k_grid_fwd / k_grid_bwd  S * (12 + 8*L*C*s + L*C*s) bytes
           k_adam                   n16 * (3*4 read + 3*4 write + 2 grad + 2 shadow) + n32 * 32 bytes
           k_found_inf              n16 * 2 + n32 * 4 bytes
-          k_ffmlp_fwd              2 * W * S flop ; k_ffmlp_bwd  6 * W * S flop (recompute + dX + dW), W = weights of the net"""
+          k_ffmlp_fwd              2 * W * S flop
+          k_ffmlp_bwd              4 * W * S flop (dL/dx and dL/dW; + nothing for the forward the kernel RECOMPUTES per tile --
+                                   that work is reported separately as frac_incl_recompute = 6 * W * S)
+        W = weights of the net, averaged over the sigma and colour nets (one launch each per step)."""
         tr = self.tr
         S = max(1, tr.mean_count)
-        w_sig, w_col = tr.n_sig, tr.n_col
+        w_avg = (tr.n_sig + tr.n_col) / 2
         hb = S * (12 + 9 * tr.L * tr.C * 2)
         table = {"k_grid_fwd": ("hbm", hb), "k_grid_bwd": ("hbm", hb), "k_adam": ("hbm", tr.n16 * 28 + tr.n32 * 32),
                  "k_found_inf": ("hbm", tr.n16 * 2 + tr.n32 * 4),
-                 "k_ffmlp_fwd": ("tensor", 2 * (w_sig + w_col) / 2 * S), "k_ffmlp_bwd": ("tensor", 6 * (w_sig + w_col) / 2 * S)}
+                 "k_ffmlp_fwd": ("tensor", 2 * w_avg * S), "k_ffmlp_bwd": ("tensor", 4 * w_avg * S)}
         cand = {k: v for k, v in prof.items() if any(k.startswith(p) for p in table)}
         if not cand:
             return None
@@ -377,15 +488,30 @@ class NerfTrainWorkload:
             ach, peak, unit = work / sec / 1e9, peaks["hbm_gbs"], "GB/s"
         else:
             ach, peak, unit = work / sec / 1e12, peaks["tflops"], "TFLOP/s"
-        return {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": self._traffic(name, S),
-                "peak_source": peaks["source"], "algorithmic_work_per_launch": work, "us_per_launch": sec * 1e6,
-                "share_of_step_kernel_time": ms / total_ms if total_ms else None, "samples_per_step": S}
+        r = {"bound": bound, "kernel": name, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": self._traffic(name, S),
+             "peak_source": peaks["source"], "algorithmic_work_per_launch": work, "us_per_launch": sec * 1e6,
+             "share_of_step_kernel_time": ms / total_ms if total_ms else None, "samples_per_step": S}
+        if name.startswith("k_ffmlp_bwd"):
+            r["frac_incl_recompute"] = ach * 1.5 / peak  # 6 W S: what the tensor pipe executes (forward recomputed on the SM)
+        r["tensor_pipe"] = TENSOR_PIPE_NOTE
+        return r
+
+    def step_roofline(self, ms, peaks):
+        """Whole training step against the HBM roofline, SURVEY.md 8(d) config 2: (N * S_bar * 1,656 B + N * 120 B) / t_step."""
+        S = max(1, self.tr.mean_count)
+        a = S * 1656 + self.N * 120
+        ach = a / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                "algorithmic_bytes_per_step": a, "formula": "samples * 1656 B + rays * 120 B (SURVEY.md 8d, config 2)"}
 
     def _traffic(self, name, S):
         """DRAM bytes (read + write) per launch of that kernel from the committed `ncu --set full` capture
-        (profiles/r1_nerf_train_ncu_summary.json), scaled per sample to this run's sample count; None if absent."""
+        (profiles/r2_nerf_train_ncu_summary.json, else the round-1 one), scaled per sample to this run's sample count; None if absent."""
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_nerf_train_ncu_summary.json")) as f:
+            path = os.path.join(ROOT, "profiles", "r2_nerf_train_ncu_summary.json")
+            if not os.path.exists(path):
+                path = os.path.join(ROOT, "profiles", "r1_nerf_train_ncu_summary.json")
+            with open(path) as f:
                 cap = json.load(f)
             runs = next(v for k, v in cap["kernels"].items() if name.startswith(k))
             per = sum(r["dram_read_bytes"] + r["dram_write_bytes"] for r in runs) / len(runs)
@@ -464,6 +590,7 @@ class RenderWorkload:
         self.T = tr.T
         self.out_host = torch.empty(self.units_per_step, 3).pin_memory()
         self.depth_host = torch.empty(self.units_per_step).pin_memory()
+        self.work_sum, self.frames_done = torch.zeros(2, dtype=torch.int64, device=dev), 0
 
     def config(self, world):
         c = {"workload": f"inference render {self.W}x{self.Hh} frames, march_rays/composite_rays from a 128^3 bitfield + network_ff shading (configs[3])",
@@ -477,6 +604,8 @@ class RenderWorkload:
         o, d = self.frames[self.i % 4]
         self.i += 1
         self.tr.render(o, d, use_graph=getattr(self, "_graph_ok", True))
+        self.work_sum += self.tr.last_render_work
+        self.frames_done += 1
 
     def profile_mode(self, on):
         """per-launch CUDA events cannot be recorded inside a graph capture / replay: the profile pass runs the loop eagerly"""
@@ -491,17 +620,39 @@ class RenderWorkload:
         self.torch.cuda.synchronize()
         return float(self.out_host[0, 0])
 
+    # algorithmic bytes: per emitted sample 32 B march write + 24 B composite read + 588 B hash encode
+    # (fp16 table: 12 + 8*L*C*2 + L*C*2) + 192 B MLP in/out; per ray and loop iteration 44 B read + 28 B state read-modify-write
+    SAMPLE_BYTES = {"k_march_rays": 32, "k_composite_rays": 24, "k_grid_fwd": 588, "k_ffmlp_fwd": 96}
+    RAY_ITER_BYTES = {"k_march_rays": 44, "k_composite_rays": 28}
+
+    def _frame_work(self):
+        """(sample rows shaded, ray-iterations marched) per frame: device-side totals the render loop keeps, averaged over every frame so far"""
+        w = self.work_sum.cpu().double() / max(1, self.frames_done)
+        return float(w[0]), float(w[1])
+
     def roofline(self, prof, peaks, steps):
-        cand = {k: v for k, v in prof.items() if k.startswith(("k_grid_fwd", "k_ffmlp_fwd", "k_march_rays", "k_composite_rays"))}
+        cand = {k: v for k, v in prof.items() if k.startswith(tuple(self.SAMPLE_BYTES))}
         if not cand:
             return None
         name = max(cand, key=lambda k: cand[k][1])
+        key = next(k for k in self.SAMPLE_BYTES if name.startswith(k))
         cnt, ms = cand[name]
         total_ms = sum(v[1] for v in prof.values())
-        return {"bound": "hbm", "kernel": name, "achieved": None, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
+        rows, ray_iters = self._frame_work()
+        alg = rows * self.SAMPLE_BYTES[key] + ray_iters * self.RAY_ITER_BYTES.get(key, 0)  # per frame, all launches of that kernel
+        ach = alg / (ms / steps * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": None,
                 "peak_source": peaks["source"], "us_per_launch": ms / cnt * 1e3, "launches_per_step": cnt / steps,
+                "algorithmic_bytes_per_step": alg, "samples_per_frame": rows, "ray_iterations_per_frame": ray_iters,
                 "share_of_step_kernel_time": ms / total_ms if total_ms else None,
-                "note": "per-iteration sample counts vary; algorithmic bytes are reported for the training workload"}
+                "note": "all launches of the kernel in one frame together: achieved = algorithmic bytes of the frame's samples / their summed duration"}
+
+    def step_roofline(self, ms, peaks):
+        rows, ray_iters = self._frame_work()
+        a = rows * sum(self.SAMPLE_BYTES.values()) + rows * 96 + ray_iters * sum(self.RAY_ITER_BYTES.values())  # two MLP launches per sample: 2 x 96 B
+        ach = a / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "algorithmic_bytes_per_step": a,
+                "formula": "samples * (32 + 24 + 588 + 192) B + ray-iterations * (44 + 28) B (SURVEY.md 8d, config 4b)"}
 
     def cpu_baseline(self, budget_s=15.0):
         from oracle import cpu_ref, nerf_step_ref as R
@@ -578,10 +729,11 @@ class SDFWorkload:
     def profile_mode(self, on):
         self._saved = getattr(self, "_saved", self.tr.use_graph)
         self.tr.use_graph = False if on else self._saved
-        if hasattr(self.tr, "flush"):
-            if on:  # per-kernel durations are taken with the kernels one after the other
+        if hasattr(self.tr, "flush"):  # a trainer with a deferred optimizer: per-kernel durations are taken one after the other
+            if on:
                 self.tr.flush()
-            self.tr.overlap_optimizer = False if on else self._overlap
+                self._saved_overlap = self.tr.overlap_optimizer
+            self.tr.overlap_optimizer = False if on else getattr(self, "_saved_overlap", False)
 
     def launches_per_step(self):
         import ngp_abi as abi
@@ -596,7 +748,7 @@ class SDFWorkload:
         tr, B = self.tr, self.B
         hb = B * (12 + 9 * tr.L * tr.C * 2)
         table = {"k_grid_fwd": ("hbm", hb), "k_grid_bwd": ("hbm", hb), "k_adam": ("hbm", tr.n16 * 28 + tr.n32 * 32),
-                 "k_ffmlp_fwd": ("tensor", 2 * tr.n32 * B), "k_ffmlp_bwd": ("tensor", 6 * tr.n32 * B)}
+                 "k_ffmlp_fwd": ("tensor", 2 * tr.n32 * B), "k_ffmlp_bwd": ("tensor", 4 * tr.n32 * B)}  # algorithmic: recompute not counted
         cand = {k: v for k, v in prof.items() if any(k.startswith(p) for p in table)}
         if not cand:
             return None
@@ -679,10 +831,81 @@ def run_reference(wl, args, rank, world):
         wl.T = 6119864
     line = {"impl": "reference", "metric": wl.metric, "value": v, "unit": wl.unit, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
-            "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world) if hasattr(wl, "enc") or True else {},
+            "dtype": wl.dtype, "data": "synthetic",
+            "config": dict(wl.config(world), reference_arm_sample=cb.get("sample"),
+                           reference_arm_note="CPU restatement timed on a BOUNDED sample of the workload (see reference_arm_sample); the value is the "
+                                              "sample's own throughput, i.e. an extrapolation to the full batch assuming linear cost in rays / points"),
             "cpu_baseline": cb, "e2e": {"value": v, "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def measure(wl, args, rank, world, dev, peaks, steps, warmup, cpu_baseline=True, cpu_budget_s=15.0):
+    """One workload, the whole contract: warm-up, EXACTLY `steps` timed steps (device events, barrier + synchronize on both
+    sides, max over ranks), the per-kernel live profile of the same region, the end-to-end leg through the plugin API with
+    pinned host buffers, and (rank 0, one GPU) the CPU baseline.  -> the JSON line as a dict (rank 0), None elsewhere."""
+    import torch
+    import ngp_abi as abi
+    wl.setup(dev, rank, world)
+    do_flush = (getattr(wl, "l2_flush", True) or args.flush) and not args.no_flush
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if do_flush else None
+    wl.l2_note = ("flushed between steps (256 MiB memset outside the per-step events)" if do_flush else
+                  "not flushed: the data one step streams (see workload) is several times the 126 MB L2")
+    for _ in range(warmup):
+        wl.step_device()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(index=dev.index or 0) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    n0 = abi.launch_count()
+    ms_local = timed_region(wl, steps, world, flush)
+    launches = (abi.launch_count() - n0) / steps
+    if hasattr(wl, "launches_per_step") and wl.launches_per_step.__func__ is not HashGridWorkload.launches_per_step:
+        launches = wl.launches_per_step()
+    clocks = sampler.stop() if sampler else None
+    ms = max_over_ranks(ms_local, world)
+    units = sum_over_ranks(float(wl.units_per_step), world)
+
+    # per-kernel durations, live, same region re-run with the library's per-launch CUDA events enabled
+    if hasattr(wl, "profile_mode"):
+        wl.profile_mode(True)
+    abi.set_option("profile_events", 1)
+    timed_region(wl, steps, world, flush)
+    prof = abi.profile_collect()
+    abi.set_option("profile_events", 0)
+    if hasattr(wl, "profile_mode"):
+        wl.profile_mode(False)
+    roof = wl.roofline(prof, peaks, steps)
+
+    # end to end through the plugin API, host buffers
+    for _ in range(2):
+        wl.step_e2e()
+    ms_e2e = max_over_ranks(e2e_region(wl, steps, world), world)
+    extra = wl.extras(steps, world) if hasattr(wl, "extras") else {}
+
+    if rank != 0:
+        return None
+    scale = 1e-6 if wl.unit.startswith("M") else 1.0
+    line = {"metric": wl.metric, "value": units / (ms * 1e-3) * scale, "unit": wl.unit, "n_gpus": world, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
+            "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world),
+            "e2e": {"value": units / (ms_e2e * 1e-3) * scale, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
+                    "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": ms_e2e},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "kernels": {k: {"launches_per_step": c / steps, "us_per_launch": t / c * 1e3} for k, (c, t) in sorted(prof.items())}}
+    if hasattr(wl, "step_algorithmic_bytes"):
+        a = wl.step_algorithmic_bytes()
+        line["roofline_step"] = {"bound": "hbm", "achieved": a / (ms_local * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": a / (ms_local * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": a}
+    elif hasattr(wl, "step_roofline"):
+        line["roofline_step"] = wl.step_roofline(ms_local, peaks)
+    line.update(extra)
+    if world == 1 and cpu_baseline:
+        line["cpu_baseline"] = wl.cpu_baseline(budget_s=cpu_budget_s)
+        if hasattr(wl, "reference_ext"):
+            line["reference_ext"] = wl.reference_ext()
+    return line
 
 
 def main():
@@ -702,6 +925,8 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="nerf_train: optimizer(n) strictly before march(n+1) (default: side by side on two streams)")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=INT", help="ngp_set_option before setup (kernel A/B tests; development only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--only", action="store_true", help="the named workload alone: no `workloads` block with the other BASELINE configs (N=1) "
+                                                        "and no single-GPU leg at the global batch (N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -720,59 +945,29 @@ def main():
     for kv in args.opt:
         k, v = kv.split("=")
         abi.set_option(k, int(v))
-    wl.setup(dev, rank, world)
-    do_flush = (getattr(wl, "l2_flush", True) or args.flush) and not args.no_flush
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if do_flush else None
-    wl.l2_note = ("flushed between steps (256 MiB memset outside the per-step events)" if do_flush else
-                  "not flushed: the data one step streams (see workload) is several times the 126 MB L2")
+    line = measure(wl, args, rank, world, dev, peaks, args.steps, args.warmup, cpu_baseline=not args.no_cpu_baseline)
 
-    for _ in range(args.warmup):
-        wl.step_device()
-    torch.cuda.synchronize()
+    # N > 1 training: the scaling denominator SURVEY.md 8(d) config 3 names -- ONE GPU at the same global batch, same model state
+    if world > 1 and args.workload == "nerf_train" and not args.only and not args.rays:
+        single = wl.single_gpu_same_global_batch(rank, world, args.steps, args.warmup)
+        if rank == 0:
+            line["single_gpu_same_global_batch"] = single
+            line["scaling_reference"] = "single_gpu_same_global_batch (strong scaling: the global batch is fixed at 2^18 rays/step)"
 
-    sampler = ClockSampler(index=local) if rank == 0 else None
-    if sampler:
-        sampler.start()
-    n0 = abi.launch_count()
-    ms_local = timed_region(wl, args.steps, world, flush)
-    launches = (abi.launch_count() - n0) / args.steps
-    if hasattr(wl, "launches_per_step") and wl.launches_per_step.__func__ is not HashGridWorkload.launches_per_step:
-        launches = wl.launches_per_step()
-    clocks = sampler.stop() if sampler else None
-    ms = max_over_ranks(ms_local, world)
-    units = sum_over_ranks(float(wl.units_per_step), world)
-
-    # per-kernel durations, live, same region re-run with the library's per-launch CUDA events enabled
-    if hasattr(wl, "profile_mode"):
-        wl.profile_mode(True)
-    abi.set_option("profile_events", 1)
-    timed_region(wl, args.steps, world, flush)
-    prof = abi.profile_collect()
-    abi.set_option("profile_events", 0)
-    if hasattr(wl, "profile_mode"):
-        wl.profile_mode(False)
-    roof = wl.roofline(prof, peaks, args.steps)
-
-    # end to end through the plugin API, host buffers
-    for _ in range(2):
-        wl.step_e2e()
-    ms_e2e = max_over_ranks(e2e_region(wl, args.steps, world), world)
-
+    # N = 1: the other BASELINE.json configs in the same line (configs[0] first: it leads BASELINE.json's metric)
+    if world == 1 and not args.only and args.workload == DEFAULT_WORKLOAD:
+        del wl
+        torch.cuda.empty_cache()
+        line["workloads"] = {}
+        for name in ("hashgrid", "render", "sdf"):
+            sub = WORKLOADS[name](args)
+            sub_line = measure(sub, args, rank, world, dev, peaks, max(3, min(args.steps, 20)), 3, cpu_baseline=not args.no_cpu_baseline, cpu_budget_s=5.0)
+            for k in ("n_gpus", "higher_is_better", "vs_baseline", "data", "clocks"):
+                sub_line.pop(k, None)
+            line["workloads"][name] = sub_line
+            del sub
+            torch.cuda.empty_cache()
     if rank == 0:
-        scale = 1e-6 if wl.unit.startswith("M") else 1.0
-        line = {"metric": wl.metric, "value": units / (ms * 1e-3) * scale, "unit": wl.unit, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None,
-                "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world),
-                "e2e": {"value": units / (ms_e2e * 1e-3) * scale, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
-                        "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": ms_e2e},
-                "gpu_launches": launches, "clocks": clocks, "roofline": roof,
-                "kernels": {k: {"launches_per_step": c / args.steps, "us_per_launch": t / c * 1e3} for k, (c, t) in sorted(prof.items())}}
-        if hasattr(wl, "step_algorithmic_bytes"):
-            a = wl.step_algorithmic_bytes()
-            line["roofline_step"] = {"bound": "hbm", "achieved": a / (ms_local * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                     "frac": a / (ms_local * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": a}
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = wl.cpu_baseline()
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist

@@ -69,7 +69,13 @@ WANT = {
     "l1tex_throughput_pct": ("l1tex__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
     "l1tex2xbar_req_active_pct": ("l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed", 1.0),
     "dram_throughput_pct": ("dram__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
+    # tcgen05-era tensor counters (the hmma ones read n/a on UTCHMMA kernels): pipe busy cycles, executed tensor ops against the
+    # pipe's peak (16384 ops/clk/SM = 8192 FMA: what a full-rate M=128 N=256 K=16 instruction sustains), TMEM port busy cycles
     "tensor_pipe_active_pct": ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 1.0),
+    "tensor_ops_pct_of_peak": ("sm__ops_path_tensor_src_fp16_dst_fp32.avg.pct_of_peak_sustained_elapsed", 1.0),
+    "tensor_ops": ("sm__ops_path_tensor_src_fp16_dst_fp32.sum", 1.0),
+    "tmem_cycles_active_pct": ("sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", 1.0),
+    "sm_cycles_elapsed": ("sm__cycles_elapsed.avg", 1.0),
     "issue_active_pct": ("smsp__issue_active.avg.pct_of_peak_sustained_active", 1.0),
     "warps_active_pct": ("sm__warps_active.avg.pct_of_peak_sustained_active", 1.0),
     "l1_hit_rate_pct": ("l1tex__t_sector_hit_rate.pct", 1.0),
@@ -97,12 +103,13 @@ def full(rep, out_json, samples, note=""):
         for k, (m, scale) in WANT.items():
             if m not in idx or r[idx[m]] in ("", "n/a"):
                 continue
-            v = float(r[idx[m]].replace(",", ""))
+            try:
+                v = float(r[idx[m]].replace(",", ""))
+            except ValueError:
+                continue
+            if v != v:  # nan: a launch the profiler could not replay
+                continue
             e[k] = v * UNIT.get(units[idx[m]], 1.0) if scale is None or k == "us" else v
-        # every tensor-pipe counter the capture holds (the tcgen05 pipes have their own names; hmma-era ones read n/a)
-        tens = {h: r[idx[h]] for h in hdr if "tensor" in h and r[idx[h]] not in ("", "n/a", "0")}
-        if tens:
-            e["tensor_counters"] = tens
         st = {h.replace("smsp__average_warps_issue_stalled_", "").replace("_per_issue_active.ratio", ""): float(r[idx[h]]) for h in stall}
         e["top_stalls_per_issue"] = {k: round(v, 2) for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:4] if k != "selected"}
         kernels[name].append(e)
