@@ -243,6 +243,23 @@ NGP_API int ngp_nerf_loss(const float *image, const float *weights_sum, const fl
 NGP_API int ngp_nerf_rgb_backward(const float *grad_rgbs, const float *rgbs, void *grad_c, uint32_t M, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_nerf_mid_backward(const float *grad_sigmas, const void *h, const void *grad_cin, float density_scale, void *grad_h,
                           uint32_t M, void *stream, const ngp_call_opts *opts);
+/* The two nets of NeRFNetwork(--ff) with the glue between them fused into the tcgen05 MLP kernels (network_ff.py:51-74,
+ * activation.py:5-17, shencoder.cu:27-120; csrc/ffmlp.cu "IO" modes): same arithmetic as ngp_ffmlp_* + ngp_nerf_mid_* +
+ * ngp_nerf_rgb_* composed, bit for bit, without cin / c / grad_c / grad_cin in HBM and without the four elementwise launches.
+ * Topology fixed by the reference: 32 -> 64 x num_layers -> 16, ReLU, fp32 (or fp16) parameters in FFMLP's layout.
+ *   sigma_forward : enc [M,32] f16 -> h [M,16] f16 and sigmas [M] f32 = density_scale * exp(h[:,0])
+ *   color_forward : dirs [M,3] f32, h [M,16] f16 -> rgbs [M,3] f32 = sigmoid(colour net([SH4(dir) | h[:,1:16] | 0])[:, :3])
+ *   color_backward: grad_rgbs, rgbs [M,3], grad_sigmas [M] (from composite_rays_train_backward), dirs, h -> grad_weights of the
+ *                   colour net (overwritten; workspace as ngp_ffmlp_backward) and grad_h [M,16] f16 = dL/dh of the sigma net's
+ *                   output: column 0 from the density (trunc_exp backward), columns 1..15 through the colour net */
+NGP_API int ngp_nerf_sigma_forward(const void *enc, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float density_scale,
+                           void *h, float *sigmas, void *stream, const ngp_call_opts *opts);
+NGP_API int ngp_nerf_color_forward(const float *dirs, const void *h, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers,
+                           float *rgbs, void *stream, const ngp_call_opts *opts);
+NGP_API int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, const float *grad_sigmas, const float *dirs, const void *h,
+                            const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float density_scale, void *grad_h,
+                            void *grad_weights, int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream,
+                            const ngp_call_opts *opts);
 /* SDF regression loss (sdf/utils.py:217-225, loss.py:7-15 mape_loss, mean over B): h [B,16] f16 (column 0 = prediction),
  * target [B] f32 -> *loss_out += loss, grad_h [B,16] f16 (scaled by *loss_scale) */
 NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts);

@@ -69,6 +69,39 @@ def test_forward_backward_matches_autograd_path():
     assert _rel(tr.g_col, net.color_net.weights.grad) < 1e-2, _rel(tr.g_col, net.color_net.weights.grad)
 
 
+def test_fused_nets_equal_the_unfused_chain():
+    """The glue between the two MLPs fused into the tcgen05 kernels (ngp_nerf_sigma_forward / color_forward / color_backward:
+    trunc_exp, SH4 + geo-feature tile built in shared memory, sigmoid, and their backward, network_ff.py:51-74) against the same
+    step through ngp_ffmlp_* + ngp_nerf_mid_* + ngp_nerf_rgb_*: every per-sample tensor bit for bit; weight / table gradients up
+    to the order of their atomic sums.  Also the inference renderer, which shades through the same two entry points."""
+    from nerf import synthetic
+    out = []
+    for fused in (True, False):
+        torch.manual_seed(7)
+        tr = _make(fused_nets=fused)
+        assert tr.fused_nets == fused
+        tr.update_extra_state()
+        tr.next_pool_batch()
+        torch.manual_seed(8)
+        tr._forward_backward()
+        torch.cuda.synchronize()
+        out.append(tr)
+    a, b = out
+    n = int(a.step_counter[0, 0])
+    assert n == int(b.step_counter[0, 0]) and n > 1000
+    assert a.cin.shape[0] == 1 and b.cin.shape[0] == b.M  # the fused path does not even allocate the matrices between the nets
+    for name in ("h", "sigmas", "rgbs", "g_sigmas", "g_rgbs", "g_h", "g_enc"):
+        assert torch.equal(getattr(a, name)[:n], getattr(b, name)[:n]), name
+    assert torch.equal(a.image, b.image) and abs(float(a.state[7]) - float(b.state[7])) <= 1e-6 * abs(float(b.state[7]))
+    assert _rel(a.g_col, b.g_col) < 1e-5 and _rel(a.g_sig, b.g_sig) < 1e-5
+    assert _rel(a.g16.float(), b.g16.float()) < 2e-2
+    o, d = synthetic.frame_rays(96, 54, "cuda", pose_index=5)
+    b.load_state_dict(a.state_dict())
+    ia, da = a.render(o, d, use_graph=False)
+    ib, db = b.render(o, d, use_graph=False)
+    assert torch.equal(ia, ib) and torch.equal(da, db)
+
+
 def test_optimizer_matches_torch_adam_and_grad_scaler():
     tr = _make(num_rays=1024)
     tr.update_extra_state()

@@ -57,6 +57,79 @@ __device__ __forceinline__ void issue_dw(uint32_t d_tmem, const uint8_t *g_tiles
 
 
 // ==========================================================================================================
+// network_ff glue fused into the MLP kernels (/root/reference/nerf/network_ff.py:51-74, activation.py:5-17)
+// ==========================================================================================================
+// IO = 0  plain FFMLP (the reference operator).
+// IO = 1  sigma net forward: besides h [M,16] the drain writes sigmas = density_scale * exp(h0)  (trunc_exp, network_ff.py:60).
+// IO = 2  colour net: the A operand tile [SH4(dir) | h1..h15 | 0] (network_ff.py:63-67, shencoder.cu:27-120) is BUILT in shared
+//         memory from dirs [M,3] f32 and h [M,16] f16 -- the 64 B/sample `cin` matrix never exists in HBM; the forward drain
+//         writes rgbs = sigmoid(c0..c2) (rounded to half like torch.sigmoid of a half tensor, network_ff.py:73) instead of c;
+//         the backward builds its upstream tile from grad_rgbs * rgb (1 - rgb) and its dL/dx drain writes
+//         grad_h = [grad_sigma * density_scale * exp(clamp(h0, -15, 15)) | dL/dcin[16..30]] (activation.py:12-17) -- so the four
+//         elementwise kernels between the two nets (k_nerf_mid_fwd/bwd, k_nerf_rgb_fwd/bwd) and c / grad_c / grad_cin are gone.
+// Arithmetic is that of those kernels, expression for expression (nerf_step.cu): results are bit-identical.
+struct nerf_io_t {
+    const float *dirs;         // [M,3]
+    float *sigmas;             // IO 1 out
+    float *rgbs;               // IO 2 forward out; IO 2 backward in
+    const float *grad_rgbs;    // IO 2 backward in [M,3]
+    const float *grad_sigmas;  // IO 2 backward in [M]
+    float density_scale;
+};
+__device__ __forceinline__ float half_round(float v) { return __half2float(__float2half_rn(v)); }
+
+// row `row` of the colour net's input tile.  parts bit 0: SH chunks (columns 0..15), bit 1: geo chunks (columns 16..31).
+// Returns the word holding (h0, h1) when the geo part was built (the backward's trunc_exp gradient needs h0).
+__device__ __forceinline__ uint32_t nerf_color_row(uint8_t *tile, const float *__restrict__ dirs, const __half *__restrict__ h, uint32_t grow,
+                                                   bool ok, uint32_t row, uint32_t parts) {
+    uint8_t *t = tile + row * kTileRowBytes;
+    const uint32_t sw = row & 7u;
+    uint32_t h01 = 0u;
+    if (parts & 1u) {
+        float x = 0.f, y = 0.f, z = 0.f;
+        if (ok) { x = dirs[3 * (size_t)grow]; y = dirs[3 * (size_t)grow + 1]; z = dirs[3 * (size_t)grow + 2]; }
+        const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+        uint4 s0, s1;
+        s0.x = pack2(0.28209479177387814f, -0.48860251190291987f * y);
+        s0.y = pack2(0.48860251190291987f * z, -0.48860251190291987f * x);
+        s0.z = pack2(1.0925484305920792f * xy, -1.0925484305920792f * yz);
+        s0.w = pack2(0.94617469575755997f * z2 - 0.31539156525251999f, -1.0925484305920792f * xz);
+        s1.x = pack2(0.54627421529603959f * x2 - 0.54627421529603959f * y2, 0.59004358992664352f * y * (-3.0f * x2 + y2));
+        s1.y = pack2(2.8906114426405538f * xy * z, 0.45704579946446572f * y * (1.0f - 5.0f * z2));
+        s1.z = pack2(0.3731763325901154f * z * (5.0f * z2 - 3.0f), 0.45704579946446572f * x * (1.0f - 5.0f * z2));
+        s1.w = pack2(1.4453057213202769f * z * (x2 - y2), 0.59004358992664352f * x * (-x2 + 3.0f * y2));
+        if (!ok) s0 = s1 = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4 *>(t + ((0u ^ sw) << 4)) = s0;
+        *reinterpret_cast<uint4 *>(t + ((1u ^ sw) << 4)) = s1;
+    }
+    if (parts & 2u) {
+        uint4 a = make_uint4(0u, 0u, 0u, 0u), b = a;
+        if (ok) { a = __ldg(reinterpret_cast<const uint4 *>(h) + 2 * (size_t)grow); b = __ldg(reinterpret_cast<const uint4 *>(h) + 2 * (size_t)grow + 1); }
+        h01 = a.x;
+        uint4 g0, g1;  // geo_feat = h[1..15] shifted down by one half, then a zero pad
+        g0.x = __byte_perm(a.x, a.y, 0x5432); g0.y = __byte_perm(a.y, a.z, 0x5432); g0.z = __byte_perm(a.z, a.w, 0x5432); g0.w = __byte_perm(a.w, b.x, 0x5432);
+        g1.x = __byte_perm(b.x, b.y, 0x5432); g1.y = __byte_perm(b.y, b.z, 0x5432); g1.z = __byte_perm(b.z, b.w, 0x5432); g1.w = b.w >> 16;
+        *reinterpret_cast<uint4 *>(t + ((2u ^ sw) << 4)) = g0;
+        *reinterpret_cast<uint4 *>(t + ((3u ^ sw) << 4)) = g1;
+    }
+    return h01;
+}
+// upstream tile of the colour net's backward: columns [col8*8, col8*8 + 16) of row `row` = [g * rgb (1 - rgb) x 3 | 0 x 13]
+__device__ __forceinline__ void nerf_grad_c_row(uint8_t *tile, const nerf_io_t &io, uint32_t grow, bool ok, uint32_t row, uint32_t col8) {
+    float g[3] = {0.f, 0.f, 0.f};
+    if (ok) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float r = io.rgbs[3 * (size_t)grow + c];
+            g[c] = io.grad_rgbs[3 * (size_t)grow + c] * r * (1.0f - r);
+        }
+    }
+    uint8_t *t = tile + row * kTileRowBytes;
+    *reinterpret_cast<uint4 *>(t + (((col8) ^ (row & 7u)) << 4)) = make_uint4(pack2(g[0], g[1]), pack2(g[2], 0.f), 0u, 0u);
+    *reinterpret_cast<uint4 *>(t + (((col8 + 1u) ^ (row & 7u)) << 4)) = make_uint4(0u, 0u, 0u, 0u);
+}
+
+// ==========================================================================================================
 // forward / inference
 // ==========================================================================================================
 template <int HID> struct split_of { static constexpr int NS = HID >= 64 ? 4 : (HID == 32 ? 2 : 1); };
@@ -67,10 +140,10 @@ __device__ __forceinline__ void pipe_sync(uint32_t id) { asm volatile("bar.sync 
 // weights: measured on B200 a layer step is latency bound (each tcgen05.mma of this size takes ~80-100 cycles to
 // ISSUE, the accumulator round trip another ~600), so throughput comes from tiles in flight, not from a
 // faster single chain.  Pipeline p: rows = its tile, TMEM columns [p*accw, (p+1)*accw), mbarrier p, named barrier 1+p.
-template <typename WT, int HID, bool GACT>
+template <typename WT, int HID, bool GACT, int IO>
 __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y,
                                                     const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, uint32_t accw,
-                                                    const int *__restrict__ limit) {
+                                                    const int *__restrict__ limit, const nerf_io_t io) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar[8];
@@ -98,9 +171,14 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
     uint32_t phase = 0;
 
     for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
-        load_rows_async(sx, x, tile * kTileRows, Beff, m.in, row, 128);
-        cp_async_commit();
-        cp_async_wait<0>();
+        if constexpr (IO == 2) {  // x = h [M,16]: thread `row` builds its row of [SH4(dir) | h1..h15 | 0]
+            const uint32_t gr = tile * kTileRows + row;
+            nerf_color_row(sx, io.dirs, x, gr, gr < Beff, row, 3u);
+        } else {
+            load_rows_async(sx, x, tile * kTileRows, Beff, m.in, row, 128);
+            cp_async_commit();
+            cp_async_wait<0>();
+        }
         fence_proxy_async();
         pipe_sync(bid);
         if (row == 0) {
@@ -128,7 +206,25 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
         phase ^= 1u;
         fence_after_sync();
         const uint32_t grow = tile * kTileRows + row;
-        epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, grow < Beff);
+        if constexpr (IO == 0) {
+            epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, grow < Beff);
+        } else {  // out == 16 (host-checked): one 16-column drain
+            float v[16];
+            tmem_ld16(trow, v);
+            if (grow < Beff) {
+                if constexpr (IO == 1) {
+                    uint4 lo, hi;
+                    lo.x = pack2(v[0], v[1]); lo.y = pack2(v[2], v[3]); lo.z = pack2(v[4], v[5]); lo.w = pack2(v[6], v[7]);
+                    hi.x = pack2(v[8], v[9]); hi.y = pack2(v[10], v[11]); hi.z = pack2(v[12], v[13]); hi.w = pack2(v[14], v[15]);
+                    reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[0] = lo;
+                    reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[1] = hi;
+                    io.sigmas[grow] = io.density_scale * __expf(half_round(v[0]));  // trunc_exp forward of the stored half
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) io.rgbs[3 * (size_t)grow + c] = half_round(1.0f / (1.0f + __expf(-half_round(v[c]))));
+                }
+            }
+        }
         fence_before_sync();
         pipe_sync(bid);  // accumulator drained before this pipeline's next first MMA overwrites it
     }
@@ -350,11 +446,12 @@ __device__ unsigned g_trn[8];
 #define NGP_TR(slot, tag) do { } while (0)
 #endif
 
-template <typename WT, int HID, bool GACT>
+template <typename WT, int HID, bool GACT, int IO>
 __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__restrict__ grad, const __half *__restrict__ x, const WT *__restrict__ w,
                                                                __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                                int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
-                                                               uint32_t np, uint32_t ns, uint32_t accw, int dual, const int *__restrict__ limit) {
+                                                               uint32_t np, uint32_t ns, uint32_t accw, int dual, const int *__restrict__ limit,
+                                                               const nerf_io_t io) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
@@ -543,12 +640,23 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                 __syncwarp();
             };
             for (uint32_t tile = blockIdx.x * np + p; tile < ntiles; tile += stride) {
-                load_rows_async(sx, x, tile * kTileRows, Beff, m.in, ptid, nth);
-                if (packed) load_rows_async(sx, grad, tile * kTileRows, Beff, m.out, ptid, nth, m.in >> 3);
-                else load_rows_async(sx + xbytes, grad, tile * kTileRows, Beff, m.out, ptid, nth);
-                if (wp == 0) NGP_TR(2 + p, 0x300u);
-                cp_async_commit();
-                cp_async_wait<0>();
+                uint32_t h01 = 0u;  // IO 2: (h0, h1) of this thread's row, kept for the trunc_exp gradient in the last drain
+                if constexpr (IO == 2) {
+                    // x = h [M,16], packed layout (in 32 + out 16 <= 64): thread (row, cg) builds its share of row `row`:
+                    // [SH4(dir) | h1..h15 | 0 | grad_c 16] -- one thread per row does all of it, two split SH + upstream / geo
+                    const uint32_t gr = tile * kTileRows + row;
+                    const bool ok = gr < Beff;
+                    const uint32_t parts = ns == 1u ? 3u : (cg == 0u ? 1u : 2u);
+                    h01 = nerf_color_row(sx, io.dirs, x, gr, ok, row, parts);
+                    if (parts & 1u) nerf_grad_c_row(sx, io, gr, ok, row, m.in >> 3);
+                } else {
+                    load_rows_async(sx, x, tile * kTileRows, Beff, m.in, ptid, nth);
+                    if (packed) load_rows_async(sx, grad, tile * kTileRows, Beff, m.out, ptid, nth, m.in >> 3);
+                    else load_rows_async(sx + xbytes, grad, tile * kTileRows, Beff, m.out, ptid, nth);
+                    if (wp == 0) NGP_TR(2 + p, 0x300u);
+                    cp_async_commit();
+                    cp_async_wait<0>();
+                }
                 fence_proxy_async();
                 __syncwarp();
                 if (selfi) self_issue(0u);
@@ -595,7 +703,24 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                 phase ^= 1u;
                 fence_after_sync();
                 if (wp == 0) NGP_TR(2 + p, 0x800u);
-                if (calc_dx) {
+                if constexpr (IO == 2) {
+                    // grad_h [M,16] = [grad_sigma * density_scale * exp(clamp(h0, -15, 15)) | dL/dcin columns 16..30]; the SH columns'
+                    // gradient (dL/ddir) is not needed.  The thread that built the geo part of the row holds h0.
+                    if ((ns == 1u || cg == 1u)) {  // warp-uniform: cg is a per-warp value
+                        float v[16];
+                        tmem_ld16(trow + 16u, v);
+                        const uint32_t grow = tile * kTileRows + row;
+                        if (grow < Beff) {
+                            const float h0 = __half22float2(*reinterpret_cast<const __half2 *>(&h01)).x;
+                            const float g0 = io.grad_sigmas[grow] * io.density_scale * __expf(fminf(fmaxf(h0, -15.f), 15.f));
+                            uint4 o0, o1;
+                            o0.x = pack2(g0, v[0]); o0.y = pack2(v[1], v[2]); o0.z = pack2(v[3], v[4]); o0.w = pack2(v[5], v[6]);
+                            o1.x = pack2(v[7], v[8]); o1.y = pack2(v[9], v[10]); o1.z = pack2(v[11], v[12]); o1.w = pack2(v[13], v[14]);
+                            reinterpret_cast<uint4 *>(grad_x + (size_t)grow * 16u)[0] = o0;
+                            reinterpret_cast<uint4 *>(grad_x + (size_t)grow * 16u)[1] = o1;
+                        }
+                    }
+                } else if (calc_dx) {
                     const uint32_t grow = tile * kTileRows + row;
                     for (uint32_t c0 = cg * 16u; c0 < m.in; c0 += ns * 16u)
                         epi_to_global(trow, grad_x + (size_t)grow * m.in, c0, c0 + 16u, grow < Beff);
@@ -685,12 +810,27 @@ int set_smem(K kernel, size_t bytes) {
     return NGP_OK;
 }
 
+// io_mode 0: the plain operator.  1 / 2: the sigma / colour net of network_ff with its glue fused in (nerf_io_t; hidden 64, ReLU,
+// fp32 parameters, out 16 -- what NeRFNetwork(--ff) uses; anything else is NGP_EUNSUPPORTED)
+int check_io(const char *fn, int io_mode, uint32_t in, uint32_t out, uint32_t hid, uint32_t act, int wdtype) {
+    if (io_mode == 0) return NGP_OK;
+    if (!(hid == 64 && in == 32 && out == 16 && act == 0 && wdtype == NGP_DTYPE_F32)) {
+        set_error("%s: the fused network_ff nets are 32 -> 64 x n -> 16, ReLU, fp32 parameters (got in %u hidden %u out %u act %u)", fn, in, hid, out, act);
+        return NGP_EUNSUPPORTED;
+    }
+    return NGP_OK;
+}
+
 int run_forward(const char *fn, const void *inputs, const void *weights, int wdtype, uint32_t B, uint32_t in, uint32_t out, uint32_t hid,
-                uint32_t nl, uint32_t act, uint32_t out_act, void *forward_buffer, void *outputs, void *stream) {
+                uint32_t nl, uint32_t act, uint32_t out_act, void *forward_buffer, void *outputs, void *stream, int io_mode = 0,
+                const nerf_io_t *iop = nullptr) {
     if (B == 0) return NGP_OK;
-    NGP_CHECK_ARG(inputs && weights && outputs, "%s: null pointer argument", fn);
+    NGP_CHECK_ARG(inputs && weights && (outputs || io_mode == 2), "%s: null pointer argument", fn);
     int rc = check_dims(fn, in, out, hid, nl, act, out_act, wdtype);
     if (rc != NGP_OK) return rc;
+    rc = check_io(fn, io_mode, in, out, hid, act, wdtype);
+    if (rc != NGP_OK) return rc;
+    const nerf_io_t io = iop ? *iop : nerf_io_t{};
     if (hid == 256) return wide_forward(fn, inputs, weights, wdtype, B, in, out, nl, act, forward_buffer, outputs, (cudaStream_t)stream);
     mlp_t m;
     make_mlp(m, B, in, out, hid, nl);
@@ -712,13 +852,22 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     uint32_t grid = div_round_up(ntiles, np);
     if (grid > (uint32_t)sm_count()) grid = (uint32_t)sm_count();
     cudaStream_t st = (cudaStream_t)stream;
+    if (io_mode) {  // one tile layout, one width: two instantiations
+        rc = io_mode == 1 ? set_smem(k_ffmlp_fwd<float, 64, false, 1>, smem) : set_smem(k_ffmlp_fwd<float, 64, false, 2>, smem);
+        if (rc != NGP_OK) return rc;
+        NGP_PROF(io_mode == 1 ? "k_ffmlp_fwd_sigma" : "k_ffmlp_fwd_color", st);
+        if (io_mode == 1) k_ffmlp_fwd<float, 64, false, 1><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const float *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit(), io);
+        else k_ffmlp_fwd<float, 64, false, 2><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const float *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit(), io);
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
 #define NGP_FWD_CASE(WT_, HID_)                                                                                              \
     {                                                                                                                        \
-        rc = m.act ? set_smem(k_ffmlp_fwd<WT_, HID_, true>, smem) : set_smem(k_ffmlp_fwd<WT_, HID_, false>, smem);               \
+        rc = m.act ? set_smem(k_ffmlp_fwd<WT_, HID_, true, 0>, smem) : set_smem(k_ffmlp_fwd<WT_, HID_, false, 0>, smem);         \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_fwd", st);                                                                                         \
-        if (m.act) k_ffmlp_fwd<WT_, HID_, true><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
-        else k_ffmlp_fwd<WT_, HID_, false><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit()); \
+        if (m.act) k_ffmlp_fwd<WT_, HID_, true, 0><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit(), io); \
+        else k_ffmlp_fwd<WT_, HID_, false, 0><<<grid, 128 * np, smem, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols, accw, batch_limit(), io); \
     }
 #define NGP_FWD_HID(WT_)                                         \
     switch (hid) {                                               \
@@ -762,13 +911,15 @@ size_t ngp_ffmlp_backward_workspace_bytes(uint32_t input_dim, uint32_t output_di
     return (((nw + 3) & ~(size_t)3) + 4) * sizeof(float);
 }
 
-int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, int weights_dtype, const void *forward_buffer, uint32_t B,
-                       uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
-                       uint32_t output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs, void *grad_weights,
-                       int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream, const ngp_call_opts *opts) {
-    ngp::opts_scope _os(opts);
-    using namespace ngp;
-    const char *fn = "ffmlp_backward";
+}  // extern "C"
+
+namespace ngp {
+namespace {
+int run_backward(const char *fn, const void *grad, const void *inputs, const void *weights, int weights_dtype, const void *forward_buffer, uint32_t B,
+                 uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                 uint32_t output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs, void *grad_weights,
+                 int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream, int io_mode = 0, const nerf_io_t *iop = nullptr) {
+    const nerf_io_t io = iop ? *iop : nerf_io_t{};
     NGP_CHECK_ARG(grad_weights, "%s: null pointer argument", fn);
     NGP_CHECK_ARG(grad_weights_dtype == NGP_DTYPE_F16 || grad_weights_dtype == NGP_DTYPE_F32, "%s: grad_weights must be a half or float tensor", fn);
     int rc = check_dims(fn, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, weights_dtype);
@@ -782,8 +933,10 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
         NGP_CHECK_CUDA(cudaMemsetAsync(grad_weights, 0, (size_t)m.nweights * (grad_weights_dtype == NGP_DTYPE_F32 ? 4 : 2), st));
         return NGP_OK;
     }
-    NGP_CHECK_ARG(grad && inputs && weights && workspace, "%s: null pointer argument", fn);
+    NGP_CHECK_ARG((grad || io_mode == 2) && inputs && weights && workspace, "%s: null pointer argument", fn);
     NGP_CHECK_ARG(!calc_grad_inputs || grad_inputs, "%s: calc_grad_inputs needs grad_inputs", fn);
+    rc = check_io(fn, io_mode, input_dim, output_dim, hidden_dim, activation, weights_dtype);
+    if (rc != NGP_OK) return rc;
     NGP_CHECK_ARG(workspace_bytes >= ngp_ffmlp_backward_workspace_bytes(input_dim, output_dim, hidden_dim, num_layers),
                   "%s: workspace too small (%zu bytes)", fn, workspace_bytes);
     if (hidden_dim == 256)
@@ -810,7 +963,7 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
     const int gf32 = grad_weights_dtype == NGP_DTYPE_F32;
     // ---- multi-pipeline variant: NP tiles in flight per CTA, one CTA per SM ----
     {
-        const int variant = get_option("ffmlp_bwd_variant", -1);
+        const int variant = io_mode ? 1 : get_option("ffmlp_bwd_variant", -1);  // the fused nets exist in the multi-pipeline kernel only
         const bool packed = input_dim + output_dim <= 64;
         const size_t per_pipe = ((size_t)ktiles(input_dim) + (packed ? 0 : ktiles(output_dim)) + (size_t)num_layers * ktiles(hidden_dim)) * kActTileBytes;
         uint32_t accw = hidden_dim > input_dim ? hidden_dim : input_dim;
@@ -844,15 +997,24 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
             const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
             uint32_t grid_mp = div_round_up(ntiles, np);
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();
+            if (io_mode == 2) {
+                rc = set_smem(k_ffmlp_bwd_mp<float, 64, false, 2>, smem_mp);
+                if (rc != NGP_OK) return rc;
+                NGP_PROF("k_ffmlp_bwd_mp_color", st);
+                k_ffmlp_bwd_mp<float, 64, false, 2><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const float *)weights, (__half *)grad_inputs,
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);
+                NGP_CHECK_LAUNCH();
+                return NGP_OK;
+            }
 #define NGP_BWDMP_CASE(WT_, HID_)                                                                                            \
     {                                                                                                                        \
-        rc = m.act ? set_smem(k_ffmlp_bwd_mp<WT_, HID_, true>, smem_mp) : set_smem(k_ffmlp_bwd_mp<WT_, HID_, false>, smem_mp);   \
+        rc = m.act ? set_smem(k_ffmlp_bwd_mp<WT_, HID_, true, 0>, smem_mp) : set_smem(k_ffmlp_bwd_mp<WT_, HID_, false, 0>, smem_mp);   \
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd_mp", st);                                                                                      \
-        if (m.act) k_ffmlp_bwd_mp<WT_, HID_, true><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit());   \
-        else k_ffmlp_bwd_mp<WT_, HID_, false><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit());   \
+        if (m.act) k_ffmlp_bwd_mp<WT_, HID_, true, 0><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);   \
+        else k_ffmlp_bwd_mp<WT_, HID_, false, 0><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);   \
     }
 #define NGP_BWDMP_HID(WT_)                                         \
     switch (hidden_dim) {                                          \
@@ -888,6 +1050,58 @@ int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights
 #undef NGP_BWD_CASE
     NGP_CHECK_LAUNCH();
     return NGP_OK;
+}
+}  // namespace
+}  // namespace ngp
+
+extern "C" {
+
+int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, int weights_dtype, const void *forward_buffer, uint32_t B,
+                       uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                       uint32_t output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs, void *grad_weights,
+                       int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    return ngp::run_backward("ffmlp_backward", grad, inputs, weights, weights_dtype, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                             activation, output_activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, grad_weights_dtype, workspace,
+                             workspace_bytes, stream);
+}
+
+/* ---- network_ff nets with their glue fused in (include/ngp_b200.h, "next" rows) ---- */
+int ngp_nerf_sigma_forward(const void *enc, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float density_scale, void *h,
+                           float *sigmas, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    if (M == 0) return NGP_OK;
+    if (!(h && sigmas)) { ngp::set_error("nerf_sigma_forward: null pointer argument"); return NGP_EINVAL; }
+    ngp::nerf_io_t io{};
+    io.sigmas = sigmas;
+    io.density_scale = density_scale;
+    return ngp::run_forward("nerf_sigma_forward", enc, weights, weights_dtype, M, 32, 16, 64, num_layers, 0, 6, nullptr, h, stream, 1, &io);
+}
+
+int ngp_nerf_color_forward(const float *dirs, const void *h, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float *rgbs,
+                           void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    if (M == 0) return NGP_OK;
+    if (!(dirs && rgbs)) { ngp::set_error("nerf_color_forward: null pointer argument"); return NGP_EINVAL; }
+    ngp::nerf_io_t io{};
+    io.dirs = dirs;
+    io.rgbs = rgbs;
+    return ngp::run_forward("nerf_color_forward", h, weights, weights_dtype, M, 32, 16, 64, num_layers, 0, 6, nullptr, nullptr, stream, 2, &io);
+}
+
+int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, const float *grad_sigmas, const float *dirs, const void *h, const void *weights,
+                            int weights_dtype, uint32_t M, uint32_t num_layers, float density_scale, void *grad_h, void *grad_weights,
+                            int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    if (!(grad_rgbs && rgbs && grad_sigmas && dirs && grad_h) && M) { ngp::set_error("nerf_color_backward: null pointer argument"); return NGP_EINVAL; }
+    ngp::nerf_io_t io{};
+    io.dirs = dirs;
+    io.rgbs = const_cast<float *>(rgbs);
+    io.grad_rgbs = grad_rgbs;
+    io.grad_sigmas = grad_sigmas;
+    io.density_scale = density_scale;
+    return ngp::run_backward("nerf_color_backward", nullptr, h, weights, weights_dtype, nullptr, M, 32, 16, 64, num_layers, 0, 6, 1, nullptr, grad_h,
+                             grad_weights, grad_weights_dtype, workspace, workspace_bytes, stream, 2, &io);
 }
 
 }  // extern "C"

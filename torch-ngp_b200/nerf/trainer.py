@@ -37,13 +37,18 @@ class NGPTrainer:
     def __init__(self, bound=1.0, num_rays=4096, device="cuda", lr=1e-2, grid_size=128, density_thresh=10.0, density_scale=1.0,
                  min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=128.0,
                  growth_interval=2000, decay_steps=30000, world_size=1, seed=0, use_graph=True, update_interval=16,
-                 num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False, init_samples_per_ray=512):
+                 num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False, init_samples_per_ray=512,
+                 fused_nets=True):
         """overlap_optimizer: defer the optimizer of step n to the start of step n+1 and run it on a second stream next to
         the ray marching of step n+1 (the marcher reads rays and the occupancy bitfield, never the parameters; Adam is
         HBM-bound, the marcher instruction-bound).  Same arithmetic in the same order; the parameters a caller reads
         between two steps lag one update until flush() -- loss(), update_extra_state(), density() and render() flush or
         read around it themselves."""
         self.dev = torch.device(device)
+        # fused_nets: the glue between the two MLPs (trunc_exp, SH, geo-feature shuffle, sigmoid and their backward) runs inside the
+        # tcgen05 MLP kernels (ngp_nerf_sigma_forward / color_forward / color_backward); False keeps the four elementwise kernels
+        # and the cin / c / grad_c / grad_cin buffers between the plain FFMLP calls -- same results bit for bit (tests).
+        self.fused_nets = bool(fused_nets)
         self.overlap_optimizer = bool(overlap_optimizer)
         self._pending = False
         self._side = None
@@ -136,10 +141,12 @@ class NGPTrainer:
         self.M = M
         self.xyzs, self.dirs, self.deltas = torch.zeros(M, 3, **f32), torch.zeros(M, 3, **f32), torch.zeros(M, 2, **f32)
         self.x01 = torch.zeros(M, 3, **f32)
-        self.enc, self.h, self.cin, self.c = torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16)
+        self.enc, self.h = torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16)
+        Mu = 1 if self.fused_nets else M  # the matrices between the nets exist only on the unfused path
+        self.cin, self.c = torch.zeros(Mu, 32, **f16), torch.zeros(Mu, 16, **f16)
         self.sigmas, self.rgbs = torch.zeros(M, **f32), torch.zeros(M, 3, **f32)
         self.g_sigmas, self.g_rgbs = torch.zeros(M, **f32), torch.zeros(M, 3, **f32)
-        self.g_c, self.g_cin, self.g_h, self.g_enc = torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16), torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16)
+        self.g_c, self.g_cin, self.g_h, self.g_enc = torch.zeros(Mu, 16, **f16), torch.zeros(Mu, 32, **f16), torch.zeros(M, 16, **f16), torch.zeros(M, 32, **f16)
         self._graph = None
 
     # ---- network pieces on raw buffers (shared by the step, the density query and the renderer) -----------
@@ -177,11 +184,21 @@ class NGPTrainer:
         """xyzs, dirs -> sigmas, rgbs on the sample buffers (network_ff.py:51-74)."""
         s = abi.stream()
         self._encode(self.xyzs, self.x01, self.enc, M, limit)
+        if self.fused_nets:
+            self._nets_forward_fused(self.enc, self.dirs, self.h, self.sigmas, self.rgbs, M, limit)
+            return
         self._sigma_forward(self.enc, self.h, M, inference, limit)
         _ck(abi.lib.ngp_nerf_mid_forward(self.h.data_ptr(), self.dirs.data_ptr(), self.density_scale, self.sigmas.data_ptr(), self.cin.data_ptr(), M, s,
                                          self._opts(limit)))
         self._color_forward(self.cin, self.c, M, inference, limit)
         _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s, self._opts(limit)))
+
+    def _nets_forward_fused(self, enc, dirs, h, sigmas, rgbs, M, limit=None):
+        """enc, dirs -> h, sigmas, rgbs: two launches (network_ff.py:55-73)"""
+        s, o = abi.stream(), self._opts(limit)
+        _ck(abi.lib.ngp_nerf_sigma_forward(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 2, self.density_scale, h.data_ptr(),
+                                           sigmas.data_ptr(), s, o))
+        _ck(abi.lib.ngp_nerf_color_forward(dirs.data_ptr(), h.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 3, rgbs.data_ptr(), s, o))
 
     # ---- one training step as a fixed launch sequence ---------------------------------------------------------
     def _march(self):
@@ -222,10 +239,15 @@ class NGPTrainer:
                                                   self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), self.ws.data_ptr(),
                                                   self.depth.data_ptr(), self.image.data_ptr(), M, N, self.T_thresh, self.g_sigmas.data_ptr(),
                                                   self.g_rgbs.data_ptr(), s))
-        _ck(lib.ngp_nerf_rgb_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_c.data_ptr(), M, s, lim))
-        _ck(lib.ngp_ffmlp_backward(self.g_c.data_ptr(), self.cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 3, 0, 6, 1,
-                                   None, self.g_cin.data_ptr(), self.g_col.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
-        _ck(lib.ngp_nerf_mid_backward(self.g_sigmas.data_ptr(), self.h.data_ptr(), self.g_cin.data_ptr(), self.density_scale, self.g_h.data_ptr(), M, s, lim))
+        if self.fused_nets:
+            _ck(lib.ngp_nerf_color_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_sigmas.data_ptr(), self.dirs.data_ptr(), self.h.data_ptr(),
+                                            self.color_w.data_ptr(), abi.DTYPE_F32, M, 3, self.density_scale, self.g_h.data_ptr(), self.g_col.data_ptr(),
+                                            abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
+        else:
+            _ck(lib.ngp_nerf_rgb_backward(self.g_rgbs.data_ptr(), self.rgbs.data_ptr(), self.g_c.data_ptr(), M, s, lim))
+            _ck(lib.ngp_ffmlp_backward(self.g_c.data_ptr(), self.cin.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 3, 0, 6, 1,
+                                       None, self.g_cin.data_ptr(), self.g_col.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
+            _ck(lib.ngp_nerf_mid_backward(self.g_sigmas.data_ptr(), self.h.data_ptr(), self.g_cin.data_ptr(), self.density_scale, self.g_h.data_ptr(), M, s, lim))
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, None, M, 32, 16, 64, 2, 0, 6, 1,
                                    None, self.g_enc.data_ptr(), self.g_sig.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, lim))
         # table gradient: g16 was cleared by the previous optimizer step (k_adam consumes and zeroes it)
@@ -565,7 +587,8 @@ class NGPTrainer:
             iota=torch.arange(N, dtype=torch.int32, device=dev), cnt2=torch.zeros(2, dtype=torch.int32, device=dev),
             work=torch.zeros(2, dtype=torch.int64, device=dev),
             xyzs=torch.zeros(cap, 3, **f32), dirs=torch.zeros(cap, 3, **f32), deltas=torch.zeros(cap, 2, **f32), x01=torch.empty(cap, 3, **f32),
-            enc=torch.empty(cap, 32, **f16), h=torch.empty(cap, 16, **f16), cin=torch.empty(cap, 32, **f16), c=torch.empty(cap, 16, **f16),
+            enc=torch.empty(cap, 32, **f16), h=torch.empty(cap, 16, **f16), cin=torch.empty(1 if self.fused_nets else cap, 32, **f16),
+            c=torch.empty(1 if self.fused_nets else cap, 16, **f16),
             sigmas=torch.empty(cap, **f32), rgbs=torch.empty(cap, 3, **f32),
             cws=torch.empty(max(1 << 16, lib.ngp_compact_alive_workspace_bytes(N)), dtype=torch.uint8, device=dev),
             noises=torch.zeros(N, **f32), zeros_n=torch.zeros(N, **f32), graphs={}, table=None)
@@ -588,10 +611,13 @@ class NGPTrainer:
         # shade the samples (inference kernels: no activations kept); rows_dev bounds every kernel on the device
         lim, rows_dev = self._opts(rs["rows_dev"]), rs["rows_dev"]
         self._encode(rs["xyzs"], rs["x01"], rs["enc"], M, rows_dev)
-        _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s, lim))
-        _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s, lim))
-        _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s, lim))
-        _ck(lib.ngp_nerf_rgb_forward(rs["c"].data_ptr(), rs["rgbs"].data_ptr(), M, s, lim))
+        if self.fused_nets:
+            self._nets_forward_fused(rs["enc"], rs["dirs"], rs["h"], rs["sigmas"], rs["rgbs"], M, rows_dev)
+        else:
+            _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s, lim))
+            _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s, lim))
+            _ck(lib.ngp_ffmlp_inference(rs["cin"].data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 3, 0, 6, None, rs["c"].data_ptr(), s, lim))
+            _ck(lib.ngp_nerf_rgb_forward(rs["c"].data_ptr(), rs["rgbs"].data_ptr(), M, s, lim))
         _ck(lib.ngp_composite_rays(n_alive, n_dev.data_ptr(), n_step, T_thresh, rs["alive"][cur].data_ptr(), rs["rays_t"].data_ptr(),
                                    rs["sigmas"].data_ptr(), rs["rgbs"].data_ptr(), rs["deltas"].data_ptr(), rs["ws"].data_ptr(), rs["depth"].data_ptr(),
                                    rs["image"].data_ptr(), s))
