@@ -409,6 +409,10 @@ class NerfTrainWorkload:
         import nerf
         from nerf import synthetic
         out = None
+        # collective part first, on EVERY rank: a deferred optimizer step of the group trainer carries an all-reduce (flush), and
+        # state_dict() would otherwise run it on rank 0 alone -- against the other ranks' barrier
+        self.tr.flush()
+        barrier_sync(world)
         if rank == 0:
             Ng = self.N * world
             spr = max(8.0, self.tr.mean_count / self.N) if self.tr.mean_count > 0 else 256.0

@@ -12,7 +12,7 @@ using namespace ngp::umma;
 // mode 2: descriptor low words advanced by a constant (add only)
 // mode 3 / 4: one descriptor pair, 4 / 2 independent TMEM accumulators in rotation
 template <int MODE>
-__global__ void __launch_bounds__(128) k_bench(uint32_t N, uint32_t reps, uint32_t nk, long long *out, uint32_t m_mn) {
+__global__ void __launch_bounds__(128) k_bench(uint32_t N, uint32_t reps, uint32_t nk, long long *out, uint32_t m_mn, uint32_t Mdim = 128) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar;
@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(128) k_bench(uint32_t N, uint32_t reps, uint32
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = s_tmem;
-    const uint32_t idesc = make_idesc(128, N, m_mn != 0, m_mn != 0);
+    const uint32_t idesc = make_idesc(Mdim, N, m_mn != 0, m_mn != 0);
     const uint32_t a0 = smem_u32(smem), b0 = smem_u32(smem + 16384);
     long long t0 = 0, t1 = 0, t2 = 0;
     uint32_t phase = 0;
@@ -109,8 +109,8 @@ int main() {
                 if (N > 128 && mode >= 3) continue;
                 auto run = [&](auto kern) {
                     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn);
-                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn);
+                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn, 128u);
+                    kern<<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn, 128u);
                     cudaError_t e = cudaDeviceSynchronize();
                     if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return; }
                     printf("major=%s N=%3u mode=%d  issue %.1f cyc/mma   complete %.1f cyc/mma\n", mn ? "MN" : "K ", N, mode, (double)out[0] / (reps * nk),
@@ -118,6 +118,15 @@ int main() {
                 };
                 if (mode == 0) run(k_bench<0>); else if (mode == 1) run(k_bench<1>); else if (mode == 2) run(k_bench<2>); else if (mode == 3) run(k_bench<3>); else run(k_bench<4>);
             }
+    // M = 64 instruction shape: is a 64-row product cheaper to issue / execute than M = 128?
+    for (int mn = 0; mn < 2; ++mn)
+        for (uint32_t N : {32u, 64u, 128u, 256u}) {
+            cudaFuncSetAttribute(k_bench<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            for (int rep = 0; rep < 2; ++rep) k_bench<1><<<1, 128, 64 * 1024>>>(N, reps, nk, out, mn, 64);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
+            printf("M=64 major=%s N=%3u  issue %.1f cyc/mma   complete %.1f cyc/mma\n", mn ? "MN" : "K ", N, (double)out[0] / (reps * nk), (double)out[1] / (reps * nk));
+        }
     cudaFuncSetAttribute(k_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     for (uint32_t N : {16u, 32u, 64u, 128u})
         for (uint32_t niss : {1u, 2u, 4u}) {

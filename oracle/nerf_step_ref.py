@@ -21,7 +21,7 @@ def _h(x, dtype=np.float32):
 class RefState:
     """Parameters + Adam moments + loss scale, numpy."""
 
-    def __init__(self, table, sigma_w, color_w, offsets, per_level_scale, base_resolution, lr=1e-2, loss_scale=128.0):
+    def __init__(self, table, sigma_w, color_w, offsets, per_level_scale, base_resolution, lr=1e-2, loss_scale=65536.0):  # GradScaler's init_scale (nerf/utils.py:328)
         self.table, self.sigma_w, self.color_w = table.astype(np.float32), sigma_w.astype(np.float32), color_w.astype(np.float32)
         self.offsets, self.pls, self.H0 = np.asarray(offsets, np.int32), float(per_level_scale), int(base_resolution)
         self.m = [np.zeros_like(p) for p in self.params()]
@@ -92,10 +92,12 @@ def forward_backward(st, rays_o, rays_d, gt, bitfield, cascade, grid_size, M, bo
 
 def adam_step(st, grads, grad_div=1.0, beta1=0.9, beta2=0.99, eps=1e-15, decay_steps=30000):
     """torch.optim.Adam + LambdaLR(0.1 ** min(iter / 30000, 1)) + GradScaler.unscale_ / skip on non-finite gradients."""
+    it = getattr(st, "it", 0)  # iterations so far: the reference's LambdaLR steps every iteration, skipped or not (nerf/utils.py:974-981)
+    st.it = it + 1
     if not all(np.isfinite(g).all() for g in grads):
         st.scale *= 0.5
         return False
-    lr = st.lr0 * 0.1 ** min(st.t / decay_steps, 1.0)
+    lr = st.lr0 * 0.1 ** min(it / decay_steps, 1.0)
     st.t += 1
     st._h16 = None
     bc1, bc2 = 1 - beta1 ** st.t, 1 - beta2 ** st.t

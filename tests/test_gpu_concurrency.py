@@ -104,7 +104,10 @@ def test_two_trainers_and_bare_modules_run_concurrently():
         # (fp16-atomic-noisy) parameters only through the loss, never through the grid (update_interval = 0)
         assert together[k]["counts"] == alone[k]["counts"], k
         assert all(abs(a - b) <= 2e-2 * abs(b) + 1e-6 for a, b in zip(together[k]["losses"], alone[k]["losses"])), (together[k]["losses"], alone[k]["losses"])
-        assert _rel(together[k]["params"][-2000:], alone[k]["params"][-2000:]) < 5e-2  # MLP weights after 12 Adam steps
+        # MLP weights after 12 Adam steps: eps = 1e-15 makes each update ~ lr * sign(g), so entries whose gradient is at the noise
+        # level of the fp16 atomics move +-lr either way from run to run (measured 3-6e-2 between two runs of the SAME job alone);
+        # a batch limit or input bound leaking from the other trainer would change sample counts and losses, checked exactly above
+        assert _rel(together[k]["params"][-2000:], alone[k]["params"][-2000:]) < 1.5e-1
     assert alone[0]["counts"] != alone[1]["counts"]  # the two trainers really do different work
     for i in range(steps):
         assert torch.equal(together[2]["y"][i], alone[2]["y"][i]), i                      # forward: bit-exact

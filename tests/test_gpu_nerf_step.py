@@ -131,11 +131,13 @@ def test_inf_gradient_skips_step_and_halves_scale():
     tr.next_pool_batch()
     tr._forward_backward()
     tr.g32[5] = float("inf")
-    before = tr.params.clone()
+    before, scale0 = tr.params.clone(), float(tr.state[4])
+    assert scale0 == 65536.0  # GradScaler's init_scale, as `main_nerf -O` starts (nerf/utils.py:328)
     tr._optimizer_step()
     torch.cuda.synchronize()
     assert torch.equal(before, tr.params)
-    assert float(tr.state[4]) == 64.0 and int(tr.state[0].view(torch.int32)) == 0
+    assert float(tr.state[4]) == 0.5 * scale0 and int(tr.state[0].view(torch.int32)) == 0
+    assert int(tr.state[13].view(torch.int32)) == 1  # the iteration counter (learning-rate schedule) advances on a skipped step too
     assert float(tr.g32.abs().max()) == 0
 
 
@@ -211,7 +213,7 @@ def test_step_matches_cpu_oracle_step():
     tr.set_pool(o, d, gt)
     tr.update_extra_state()
     st = R.RefState(tr.embeddings.cpu().numpy(), tr.sigma_w.cpu().numpy(), tr.color_w.cpu().numpy(), tr.offsets_host, tr.per_level_scale,
-                    tr.base_resolution)
+                    tr.base_resolution, loss_scale=float(tr.state[4]))
     bits = tr.density_bitfield.cpu().numpy()
     for step in range(2):
         tr.next_pool_batch()

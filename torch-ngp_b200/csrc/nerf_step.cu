@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(256) k_sdf_loss(const uint4 *__restrict__ h, c
 //   [4] loss scale                   [5] growth tracker (int)  [6] found_inf (int)    [7] loss accumulator
 //   [8] loss of the last finished step                         [9] lr0                [10] decay steps  [11] decay factor
 //   [12] growth interval (int)
-enum { ST_STEP = 0, ST_LR, ST_BC1, ST_BC2, ST_SCALE, ST_GROWTH, ST_FOUND_INF, ST_LOSS, ST_LAST_LOSS, ST_LR0, ST_DECAY_STEPS, ST_DECAY, ST_GROWTH_INTERVAL };
+enum { ST_STEP = 0, ST_LR, ST_BC1, ST_BC2, ST_SCALE, ST_GROWTH, ST_FOUND_INF, ST_LOSS, ST_LAST_LOSS, ST_LR0, ST_DECAY_STEPS, ST_DECAY, ST_GROWTH_INTERVAL, ST_ITER };
 
 // start of a step: clear the loss accumulator and the inf flag; derive lr / bias corrections for step t = count + 1
 __global__ void k_step_begin(float *__restrict__ st, float beta1, float beta2) {
@@ -181,8 +181,10 @@ __global__ void k_step_begin(float *__restrict__ st, float beta1, float beta2) {
     const int t = __float_as_int(st[ST_STEP]) + 1;
     st[ST_LOSS] = 0.f;
     st[ST_FOUND_INF] = __int_as_float(0);
-    // LambdaLR(optimizer, lambda iter: 0.1 ** min(iter / 30000, 1)) evaluated at the number of finished steps (main_nerf.py:197)
-    const float frac = fminf((float)(t - 1) / st[ST_DECAY_STEPS], 1.0f);
+    // LambdaLR(optimizer, lambda iter: 0.1 ** min(iter / 30000, 1)) (main_nerf.py:197): the scheduler steps once per ITERATION,
+    // also when GradScaler skipped the optimizer step (nerf/utils.py:974-981) -- ST_ITER counts iterations, ST_STEP the optimizer
+    // steps Adam's bias correction sees (torch.optim.Adam's own counter does not advance on a skipped step)
+    const float frac = fminf((float)__float_as_int(st[ST_ITER]) / st[ST_DECAY_STEPS], 1.0f);
     st[ST_LR] = st[ST_LR0] * powf(st[ST_DECAY], frac);
     st[ST_BC1] = 1.0f - powf(beta1, (float)t);
     st[ST_BC2] = 1.0f - powf(beta2, (float)t);
@@ -203,6 +205,7 @@ __global__ void k_step_end(float *__restrict__ st) {
         }
     }
     st[ST_GROWTH] = __int_as_float(growth);
+    st[ST_ITER] = __int_as_float(__float_as_int(st[ST_ITER]) + 1);
     st[ST_LAST_LOSS] = st[ST_LOSS];
 }
 

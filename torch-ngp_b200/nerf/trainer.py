@@ -25,7 +25,7 @@ import ffmlp as _ffmlp
 import gridencoder as _gridencoder
 import raymarching as _raymarching
 
-_ST_STEP, _ST_LR, _ST_BC1, _ST_BC2, _ST_SCALE, _ST_GROWTH, _ST_FOUND_INF, _ST_LOSS, _ST_LAST_LOSS, _ST_LR0, _ST_DECAY_STEPS, _ST_DECAY, _ST_GROWTH_INTERVAL = range(13)
+_ST_STEP, _ST_LR, _ST_BC1, _ST_BC2, _ST_SCALE, _ST_GROWTH, _ST_FOUND_INF, _ST_LOSS, _ST_LAST_LOSS, _ST_LR0, _ST_DECAY_STEPS, _ST_DECAY, _ST_GROWTH_INTERVAL, _ST_ITER = range(14)
 
 
 def _ck(rc):
@@ -35,11 +35,14 @@ def _ck(rc):
 
 class NGPTrainer:
     def __init__(self, bound=1.0, num_rays=4096, device="cuda", lr=1e-2, grid_size=128, density_thresh=10.0, density_scale=1.0,
-                 min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=128.0,
+                 min_near=0.2, dt_gamma=0.0, max_steps=1024, bg_color=1.0, T_thresh=1e-4, perturb=True, loss_scale=65536.0,
                  growth_interval=2000, decay_steps=30000, world_size=1, seed=0, use_graph=True, update_interval=16,
                  num_levels=16, log2_hashmap_size=19, base_resolution=16, overlap_optimizer=False, init_samples_per_ray=512,
                  fused_nets=True):
-        """overlap_optimizer: defer the optimizer of step n to the start of step n+1 and run it on a second stream next to
+        """loss_scale / growth_interval: torch.cuda.amp.GradScaler's defaults (init_scale 2^16, growth every 2000 clean steps, halved
+        on a non-finite gradient), which is what `main_nerf -O` trains with (nerf/utils.py:328); the learning-rate decay counts
+        iterations, skipped optimizer steps included, like the reference's per-iteration LambdaLR.step().
+        overlap_optimizer: defer the optimizer of step n to the start of step n+1 and run it on a second stream next to
         the ray marching of step n+1 (the marcher reads rays and the occupancy bitfield, never the parameters; Adam is
         HBM-bound, the marcher instruction-bound).  Same arithmetic in the same order; the parameters a caller reads
         between two steps lag one update until flush() -- loss(), update_extra_state(), density() and render() flush or
