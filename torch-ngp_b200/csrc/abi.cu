@@ -30,6 +30,7 @@ static std::map<std::string, int> &options() {
         {"hashgrid_v3_minb_bwd", -1},  // v3 backward: same
         {"hashgrid_v3_mix_fwd", 0},    // v3 forward: warps of one block work on different level groups (1) or whole blocks do (0)
         {"hashgrid_v3_mix_bwd", 1},    // v3 backward: same choice (measured: helps the backward on ray-ordered samples, hurts the forward on random points)
+        {"hashgrid_v3_unroll_bwd", -1}, // v3 backward: four levels of a thread unrolled (1) or one loop body (0: 4x smaller code, no instruction-cache thrash: the default)
         {"hashgrid_bwd_red4", 2},      // v3 backward, fp16 table: one red.v4.f16x2 per 4-entry group holding both x-neighbours: 0 never, 1 always, 2 when the lanes of a warp do not share groups (random points)
 #ifdef NGP_FFMLP_DEBUG
         {"ffmlp_ablate", 0},           // developer builds only: timing experiments with WRONG results (1 skip the weight-gradient MMAs, 2 the layer MMAs, 3 both)

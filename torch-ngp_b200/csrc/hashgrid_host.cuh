@@ -170,9 +170,12 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
             }
         }
         NGP_PROF("k_grid_bwd_v3", st);
-#define NGP_BWD_V3(MINB, MIX) k_grid_bwd_v3<T, MINB, MIX><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit())
-        if (mix) { if (occ6) NGP_BWD_V3(6, true); else NGP_BWD_V3(4, true); }
-        else { if (occ6) NGP_BWD_V3(6, false); else NGP_BWD_V3(4, false); }
+        const int un_opt = get_option("hashgrid_v3_unroll_bwd", -1);
+        const bool unroll = un_opt > 0;  // default: one loop body (A/B in one run: -13 % per ray-ordered sample, no difference on unordered points)
+#define NGP_BWD_V3(MINB, MIX) { if (unroll) k_grid_bwd_v3<T, MINB, MIX, true><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit()); \
+                                else k_grid_bwd_v3<T, MINB, MIX, false><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit()); }
+        if (mix) { if (occ6) NGP_BWD_V3(6, true) else NGP_BWD_V3(4, true) }
+        else { if (occ6) NGP_BWD_V3(6, false) else NGP_BWD_V3(4, false) }
 #undef NGP_BWD_V3
         NGP_CHECK_LAUNCH();
         return NGP_OK;

@@ -274,7 +274,7 @@ __device__ __forceinline__ void red_rows(T *__restrict__ tab, const uint32_t i0[
 // Segmented warp reduction over runs of equal cells (see k_grid_bwd_d3c2_lg4), with two changes:
 // the shuffle rounds stop at the longest run of the warp (REDUX max) instead of always running five,
 // and the index arithmetic is the per-kind code above.
-template <typename T, int MINB, bool MIX>
+template <typename T, int MINB, bool MIX, bool UNROLL>
 __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                      const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
@@ -303,14 +303,20 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
             for (int k = 0; k < 4; ++k) gv[k] = entry_io<T>::loadg(grad + ((size_t)(l0 + k) * Bs + b) * 2);
         }
     }
-#pragma unroll
+    // UNROLL = false: the body (three index kinds, sixteen-value segmented reduction, reduction variants) is ~2 k instructions;
+    // four copies made a 131 KB kernel whose warps -- each on its own level group and kind -- thrashed the instruction cache
+    // (ncu: "no_instruction" was the top stall reason).  Measured back to back in one job (option hashgrid_v3_unroll_bwd):
+    // ray-ordered fp16 samples 309-323 -> 270-280 ps/sample (the path that runs the segmented reduction); unordered points
+    // (configs[0], the SDF step) do not care either way.  The level's gradient is picked with selects so gv[] stays in registers.
+#pragma unroll(UNROLL ? 4 : 1)
     for (int k = 0; k < 4; ++k) {
         if (l0 + k < skip) continue;  // coarse levels accumulated in shared memory by k_grid_bwd_d3c2_smem
         const lv3_t lv = my_lv[k];
         T *tab = grad_grid + (size_t)lv.offset * 2;
+        const float2 gk = k == 0 ? gv[0] : (k == 1 ? gv[1] : (k == 2 ? gv[2] : gv[3]));
         // A zero upstream gradient adds nothing: drop the lane for this level.  In NeRF training every sample behind
         // the point where a ray's transmittance fell below T_thresh has an exactly zero gradient.
-        const bool valid = inside && (gv[k].x != 0.f || gv[k].y != 0.f);
+        const bool valid = inside && (gk.x != 0.f || gk.y != 0.f);
         if (__ballot_sync(0xffffffffu, valid) == 0) continue;
         cell3_t c;
         uint32_t i0[4], i1[4];
@@ -321,8 +327,8 @@ __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__
         float s[16];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            s[4 * q + 0] = c.w0[q] * gv[k].x; s[4 * q + 1] = c.w0[q] * gv[k].y;
-            s[4 * q + 2] = c.w1[q] * gv[k].x; s[4 * q + 3] = c.w1[q] * gv[k].y;
+            s[4 * q + 0] = c.w0[q] * gk.x; s[4 * q + 1] = c.w0[q] * gk.y;
+            s[4 * q + 2] = c.w1[q] * gk.x; s[4 * q + 3] = c.w1[q] * gk.y;
         }
         if (!warp_agg) {
             if (valid) red_rows<T>(tab, i0, i1, s, red4);
