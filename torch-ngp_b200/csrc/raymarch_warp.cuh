@@ -388,7 +388,17 @@ __global__ void __launch_bounds__(kWarpRays * 32) k_composite_train_bwd_warp(
     const uint32_t n = blockIdx.x * kWarpRays + wid;
     if (n >= N) return;
     const uint32_t index = (uint32_t)rays[3 * (size_t)n], offset = (uint32_t)rays[3 * (size_t)n + 1], num_steps = (uint32_t)rays[3 * (size_t)n + 2];
-    if (num_steps == 0 || offset + num_steps > M) return;
+    // Every sample slot of this ray is WRITTEN: zeros where the reference kernel leaves its caller's zero-initialised buffers
+    // untouched (behind the point where the transmittance fell below T_thresh; rays that did not fit the buffers).  Same result
+    // for a caller that zero-fills first (the plugin wrapper, raymarching.py:239-240), and the trainers skip those two fills.
+    if (num_steps == 0) return;
+    if (offset + num_steps > M) {
+        for (uint32_t j = offset + lane; j < M && offset < M; j += 32) {
+            grad_sigmas[j] = 0.f;
+            grad_rgbs[3 * (size_t)j] = 0.f; grad_rgbs[3 * (size_t)j + 1] = 0.f; grad_rgbs[3 * (size_t)j + 2] = 0.f;
+        }
+        return;
+    }
     const float gi0 = grad_image[3 * (size_t)index], gi1 = grad_image[3 * (size_t)index + 1], gi2 = grad_image[3 * (size_t)index + 2];
     const float gws = grad_weights_sum[index], gd = grad_depth[index];
     const float r_final = image[3 * (size_t)index], g_final = image[3 * (size_t)index + 1], b_final = image[3 * (size_t)index + 2];
@@ -420,8 +430,17 @@ __global__ void __launch_bounds__(kWarpRays * 32) k_composite_train_bwd_warp(
             gc[3 * (size_t)i] = gi0 * w; gc[3 * (size_t)i + 1] = gi1 * w; gc[3 * (size_t)i + 2] = gi2 * w;
             gs[i] = dx * (gi0 * (T_after * c0 - (r_final - rc)) + gi1 * (T_after * c1 - (g_final - gc_)) + gi2 * (T_after * c2 - (b_final - bc)) +
                           gd * (T_after * tc - (d_final - dc)) + gws * (1 - ws_final));
+        } else if (valid) {
+            gc[3 * (size_t)i] = 0.f; gc[3 * (size_t)i + 1] = 0.f; gc[3 * (size_t)i + 2] = 0.f;
+            gs[i] = 0.f;
         }
-        if (stop) break;
+        if (stop) {
+            for (uint32_t j = base + 32 + lane; j < num_steps; j += 32) {
+                gc[3 * (size_t)j] = 0.f; gc[3 * (size_t)j + 1] = 0.f; gc[3 * (size_t)j + 2] = 0.f;
+                gs[j] = 0.f;
+            }
+            break;
+        }
         T = __shfl_sync(0xffffffffu, T_after, 31);
         t = __shfl_sync(0xffffffffu, tc, 31);
         r = __shfl_sync(0xffffffffu, rc, 31); g = __shfl_sync(0xffffffffu, gc_, 31); b = __shfl_sync(0xffffffffu, bc, 31);

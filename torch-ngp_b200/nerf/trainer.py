@@ -52,6 +52,8 @@ class NGPTrainer:
         # tcgen05 MLP kernels (ngp_nerf_sigma_forward / color_forward / color_backward); False keeps the four elementwise kernels
         # and the cin / c / grad_c / grad_cin buffers between the plain FFMLP calls -- same results bit for bit (tests).
         self.fused_nets = bool(fused_nets)
+        # the warp-per-ray compositor backward writes every sample slot of every ray (zeros behind the cut-off): no zero fill per step
+        self._bwd_writes_all = abi.get_option("composite_variant") != 0
         self.overlap_optimizer = bool(overlap_optimizer)
         self._pending = False
         self._side = None
@@ -236,8 +238,9 @@ class NGPTrainer:
         _ck(lib.ngp_nerf_loss(self.image.data_ptr(), self.ws.data_ptr(), self.gt.data_ptr(), self.bg_color, N, self.state[_ST_SCALE:].data_ptr(),
                               self.g_image.data_ptr(), self.g_ws.data_ptr(), self.g_depth.data_ptr(), self.state[_ST_LOSS:].data_ptr(), s))
         # ---- backward ----
-        self.g_sigmas.zero_()
-        self.g_rgbs.zero_()
+        if not self._bwd_writes_all:  # the thread-per-ray compositor leaves slots behind a ray's cut-off untouched (like the reference's)
+            self.g_sigmas.zero_()
+            self.g_rgbs.zero_()
         _ck(lib.ngp_composite_rays_train_backward(self.g_ws.data_ptr(), self.g_depth.data_ptr(), self.g_image.data_ptr(), self.sigmas.data_ptr(),
                                                   self.rgbs.data_ptr(), self.deltas.data_ptr(), self.rays.data_ptr(), self.ws.data_ptr(),
                                                   self.depth.data_ptr(), self.image.data_ptr(), M, N, self.T_thresh, self.g_sigmas.data_ptr(),
@@ -393,6 +396,24 @@ class NGPTrainer:
         """Loss of the last finished step (device -> host read).  With a deferred optimizer step pending, the value is
         still in the accumulator slot (k_step_end has not copied it yet): read it there instead of forcing the update."""
         return float(self.state[_ST_LOSS if self._pending else _ST_LAST_LOSS].item())
+
+    def loss_async(self):
+        """The same read without stalling the launch queue: enqueues the device -> host copy of the last step's loss into pinned
+        memory on the current stream (it lands after that step's kernels and before the next step clears the accumulator) and
+        returns a function that waits for THAT copy only and gives the value.  A training loop calls it after every step and
+        collects the value one step later, so the host keeps launching while the GPU works."""
+        ring = self.__dict__.setdefault("_loss_ring", {"i": 0, "buf": torch.zeros(8, dtype=torch.float32).pin_memory(),
+                                                        "ev": [torch.cuda.Event() for _ in range(8)]})
+        i = ring["i"] = (ring["i"] + 1) % 8
+        slot = _ST_LOSS if self._pending else _ST_LAST_LOSS
+        ring["buf"][i:i + 1].copy_(self.state[slot:slot + 1], non_blocking=True)
+        ev = ring["ev"][i]
+        ev.record()
+
+        def get():
+            ev.synchronize()
+            return float(ring["buf"][i])
+        return get
 
     # ---- synthetic ray pool (device resident inputs for the kernel-side benchmark) ----------------------------
     def set_pool(self, rays_o, rays_d, gt):
