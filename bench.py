@@ -735,8 +735,13 @@ class SDFWorkload:
     def step_e2e(self):
         p, y = self.batches_host[self.i % 4]
         self.i += 1
-        self.tr.train_step(p, y)
-        return self.tr.loss()
+        self.tr.train_step(p, y)  # 16 MB of pinned host input per step, staged on a side stream behind the previous step
+        prev, self._loss_get = getattr(self, "_loss_get", None), self.tr.loss_async()  # every step's loss is copied; collected one step later
+        return prev() if prev is not None else None
+
+    def e2e_finish(self):
+        get, self._loss_get = getattr(self, "_loss_get", None), None
+        return get() if get is not None else None
 
     def profile_mode(self, on):
         self._saved = getattr(self, "_saved", self.tr.use_graph)

@@ -102,6 +102,34 @@ def test_fused_nets_equal_the_unfused_chain():
     assert torch.equal(ia, ib) and torch.equal(da, db)
 
 
+def test_host_batches_fed_on_a_side_stream_equal_device_batches():
+    """train_step(pinned host tensors): the batch is staged on a side stream (nerf/feed.py) and the loss collected asynchronously
+    (loss_async); same samples and losses as with device-resident batches, including across the staging ring's reuse."""
+    from nerf import synthetic
+    o, d, gt = synthetic.make_pool(6, 1024, "cuda", seed=5)
+    host = [t.cpu().pin_memory() for t in (o, d, gt)]
+    runs = []
+    for use_host in (False, True):
+        torch.manual_seed(3)
+        tr = _make(num_rays=1024, graph=True, perturb=False, update_interval=0)
+        tr.update_extra_state()
+        counts, losses, pend = [], [], None
+        for k in range(6):
+            sl = slice(k * 1024, (k + 1) * 1024)
+            src = host if use_host else (o, d, gt)
+            tr.train_step(src[0][sl], src[1][sl], src[2][sl])
+            counts.append(tr.step_counter[0, :1].clone())
+            if pend is not None:
+                losses.append(pend())
+            pend = tr.loss_async()
+        losses.append(pend())
+        torch.cuda.synchronize()
+        runs.append(([int(c) for c in counts], losses))
+    assert runs[0][0] == runs[1][0] and runs[0][0][0] > 1000
+    assert all(abs(a - b) <= 2e-2 * abs(b) + 1e-7 for a, b in zip(runs[1][1], runs[0][1])), runs
+    assert abs(runs[1][1][0] - runs[0][1][0]) <= 1e-6 * runs[0][1][0]  # first step: identical parameters, identical batch
+
+
 def test_optimizer_matches_torch_adam_and_grad_scaler():
     tr = _make(num_rays=1024)
     tr.update_extra_state()

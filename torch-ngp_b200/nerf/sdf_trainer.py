@@ -91,9 +91,11 @@ class SDFTrainer:
 
     def train_step(self, points=None, sdfs=None):
         """points [B,3] in [-1,1], sdfs [B] (device or pinned host tensors); None keeps the current batch buffers."""
-        if points is not None:
-            self.points.copy_(points, non_blocking=True)
-            self.sdfs.copy_(sdfs, non_blocking=True)
+        if points is not None:  # host batches travel on a side stream while the previous step computes (nerf/feed.py)
+            if getattr(self, "_feed", None) is None:
+                from .feed import HostFeed
+                self._feed = HostFeed(self.dev)
+            self._feed.stage((self.points, self.sdfs), (points, sdfs))
         if self.use_graph and self._graph is None:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
@@ -119,6 +121,21 @@ class SDFTrainer:
 
     def loss(self):
         return float(self.state[_ST_LAST_LOSS].item())
+
+    def loss_async(self):
+        """Enqueue the device -> host copy of the last step's loss into pinned memory; returns a function that waits for THAT copy
+        only and gives the value (collected one step later, the host keeps launching: see NGPTrainer.loss_async)."""
+        ring = self.__dict__.setdefault("_loss_ring", {"i": 0, "buf": torch.zeros(8, dtype=torch.float32).pin_memory(),
+                                                        "ev": [torch.cuda.Event() for _ in range(8)]})
+        i = ring["i"] = (ring["i"] + 1) % 8
+        ring["buf"][i:i + 1].copy_(self.state[_ST_LAST_LOSS:_ST_LAST_LOSS + 1], non_blocking=True)
+        ev = ring["ev"][i]
+        ev.record()
+
+        def get():
+            ev.synchronize()
+            return float(ring["buf"][i])
+        return get
 
     @torch.no_grad()
     def predict(self, points):

@@ -56,6 +56,7 @@ class NGPTrainer:
         self._bwd_writes_all = abi.get_option("composite_variant") != 0
         self.overlap_optimizer = bool(overlap_optimizer)
         self._pending = False
+        self._feed = None
         self._side = None
         self._g_steady = None
         self.adam_blocks_per_sm = 5  # grid cap of k_adam while it shares the SMs with the marcher
@@ -371,10 +372,11 @@ class NGPTrainer:
     def train_step(self, rays_o=None, rays_d=None, gt=None):
         """One optimisation step.  rays_o / rays_d / gt: [N,3] tensors (device, or pinned host -> async H2D); None keeps
         whatever is in the ray buffers (e.g. filled by next_pool_batch)."""
-        if rays_o is not None:
-            self.rays_o.copy_(rays_o, non_blocking=True)
-            self.rays_d.copy_(rays_d, non_blocking=True)
-            self.gt.copy_(gt, non_blocking=True)
+        if rays_o is not None:  # host batches travel on a side stream while the previous step computes (nerf/feed.py)
+            if self._feed is None:
+                from .feed import HostFeed
+                self._feed = HostFeed(self.dev)
+            self._feed.stage((self.rays_o, self.rays_d, self.gt), (rays_o, rays_d, gt))
         if self.update_interval > 0 and self.global_step % self.update_interval == 0:
             self.update_extra_state()
         if self.use_graph and self._graph is None:
