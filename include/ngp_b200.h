@@ -256,6 +256,12 @@ NGP_API int ngp_nerf_sigma_forward(const void *enc, const void *weights, int wei
                            void *h, float *sigmas, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_nerf_color_forward(const float *dirs, const void *h, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers,
                            float *rgbs, void *stream, const ngp_call_opts *opts);
+/* sigma_forward + color_forward in ONE launch (both weight sets staged once per CTA, the encoding tile becomes the colour net's
+ * input tile in place): h may be NULL (inference: the sigma net's output never leaves the SM); non-NULL h [M,16] is written for
+ * ngp_nerf_color_backward.  Same results as the two calls, bit for bit. */
+NGP_API int ngp_nerf_nets_forward(const void *enc, const float *dirs, const void *weights_sigma, const void *weights_color, int weights_dtype,
+                          uint32_t M, uint32_t num_layers_sigma, uint32_t num_layers_color, float density_scale, void *h, float *sigmas,
+                          float *rgbs, void *stream, const ngp_call_opts *opts);
 NGP_API int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, const float *grad_sigmas, const float *dirs, const void *h,
                             const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float density_scale, void *grad_h,
                             void *grad_weights, int grad_weights_dtype, void *workspace, size_t workspace_bytes, void *stream,

@@ -76,9 +76,10 @@ def test_fused_nets_equal_the_unfused_chain():
     to the order of their atomic sums.  Also the inference renderer, which shades through the same two entry points."""
     from nerf import synthetic
     out = []
-    for fused in (True, False):
+    for fused, merged in ((True, True), (False, False), (True, False)):  # one launch for both nets / the unfused chain / one launch per net
         torch.manual_seed(7)
         tr = _make(fused_nets=fused)
+        tr.merged_forward = merged
         assert tr.fused_nets == fused
         tr.update_extra_state()
         tr.next_pool_batch()
@@ -86,8 +87,10 @@ def test_fused_nets_equal_the_unfused_chain():
         tr._forward_backward()
         torch.cuda.synchronize()
         out.append(tr)
-    a, b = out
+    a, b, c = out
     n = int(a.step_counter[0, 0])
+    for name in ("h", "sigmas", "rgbs", "g_h", "g_enc"):
+        assert torch.equal(getattr(a, name)[:n], getattr(c, name)[:n]), name
     assert n == int(b.step_counter[0, 0]) and n > 1000
     assert a.cin.shape[0] == 1 and b.cin.shape[0] == b.M  # the fused path does not even allocate the matrices between the nets
     for name in ("h", "sigmas", "rgbs", "g_sigmas", "g_rgbs", "g_h", "g_enc"):

@@ -233,6 +233,142 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd(const __half *__restrict__ x
 }
 
 // ==========================================================================================================
+// both nets of NeRFNetwork(--ff) in ONE launch: enc -> sigma net -> (h, sigma) -> [SH4(dir) | h1..h15 | 0] -> colour net -> rgb
+// ==========================================================================================================
+// Same pipelines as k_ffmlp_fwd (one warpgroup per 128-row tile, thread = row); the weights of both nets are staged once per
+// CTA (44 KB), the X tile that held the encoding becomes the colour net's input tile as soon as the sigma net's first product
+// has read it, and the row of h a thread has just drained goes into that tile from registers: h [M,16] is written for the
+// backward (TRAIN) but never read back, and in inference it does not exist.  Arithmetic per sample is that of
+// ngp_nerf_sigma_forward + ngp_nerf_color_forward, expression for expression.
+template <bool TRAIN>
+__global__ void __launch_bounds__(1024) k_nerf_nets_fwd(const __half *__restrict__ enc, const float *__restrict__ w_sig, const float *__restrict__ w_col,
+                                                        __half *__restrict__ h_out, const mlp_t ms, const mlp_t mc, uint32_t ntiles, uint32_t tmem_cols,
+                                                        const int *__restrict__ limit, const nerf_io_t io) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_bar[8];
+    const uint32_t Beff = eff_batch(ms.B, limit);
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
+    uint8_t *sw1 = smem, *sw2 = smem + ms.wbytes;
+    uint8_t *sx = smem + ms.wbytes + mc.wbytes + pipe * (2 * kActTileBytes);
+    uint8_t *sa = sx + kActTileBytes;
+    stage_weights<float>(sw1, w_sig, ms, tid, blockDim.x);
+    stage_weights<float>(sw2, w_col, mc, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid < np) mbar_init(&s_bar[tid], 1);
+    if (tid == 0) mbar_init_fence();
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem + pipe * 64u;
+    const uint32_t trow = tmem + (((warp & 3u) * 32u) << 16);
+    uint64_t *bar = &s_bar[pipe];
+    const uint32_t bid = 1u + pipe;
+    uint32_t phase = 0;
+    // one round: wait for the product, drain 64 columns with ReLU into `sa`, hand the next product to the tensor core
+    auto hidden_round = [&](const uint8_t *w_next, uint32_t n_next) {
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        epi_relu_to_tile<32>(trow, sa, row, 0u);
+        epi_relu_to_tile<32>(trow, sa, row, 32u);
+        fence_proxy_async();
+        fence_before_sync();
+        pipe_sync(bid);
+        if (row == 0) {
+            fence_after_sync();
+            issue_fwd(tmem, sa, w_next, n_next, 64u);
+            mma_commit(bar);
+        }
+    };
+    for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
+        const uint32_t grow = tile * kTileRows + row;
+        const bool ok = grow < Beff;
+        load_rows_async(sx, enc, tile * kTileRows, Beff, 32u, row, 128);
+        cp_async_commit();
+        float dx = 0.f, dy = 0.f, dz = 0.f;  // the direction of this thread's sample: requested now, used after the sigma net
+        if (ok) { dx = io.dirs[3 * (size_t)grow]; dy = io.dirs[3 * (size_t)grow + 1]; dz = io.dirs[3 * (size_t)grow + 2]; }
+        cp_async_wait<0>();
+        fence_proxy_async();
+        pipe_sync(bid);
+        if (row == 0) {
+            fence_after_sync();
+            issue_fwd(tmem, sx, sw1 + ms.soff[0], 64u, 32u);
+            mma_commit(bar);
+        }
+        hidden_round(sw1 + ms.soff[1], 64u);
+        hidden_round(sw1 + ms.soff[2], 16u);
+        // ---- h, sigma, and the colour net's input tile (into the X tile: the sigma net's layer 0 is long done with it) ----
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        {
+            float v[16];
+            tmem_ld16(trow, v);
+            uint4 lo, hi;
+            lo.x = pack2(v[0], v[1]); lo.y = pack2(v[2], v[3]); lo.z = pack2(v[4], v[5]); lo.w = pack2(v[6], v[7]);
+            hi.x = pack2(v[8], v[9]); hi.y = pack2(v[10], v[11]); hi.z = pack2(v[12], v[13]); hi.w = pack2(v[14], v[15]);
+            if (!ok) lo = hi = make_uint4(0u, 0u, 0u, 0u);
+            if (ok) {
+                if (TRAIN) {
+                    reinterpret_cast<uint4 *>(h_out + (size_t)grow * 16u)[0] = lo;
+                    reinterpret_cast<uint4 *>(h_out + (size_t)grow * 16u)[1] = hi;
+                }
+                io.sigmas[grow] = io.density_scale * __expf(half_round(v[0]));
+            }
+            const float x = dx, y = dy, z = dz;
+            const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+            uint4 s0, s1;
+            s0.x = pack2(0.28209479177387814f, -0.48860251190291987f * y);
+            s0.y = pack2(0.48860251190291987f * z, -0.48860251190291987f * x);
+            s0.z = pack2(1.0925484305920792f * xy, -1.0925484305920792f * yz);
+            s0.w = pack2(0.94617469575755997f * z2 - 0.31539156525251999f, -1.0925484305920792f * xz);
+            s1.x = pack2(0.54627421529603959f * x2 - 0.54627421529603959f * y2, 0.59004358992664352f * y * (-3.0f * x2 + y2));
+            s1.y = pack2(2.8906114426405538f * xy * z, 0.45704579946446572f * y * (1.0f - 5.0f * z2));
+            s1.z = pack2(0.3731763325901154f * z * (5.0f * z2 - 3.0f), 0.45704579946446572f * x * (1.0f - 5.0f * z2));
+            s1.w = pack2(1.4453057213202769f * z * (x2 - y2), 0.59004358992664352f * x * (-x2 + 3.0f * y2));
+            if (!ok) s0 = s1 = make_uint4(0u, 0u, 0u, 0u);
+            uint4 g0, g1;  // geo_feat = h[1..15] shifted down by one half, then a zero pad
+            g0.x = __byte_perm(lo.x, lo.y, 0x5432); g0.y = __byte_perm(lo.y, lo.z, 0x5432); g0.z = __byte_perm(lo.z, lo.w, 0x5432); g0.w = __byte_perm(lo.w, hi.x, 0x5432);
+            g1.x = __byte_perm(hi.x, hi.y, 0x5432); g1.y = __byte_perm(hi.y, hi.z, 0x5432); g1.z = __byte_perm(hi.z, hi.w, 0x5432); g1.w = hi.w >> 16;
+            uint8_t *t = sx + row * kTileRowBytes;
+            const uint32_t swz = row & 7u;
+            *reinterpret_cast<uint4 *>(t + ((0u ^ swz) << 4)) = s0;
+            *reinterpret_cast<uint4 *>(t + ((1u ^ swz) << 4)) = s1;
+            *reinterpret_cast<uint4 *>(t + ((2u ^ swz) << 4)) = g0;
+            *reinterpret_cast<uint4 *>(t + ((3u ^ swz) << 4)) = g1;
+        }
+        fence_proxy_async();
+        fence_before_sync();
+        pipe_sync(bid);
+        if (row == 0) {
+            fence_after_sync();
+            issue_fwd(tmem, sx, sw2 + mc.soff[0], 64u, 32u);
+            mma_commit(bar);
+        }
+        for (uint32_t l = 0; l < mc.nl; ++l) hidden_round(sw2 + mc.soff[l + 1], mc.rows[l + 1]);
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        {
+            float v[16];
+            tmem_ld16(trow, v);
+            if (ok) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) io.rgbs[3 * (size_t)grow + c] = half_round(1.0f / (1.0f + __expf(-half_round(v[c]))));
+            }
+        }
+        fence_before_sync();
+        pipe_sync(bid);  // accumulator drained before this pipeline's next first MMA overwrites it
+    }
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
+}
+
+// ==========================================================================================================
 // backward (recomputes the forward per tile; dW accumulated in TMEM across the CTA's tiles)
 // ==========================================================================================================
 struct bwd_cols_t {
@@ -1087,6 +1223,43 @@ int ngp_nerf_color_forward(const float *dirs, const void *h, const void *weights
     io.dirs = dirs;
     io.rgbs = rgbs;
     return ngp::run_forward("nerf_color_forward", h, weights, weights_dtype, M, 32, 16, 64, num_layers, 0, 6, nullptr, nullptr, stream, 2, &io);
+}
+
+int ngp_nerf_nets_forward(const void *enc, const float *dirs, const void *weights_sigma, const void *weights_color, int weights_dtype, uint32_t M,
+                          uint32_t num_layers_sigma, uint32_t num_layers_color, float density_scale, void *h, float *sigmas, float *rgbs, void *stream,
+                          const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    using namespace ngp;
+    const char *fn = "nerf_nets_forward";
+    if (M == 0) return NGP_OK;
+    NGP_CHECK_ARG(enc && dirs && weights_sigma && weights_color && sigmas && rgbs, "%s: null pointer argument", fn);
+    if (weights_dtype != NGP_DTYPE_F32 || num_layers_sigma != 2 || num_layers_color < 2 || num_layers_color > 6) {
+        set_error("%s: fp32 parameters, a 2-layer sigma net and a 2..6-layer colour net (network_ff.py:26-49 uses 2 and 3)", fn);
+        return NGP_EUNSUPPORTED;
+    }
+    mlp_t ms, mc;
+    make_mlp(ms, M, 32, 16, 64, num_layers_sigma);
+    make_mlp(mc, M, 32, 16, 64, num_layers_color);
+    const uint32_t ntiles = div_round_up(M, kTileRows);
+    const size_t per_pipe = 2 * kActTileBytes;
+    uint32_t np = (uint32_t)((kMaxSmem - 1024 - ms.wbytes - mc.wbytes) / per_pipe);
+    if (np > 8) np = 8;
+    const uint32_t per_cta_need = div_round_up(ntiles, (uint32_t)sm_count());
+    if (np > per_cta_need) np = per_cta_need;
+    const size_t smem = ms.wbytes + mc.wbytes + np * per_pipe;
+    const uint32_t cols = tmem_cols_pow2(np * 64u);
+    uint32_t grid = div_round_up(ntiles, np);
+    if (grid > (uint32_t)sm_count()) grid = (uint32_t)sm_count();
+    nerf_io_t io{};
+    io.dirs = dirs; io.sigmas = sigmas; io.rgbs = rgbs; io.density_scale = density_scale;
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = h ? set_smem(k_nerf_nets_fwd<true>, smem) : set_smem(k_nerf_nets_fwd<false>, smem);
+    if (rc != NGP_OK) return rc;
+    NGP_PROF("k_nerf_nets_fwd", st);
+    if (h) k_nerf_nets_fwd<true><<<grid, 128 * np, smem, st>>>((const __half *)enc, (const float *)weights_sigma, (const float *)weights_color, (__half *)h, ms, mc, ntiles, cols, batch_limit(), io);
+    else k_nerf_nets_fwd<false><<<grid, 128 * np, smem, st>>>((const __half *)enc, (const float *)weights_sigma, (const float *)weights_color, nullptr, ms, mc, ntiles, cols, batch_limit(), io);
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
 }
 
 int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, const float *grad_sigmas, const float *dirs, const void *h, const void *weights,

@@ -52,6 +52,7 @@ class NGPTrainer:
         # tcgen05 MLP kernels (ngp_nerf_sigma_forward / color_forward / color_backward); False keeps the four elementwise kernels
         # and the cin / c / grad_c / grad_cin buffers between the plain FFMLP calls -- same results bit for bit (tests).
         self.fused_nets = bool(fused_nets)
+        self.merged_forward = True  # with fused_nets: both nets' forward in one launch (ngp_nerf_nets_forward); False: one launch per net
         # the warp-per-ray compositor backward writes every sample slot of every ray (zeros behind the cut-off): no zero fill per step
         self._bwd_writes_all = abi.get_option("composite_variant") != 0
         self.overlap_optimizer = bool(overlap_optimizer)
@@ -199,9 +200,13 @@ class NGPTrainer:
         self._color_forward(self.cin, self.c, M, inference, limit)
         _ck(abi.lib.ngp_nerf_rgb_forward(self.c.data_ptr(), self.rgbs.data_ptr(), M, s, self._opts(limit)))
 
-    def _nets_forward_fused(self, enc, dirs, h, sigmas, rgbs, M, limit=None):
-        """enc, dirs -> h, sigmas, rgbs: two launches (network_ff.py:55-73)"""
+    def _nets_forward_fused(self, enc, dirs, h, sigmas, rgbs, M, limit=None, keep_h=True):
+        """enc, dirs -> (h,) sigmas, rgbs (network_ff.py:55-73): one launch for both nets; keep_h=False (inference) leaves h on the SM"""
         s, o = abi.stream(), self._opts(limit)
+        if self.merged_forward:
+            _ck(abi.lib.ngp_nerf_nets_forward(enc.data_ptr(), dirs.data_ptr(), self.sigma_w.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 2, 3,
+                                              self.density_scale, h.data_ptr() if keep_h else None, sigmas.data_ptr(), rgbs.data_ptr(), s, o))
+            return
         _ck(abi.lib.ngp_nerf_sigma_forward(enc.data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 2, self.density_scale, h.data_ptr(),
                                            sigmas.data_ptr(), s, o))
         _ck(abi.lib.ngp_nerf_color_forward(dirs.data_ptr(), h.data_ptr(), self.color_w.data_ptr(), abi.DTYPE_F32, M, 3, rgbs.data_ptr(), s, o))
@@ -638,7 +643,7 @@ class NGPTrainer:
         lim, rows_dev = self._opts(rs["rows_dev"]), rs["rows_dev"]
         self._encode(rs["xyzs"], rs["x01"], rs["enc"], M, rows_dev)
         if self.fused_nets:
-            self._nets_forward_fused(rs["enc"], rs["dirs"], rs["h"], rs["sigmas"], rs["rgbs"], M, rows_dev)
+            self._nets_forward_fused(rs["enc"], rs["dirs"], rs["h"], rs["sigmas"], rs["rgbs"], M, rows_dev, keep_h=False)
         else:
             _ck(lib.ngp_ffmlp_inference(rs["enc"].data_ptr(), self.sigma_w.data_ptr(), abi.DTYPE_F32, M, 32, 16, 64, 2, 0, 6, None, rs["h"].data_ptr(), s, lim))
             _ck(lib.ngp_nerf_mid_forward(rs["h"].data_ptr(), rs["dirs"].data_ptr(), self.density_scale, rs["sigmas"].data_ptr(), rs["cin"].data_ptr(), M, s, lim))

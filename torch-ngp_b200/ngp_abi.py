@@ -80,6 +80,7 @@ SIGNATURES = {
     "ngp_nerf_mid_backward": (_int, [_vp, _vp, _vp, _f32, _vp, _u32, _vp, _op]),
     "ngp_nerf_sigma_forward": (_int, [_vp, _vp, _int, _u32, _u32, _f32, _vp, _vp, _vp, _op]),
     "ngp_nerf_color_forward": (_int, [_vp, _vp, _vp, _int, _u32, _u32, _vp, _vp, _op]),
+    "ngp_nerf_nets_forward": (_int, [_vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _f32, _vp, _vp, _vp, _vp, _op]),
     "ngp_nerf_color_backward": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _f32, _vp, _vp, _int, _vp, _sz, _vp, _op]),
     "ngp_step_begin": (_int, [_vp, _f32, _f32, _vp]),
     "ngp_step_end": (_int, [_vp, _vp]),
