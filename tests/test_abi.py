@@ -120,3 +120,19 @@ def test_grid_encoder_state_dict_layout():
     assert sd["offsets"].shape == (17,) and sd["offsets"].dtype == torch.int32
     assert enc.output_dim == 32 and int(enc.n_params) == 12239728
     assert sd["embeddings"].abs().max() <= 1e-4
+
+
+def test_nerf_network_registers_the_reference_state_dict_keys():
+    """nerf.NeRFNetwork is the module of network_ff.py:11-74 on top of NeRFRenderer's buffers (renderer.py:83-100): the keys a
+    reference checkpoint's `model` dict holds, so load_state_dict(strict=True) accepts it; and density_scale is NOT applied by the
+    module (the renderer applies it, renderer.py:295) -- checked on the attribute level here, numerically in the GPU tests."""
+    import inspect
+    import nerf
+    net = nerf.NeRFNetwork(bound=2, log2_hashmap_size=10, density_scale=3)
+    keys = set(net.state_dict().keys())
+    assert keys == {"aabb_train", "aabb_infer", "density_grid", "density_bitfield", "step_counter", "encoder.embeddings", "encoder.offsets",
+                    "sigma_net.weights", "color_net.weights"}, keys
+    assert net.cascade == 2 and tuple(net.density_grid.shape) == (2, 128 ** 3) and net.density_bitfield.numel() == 2 * 128 ** 3 // 8
+    assert net.step_counter.dtype.is_floating_point is False and tuple(net.step_counter.shape) == (16, 2)
+    src = inspect.getsource(nerf.NeRFNetwork.forward) + inspect.getsource(nerf.NeRFNetwork.density)
+    assert "density_scale" not in src
