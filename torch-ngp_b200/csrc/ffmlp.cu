@@ -368,6 +368,152 @@ __global__ void __launch_bounds__(1024) k_nerf_nets_fwd(const __half *__restrict
     if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
 }
 
+// ---- the same two nets with every activation in TENSOR MEMORY ------------------------------------------------------------
+// The drain of a layer (tcgen05.ld -> ReLU -> fp16) writes the next layer's A operand back into TMEM with tcgen05.st (row = lane,
+// two K elements per 32-bit column) and the products read it there (tcgen05.mma, A from TMEM): no activation tile in shared
+// memory at all, the inputs go global -> registers -> TMEM.  Why: measured (benchmarks/umma_issue_bench.cu, tmem_ld_bench.cu) a
+// shared-memory-operand MMA holds the SM's 128 B/clk shared-memory port for (4 KB + N x 32 B) / 128 cycles and a 128 x 64 drain
+// for 16 KB / 128 = 128 cycles; with A in TMEM only the weights (N x 32 B per instruction) cross that port.  Shared memory
+// holds the two weight images (44 KB); a pipeline owns 96 TMEM columns (64 accumulator + 32 operand), five pipelines per SM.
+// Same values and the same accumulation order as k_nerf_nets_fwd: results are bit-identical.
+__device__ __forceinline__ void issue_fwd_ts(uint32_t d_tmem, uint32_t a_tmem, const uint8_t *w_img, uint32_t N, uint32_t K) {
+    const uint32_t idesc = make_idesc(128, N, false, false);
+    const uint32_t b_base = smem_u32(w_img);
+    for (uint32_t k16 = 0; k16 < K / 16; ++k16) {
+        const uint64_t bd = make_desc(b_base + (k16 >> 2) * N * kTileRowBytes + (k16 & 3u) * 32u, 0, kAtomBytes);
+        mma_f16_ts(d_tmem, a_tmem + k16 * 8u, bd, idesc, k16 > 0 ? 1u : 0u);
+    }
+}
+
+template <bool TRAIN>
+__global__ void __launch_bounds__(640) k_nerf_nets_fwd_tm(const __half *__restrict__ enc, const float *__restrict__ w_sig, const float *__restrict__ w_col,
+                                                          __half *__restrict__ h_out, const mlp_t ms, const mlp_t mc, uint32_t ntiles, uint32_t tmem_cols,
+                                                          const int *__restrict__ limit, const nerf_io_t io) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_bar[8];
+    const uint32_t Beff = eff_batch(ms.B, limit);
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
+    uint8_t *sw1 = smem, *sw2 = smem + ms.wbytes;
+    stage_weights<float>(sw1, w_sig, ms, tid, blockDim.x);
+    stage_weights<float>(sw2, w_col, mc, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid < np) mbar_init(&s_bar[tid], 1);
+    if (tid == 0) mbar_init_fence();
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t acc = s_tmem + pipe * 96u, aop = acc + 64u;          // accumulator / operand columns of this pipeline
+    const uint32_t lane_off = ((warp & 3u) * 32u) << 16;                 // this warp's 32 TMEM lanes
+    const uint32_t trow = acc + lane_off, arow = aop + lane_off;
+    uint64_t *bar = &s_bar[pipe];
+    const uint32_t bid = 1u + pipe;
+    uint32_t phase = 0;
+    // hand the operand this thread has just stored to the tensor core: every row of the tile must be in TMEM first
+    auto publish_and_issue = [&](const uint8_t *w_img, uint32_t N, uint32_t K) {
+        tmem_st_wait();
+        fence_before_sync();
+        pipe_sync(bid);
+        if (row == 0) {
+            fence_after_sync();
+            issue_fwd_ts(acc, aop, w_img, N, K);
+            mma_commit(bar);
+        }
+    };
+    auto hidden_round = [&](const uint8_t *w_next, uint32_t n_next) {
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+#pragma unroll
+        for (uint32_t c0 = 0; c0 < 64; c0 += 32) {
+            float v[32];
+            tmem_ld32(trow + c0, v);
+            uint32_t p[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) p[j] = relu2(v[2 * j], v[2 * j + 1]);
+            tmem_st16(arow + (c0 >> 1), p);
+        }
+        publish_and_issue(w_next, n_next, 64u);
+    };
+    for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
+        const uint32_t grow = tile * kTileRows + row;
+        const bool ok = grow < Beff;
+        {
+            uint4 x[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) x[q] = ok ? __ldg(reinterpret_cast<const uint4 *>(enc + (size_t)grow * 32u) + q) : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t p[16] = {x[0].x, x[0].y, x[0].z, x[0].w, x[1].x, x[1].y, x[1].z, x[1].w, x[2].x, x[2].y, x[2].z, x[2].w, x[3].x, x[3].y, x[3].z, x[3].w};
+            tmem_st16(arow, p);
+        }
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (ok) { dx = io.dirs[3 * (size_t)grow]; dy = io.dirs[3 * (size_t)grow + 1]; dz = io.dirs[3 * (size_t)grow + 2]; }
+        publish_and_issue(sw1 + ms.soff[0], 64u, 32u);
+        hidden_round(sw1 + ms.soff[1], 64u);
+        hidden_round(sw1 + ms.soff[2], 16u);
+        // ---- h, sigma, and the colour net's input row ----
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        {
+            float v[16];
+            tmem_ld16(trow, v);
+            uint4 lo, hi;
+            lo.x = pack2(v[0], v[1]); lo.y = pack2(v[2], v[3]); lo.z = pack2(v[4], v[5]); lo.w = pack2(v[6], v[7]);
+            hi.x = pack2(v[8], v[9]); hi.y = pack2(v[10], v[11]); hi.z = pack2(v[12], v[13]); hi.w = pack2(v[14], v[15]);
+            if (ok) {
+                if (TRAIN) {
+                    reinterpret_cast<uint4 *>(h_out + (size_t)grow * 16u)[0] = lo;
+                    reinterpret_cast<uint4 *>(h_out + (size_t)grow * 16u)[1] = hi;
+                }
+                io.sigmas[grow] = io.density_scale * __expf(half_round(v[0]));
+            } else {
+                lo = hi = make_uint4(0u, 0u, 0u, 0u);
+            }
+            const float x = dx, y = dy, z = dz;
+            const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+            uint32_t p[16];
+            p[0] = pack2(0.28209479177387814f, -0.48860251190291987f * y);
+            p[1] = pack2(0.48860251190291987f * z, -0.48860251190291987f * x);
+            p[2] = pack2(1.0925484305920792f * xy, -1.0925484305920792f * yz);
+            p[3] = pack2(0.94617469575755997f * z2 - 0.31539156525251999f, -1.0925484305920792f * xz);
+            p[4] = pack2(0.54627421529603959f * x2 - 0.54627421529603959f * y2, 0.59004358992664352f * y * (-3.0f * x2 + y2));
+            p[5] = pack2(2.8906114426405538f * xy * z, 0.45704579946446572f * y * (1.0f - 5.0f * z2));
+            p[6] = pack2(0.3731763325901154f * z * (5.0f * z2 - 3.0f), 0.45704579946446572f * x * (1.0f - 5.0f * z2));
+            p[7] = pack2(1.4453057213202769f * z * (x2 - y2), 0.59004358992664352f * x * (-x2 + 3.0f * y2));
+            if (!ok) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) p[j] = 0u;
+            }
+            // geo_feat = h[1..15] shifted down by one half, then a zero pad
+            p[8] = __byte_perm(lo.x, lo.y, 0x5432); p[9] = __byte_perm(lo.y, lo.z, 0x5432); p[10] = __byte_perm(lo.z, lo.w, 0x5432); p[11] = __byte_perm(lo.w, hi.x, 0x5432);
+            p[12] = __byte_perm(hi.x, hi.y, 0x5432); p[13] = __byte_perm(hi.y, hi.z, 0x5432); p[14] = __byte_perm(hi.z, hi.w, 0x5432); p[15] = hi.w >> 16;
+            tmem_st16(arow, p);
+        }
+        publish_and_issue(sw2 + mc.soff[0], 64u, 32u);
+        for (uint32_t l = 0; l < mc.nl; ++l) hidden_round(sw2 + mc.soff[l + 1], mc.rows[l + 1]);
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        {
+            float v[16];
+            tmem_ld16(trow, v);
+            if (ok) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) io.rgbs[3 * (size_t)grow + c] = half_round(1.0f / (1.0f + __expf(-half_round(v[c]))));
+            }
+        }
+        // the next tile's first tcgen05.st / product touch columns whose readers (this drain, the last product) are done:
+        // the drain above is complete for this thread, and the pipe_sync inside publish_and_issue orders the other rows' drains
+        // before the elected thread issues
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
+}
+
 // ==========================================================================================================
 // backward (recomputes the forward per tile; dW accumulated in TMEM across the CTA's tiles)
 // ==========================================================================================================
@@ -1253,6 +1399,20 @@ int ngp_nerf_nets_forward(const void *enc, const float *dirs, const void *weight
     nerf_io_t io{};
     io.dirs = dirs; io.sigmas = sigmas; io.rgbs = rgbs; io.density_scale = density_scale;
     cudaStream_t st = (cudaStream_t)stream;
+    if (get_option("nerf_nets_tmem", 1)) {  // activations in tensor memory (default); 0: activation tiles in shared memory
+        uint32_t npt = 5;  // 96 TMEM columns per pipeline
+        if (npt > per_cta_need) npt = per_cta_need;
+        const size_t smem_t = ms.wbytes + mc.wbytes;
+        uint32_t grid_t = div_round_up(ntiles, npt);
+        if (grid_t > (uint32_t)sm_count()) grid_t = (uint32_t)sm_count();
+        int rc_t = h ? set_smem(k_nerf_nets_fwd_tm<true>, smem_t) : set_smem(k_nerf_nets_fwd_tm<false>, smem_t);
+        if (rc_t != NGP_OK) return rc_t;
+        NGP_PROF("k_nerf_nets_fwd_tm", st);
+        if (h) k_nerf_nets_fwd_tm<true><<<grid_t, 128 * npt, smem_t, st>>>((const __half *)enc, (const float *)weights_sigma, (const float *)weights_color, (__half *)h, ms, mc, ntiles, 512u, batch_limit(), io);
+        else k_nerf_nets_fwd_tm<false><<<grid_t, 128 * npt, smem_t, st>>>((const __half *)enc, (const float *)weights_sigma, (const float *)weights_color, nullptr, ms, mc, ntiles, 512u, batch_limit(), io);
+        NGP_CHECK_LAUNCH();
+        return NGP_OK;
+    }
     int rc = h ? set_smem(k_nerf_nets_fwd<true>, smem) : set_smem(k_nerf_nets_fwd<false>, smem);
     if (rc != NGP_OK) return rc;
     NGP_PROF("k_nerf_nets_fwd", st);
