@@ -41,6 +41,7 @@ static std::map<std::string, int> &options() {
         {"march_variant", -1},         // training marcher: -1 auto / 1 warp per ray (ballot replay of the skip rule), 0 thread per ray
         {"march_masks", 1},            // warp marcher: record emit masks in pass 1 when the workspace has room (0: always re-march)
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
+        {"ffmlp_fwd_tmem", 1},         // FFMLP forward, hidden <= 64: activations in tensor memory (1) or in shared-memory tiles (0); same results
         {"nerf_nets_tmem", 1},         // ngp_nerf_nets_forward: activations in tensor memory, A operand read from TMEM (1) or activation tiles in shared memory (0); same results
         {"ffmlp_available", 1},
         {"ffmlp_bwd_variant", -1},     // -1 auto / 1: multi-pipeline backward (one MMA-issuer warp, up to 4 tiles in flight), 0: one tile per CTA

@@ -385,6 +385,102 @@ __device__ __forceinline__ void issue_fwd_ts(uint32_t d_tmem, uint32_t a_tmem, c
     }
 }
 
+// The plain operator (and the sigma net, IO 1) the same way, for hidden <= 64: pipeline columns = accumulator (max(hid, out)
+// rounded to 32) + operand (max(in, hid) / 2).  Inputs go global -> registers -> TMEM in 32-half pieces.
+template <typename WT, int HID, bool GACT, int IO>
+__global__ void __launch_bounds__(1024) k_ffmlp_fwd_tm(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y, const mlp_t m,
+                                                       uint32_t ntiles, uint32_t tmem_cols, uint32_t accw, uint32_t pcols,
+                                                       const int *__restrict__ limit, const nerf_io_t io) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_bar[8];
+    const uint32_t Beff = eff_batch(m.B, limit);
+    ntiles = min(ntiles, div_round_up(Beff, kTileRows));
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
+    uint8_t *sw = smem;
+    stage_weights<WT>(sw, w, m, tid, blockDim.x);
+    if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
+    if (tid < np) mbar_init(&s_bar[tid], 1);
+    if (tid == 0) mbar_init_fence();
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t acc = s_tmem + pipe * pcols, aop = acc + accw;
+    const uint32_t lane_off = ((warp & 3u) * 32u) << 16;
+    const uint32_t trow = acc + lane_off, arow = aop + lane_off;
+    uint64_t *bar = &s_bar[pipe];
+    const uint32_t bid = 1u + pipe;
+    uint32_t phase = 0;
+    auto publish_and_issue = [&](const uint8_t *w_img, uint32_t N, uint32_t K) {
+        tmem_st_wait();
+        fence_before_sync();
+        pipe_sync(bid);
+        if (row == 0) {
+            fence_after_sync();
+            issue_fwd_ts(acc, aop, w_img, N, K);
+            mma_commit(bar);
+        }
+    };
+    for (uint32_t tile = blockIdx.x * np + pipe; tile < ntiles; tile += gridDim.x * np) {
+        const uint32_t grow = tile * kTileRows + row;
+        const bool ok = grow < Beff;
+        for (uint32_t c0 = 0; c0 < m.in; c0 += 32) {  // 32 halves = 16 columns per store; in % 32 == 16 leaves a half-filled last piece
+            uint32_t p[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool in_row = ok && c0 + 8u * q < m.in;
+                const uint4 v = in_row ? __ldg(reinterpret_cast<const uint4 *>(x + (size_t)grow * m.in + c0) + q) : make_uint4(0u, 0u, 0u, 0u);
+                p[4 * q] = v.x; p[4 * q + 1] = v.y; p[4 * q + 2] = v.z; p[4 * q + 3] = v.w;
+            }
+            tmem_st16(arow + (c0 >> 1), p);
+        }
+        publish_and_issue(sw + m.soff[0], m.hid, m.in);
+        for (uint32_t l = 0; l < m.nl; ++l) {
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            fence_after_sync();
+            constexpr int CW = HID < 32 ? HID : 32;
+#pragma unroll
+            for (int c0 = 0; c0 < HID; c0 += CW) {
+                float v[CW];
+                tmem_ldN<CW>(trow + c0, v);
+                uint32_t p[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) p[j] = 0u;
+#pragma unroll
+                for (int j = 0; j < CW / 2; ++j) {
+                    if (GACT && m.act != 0u) p[j] = pack2(act_fwd(m.act, v[2 * j]), act_fwd(m.act, v[2 * j + 1]));
+                    else p[j] = relu2(v[2 * j], v[2 * j + 1]);
+                }
+                tmem_st16(arow + (c0 >> 1), p);  // HID 16: the upper eight columns written are zeros past this layer's K, never read
+            }
+            publish_and_issue(sw + m.soff[l + 1], m.rows[l + 1], m.hid);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        fence_after_sync();
+        if constexpr (IO == 0) {
+            epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, ok);
+        } else {
+            float v[16];
+            tmem_ld16(trow, v);
+            if (ok) {
+                uint4 lo, hi;
+                lo.x = pack2(v[0], v[1]); lo.y = pack2(v[2], v[3]); lo.z = pack2(v[4], v[5]); lo.w = pack2(v[6], v[7]);
+                hi.x = pack2(v[8], v[9]); hi.y = pack2(v[10], v[11]); hi.z = pack2(v[12], v[13]); hi.w = pack2(v[14], v[15]);
+                reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[0] = lo;
+                reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[1] = hi;
+                io.sigmas[grow] = io.density_scale * __expf(half_round(v[0]));
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
+}
+
 template <bool TRAIN>
 __global__ void __launch_bounds__(640) k_nerf_nets_fwd_tm(const __half *__restrict__ enc, const float *__restrict__ w_sig, const float *__restrict__ w_col,
                                                           __half *__restrict__ h_out, const mlp_t ms, const mlp_t mc, uint32_t ntiles, uint32_t tmem_cols,
@@ -1134,6 +1230,44 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     uint32_t grid = div_round_up(ntiles, np);
     if (grid > (uint32_t)sm_count()) grid = (uint32_t)sm_count();
     cudaStream_t st = (cudaStream_t)stream;
+    // ---- activations in tensor memory (hidden <= 64, plain operator and the sigma net): the default ----
+    if (hid <= 64 && io_mode != 2 && get_option("ffmlp_fwd_tmem", 1)) {
+        const uint32_t acols = ((in > hid ? in : hid) / 2u + 7u) & ~7u;
+        uint32_t opcols = (acols + 15u) & ~15u;              // tcgen05.st writes 16 columns at a time
+        if (hid == 16 && opcols < 16u) opcols = 16u;
+        const uint32_t pcols = accw + opcols;
+        uint32_t npt = 512u / pcols;
+        if (npt > 8) npt = 8;
+        if (np_opt > 0 && (uint32_t)np_opt < npt) npt = (uint32_t)np_opt;
+        if (npt > per_cta_need) npt = per_cta_need;
+        if (npt >= 1 && m.wbytes + 1024 <= kMaxSmem) {
+            const size_t smem_t = m.wbytes;
+            const uint32_t cols_t = tmem_cols_pow2(npt * pcols);
+            uint32_t grid_t = div_round_up(ntiles, npt);
+            if (grid_t > (uint32_t)sm_count()) grid_t = (uint32_t)sm_count();
+#define NGP_FWDTM_LAUNCH(WT_, HID_, G_, IO_)                                                                                 \
+    {                                                                                                                        \
+        rc = set_smem(k_ffmlp_fwd_tm<WT_, HID_, G_, IO_>, smem_t);                                                           \
+        if (rc != NGP_OK) return rc;                                                                                         \
+        NGP_PROF(IO_ == 1 ? "k_ffmlp_fwd_tm_sigma" : "k_ffmlp_fwd_tm", st);                                                  \
+        k_ffmlp_fwd_tm<WT_, HID_, G_, IO_><<<grid_t, 128 * npt, smem_t, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols_t, accw, pcols, batch_limit(), io); \
+    }
+#define NGP_FWDTM_CASE(WT_, HID_) { if (m.act) NGP_FWDTM_LAUNCH(WT_, HID_, true, 0) else NGP_FWDTM_LAUNCH(WT_, HID_, false, 0) }
+#define NGP_FWDTM_HID(WT_)                                       \
+    switch (hid) {                                               \
+        case 16: NGP_FWDTM_CASE(WT_, 16) break;                  \
+        case 32: NGP_FWDTM_CASE(WT_, 32) break;                  \
+        default: NGP_FWDTM_CASE(WT_, 64) break;                  \
+    }
+            if (io_mode == 1) NGP_FWDTM_LAUNCH(float, 64, false, 1)
+            else if (wdtype == NGP_DTYPE_F16) NGP_FWDTM_HID(__half) else NGP_FWDTM_HID(float)
+#undef NGP_FWDTM_HID
+#undef NGP_FWDTM_CASE
+#undef NGP_FWDTM_LAUNCH
+            NGP_CHECK_LAUNCH();
+            return NGP_OK;
+        }
+    }
     if (io_mode) {  // one tile layout, one width: two instantiations
         rc = io_mode == 1 ? set_smem(k_ffmlp_fwd<float, 64, false, 1>, smem) : set_smem(k_ffmlp_fwd<float, 64, false, 2>, smem);
         if (rc != NGP_OK) return rc;
