@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(128) k_bench(uint32_t N, uint32_t reps, uint32
 
 // several issuing warps at once (one elected lane each, own accumulator, own commit barrier): is the ~64-cycle figure a
 // per-thread issue cost or the tensor pipe's?
-__global__ void __launch_bounds__(128) k_multi(uint32_t N, uint32_t reps, uint32_t nk, long long *out, uint32_t niss) {
+__global__ void __launch_bounds__(128) k_multi(uint32_t N, uint32_t reps, uint32_t nk, long long *out, uint32_t niss, uint32_t m_mn = 0, uint32_t mixed = 0) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar[4];
@@ -84,12 +84,14 @@ __global__ void __launch_bounds__(128) k_multi(uint32_t N, uint32_t reps, uint32
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = s_tmem, warp = threadIdx.x >> 5;
-    const uint32_t idesc = make_idesc(128, N, false, false);
+    // m_mn: both operands MN-major (the weight-gradient products G^T H); mixed: odd issuers MN-major, even ones K-major
+    const bool mn = m_mn && (!mixed || (warp & 1u));
+    const uint32_t idesc = make_idesc(128, N, mn, mn);
     const uint64_t ad = make_desc(smem_u32(smem), 0, kAtomBytes), bd = make_desc(smem_u32(smem + 16384), 0, kAtomBytes);
     const long long t0 = clock64();
     if ((threadIdx.x & 31u) == 0 && warp < niss) {
         for (uint32_t r = 0; r < reps; ++r)
-            for (uint32_t k = 0; k < nk; ++k) mma_f16(tmem + warp * 128u, ad, bd, idesc, 1u);
+            for (uint32_t k = 0; k < nk; ++k) mma_f16(tmem + warp * 128u, ad + (mn ? (uint64_t)(k & 7u) * 128u : (uint64_t)(k & 3u) * 2u), bd + (mn ? (uint64_t)(k & 7u) * 128u : (uint64_t)(k & 3u) * 2u), idesc, 1u);
         mma_commit(&s_bar[warp]);
     }
     if (warp < niss) mbar_wait(&s_bar[warp], 0);
@@ -135,5 +137,13 @@ int main() {
             if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
             printf("multi-issuer N=%3u issuers=%u  complete %.1f cyc per mma (aggregate over issuers)\n", N, niss, (double)out[1] / (reps * nk * niss));
         }
+    for (uint32_t mixed : {0u, 1u})
+        for (uint32_t N : {32u, 64u})
+            for (uint32_t niss : {1u, 2u, 4u}) {
+                for (int rep = 0; rep < 2; ++rep) k_multi<<<1, 128, 64 * 1024>>>(N, reps, nk, out, niss, 1u, mixed);
+                cudaError_t e = cudaDeviceSynchronize();
+                if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
+                printf("multi-issuer %s N=%3u issuers=%u  complete %.1f cyc per mma\n", mixed ? "MN/K mixed" : "MN-major  ", N, niss, (double)out[1] / (reps * nk * niss));
+            }
     return 0;
 }

@@ -41,6 +41,7 @@ static std::map<std::string, int> &options() {
         {"march_variant", -1},         // training marcher: -1 auto / 1 warp per ray (ballot replay of the skip rule), 0 thread per ray
         {"march_masks", 1},            // warp marcher: record emit masks in pass 1 when the workspace has room (0: always re-march)
         {"composite_variant", -1},     // training compositor: -1 auto / 1 warp per ray (scans), 0 thread per ray
+        {"ffmlp_bwd_tmem", 0},         // FFMLP backward, hidden 64: K = 64 layer products read A from tensor memory: 0 off (default: measured no gain, the backward is bound by its per-round chain, not by operand traffic), 1 when it costs no tile pipeline, 2 always
         {"ffmlp_fwd_tmem", 1},         // FFMLP forward, hidden <= 64: activations in tensor memory (1) or in shared-memory tiles (0); same results
         {"nerf_nets_tmem", 1},         // ngp_nerf_nets_forward: activations in tensor memory, A operand read from TMEM (1) or activation tiles in shared memory (0); same results
         {"ffmlp_available", 1},

@@ -387,6 +387,15 @@ __device__ __forceinline__ void issue_fwd_ts(uint32_t d_tmem, uint32_t a_tmem, c
 
 // The plain operator (and the sigma net, IO 1) the same way, for hidden <= 64: pipeline columns = accumulator (max(hid, out)
 // rounded to 32) + operand (max(in, hid) / 2).  Inputs go global -> registers -> TMEM in 32-half pieces.
+// D[128 x N] = G[128 x K] (TMEM, K-major) * W, W = weight image [K rows x N cols] read as an MN-major B operand (see issue_bwd_dx)
+__device__ __forceinline__ void issue_bwd_dx_ts(uint32_t d_tmem, uint32_t a_tmem, const uint8_t *w_img, uint32_t N, uint32_t K) {
+    const uint32_t idesc = make_idesc(128, N, false, true);
+    const uint32_t b_base = smem_u32(w_img);
+    const uint32_t b_lbo = N > 64 ? K * kTileRowBytes : 0u;
+    for (uint32_t k16 = 0; k16 < K / 16; ++k16)
+        mma_f16_ts(d_tmem, a_tmem + k16 * 8u, make_desc(b_base + k16 * 2048u, b_lbo, kAtomBytes), idesc, k16 > 0 ? 1u : 0u);
+}
+
 template <typename WT, int HID, bool GACT, int IO>
 __global__ void __launch_bounds__(1024) k_ffmlp_fwd_tm(const __half *__restrict__ x, const WT *__restrict__ w, __half *__restrict__ y, const mlp_t m,
                                                        uint32_t ntiles, uint32_t tmem_cols, uint32_t accw, uint32_t pcols,
@@ -829,7 +838,16 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                                                                __half *__restrict__ grad_x, float *__restrict__ ws, void *__restrict__ grad_w,
                                                                int grad_w_f32, const mlp_t m, uint32_t ntiles, uint32_t tmem_cols, int calc_dx,
                                                                uint32_t np, uint32_t ns, uint32_t accw, int dual, const int *__restrict__ limit,
-                                                               const nerf_io_t io) {
+                                                               const nerf_io_t io, uint32_t opc) {
+    // accw: TMEM columns per pipeline = accumulator + opc operand columns.  opc = 32 (option ffmlp_bwd_tmem; hidden 64, ReLU,
+    // self-issuing pipelines; OFF by default -- A/B in one job: 218 vs 219 ps/sample for the colour net, the backward is bound by
+    // its per-round chain (drain -> barrier -> issue behind the other pipelines' and the weight-gradient products -> completion),
+    // not by operand traffic; the forward kernels, which have no weight-gradient products and need no shared-memory copy of the
+    // activations at all, gained 36 % from the same idea):
+    // the drains also store H_l / G_l into the pipeline's operand columns and the K = 64 layer products read A from there
+    // (tcgen05.mma, A in TMEM) -- 4 KB less shared-memory operand traffic per instruction on the port that bounds this kernel;
+    // the products whose A is the input tile or the upstream tile (K = in, K = out) and all weight-gradient products (both
+    // operands transposed) keep their shared-memory operands.  opc = 0: every operand in shared memory.
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ uint32_t s_last;
@@ -991,6 +1009,8 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
         if (p < np) {
             uint8_t *sx = smem + m.wbytes + p * per_pipe, *sh = sx + hoff;
             const uint32_t trow = tmem + p * accw + ((q * 32u) << 16);
+            const uint32_t arow = trow + (accw - opc);  // this row's operand columns (opc != 0)
+            const bool atm = opc != 0u;
             uint32_t phase = 0, phase2 = 0;
             // round rr of this pipeline's tile: operands are in shared memory (every writer has fenced), accumulator drained
             auto self_issue = [&](uint32_t rr) {
@@ -1001,16 +1021,23 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                 // address) stays on the uniform datapath the tcgen05 instructions read from
                 const uint32_t pu = __reduce_max_sync(0xffffffffu, p), ru = __reduce_max_sync(0xffffffffu, rr);
                 uint8_t *ux = smem + m.wbytes + pu * per_pipe, *ugo = ux + goff, *uh = ux + hoff;
-                const uint32_t acc = tmem + pu * accw;
+                const uint32_t acc = tmem + pu * accw, aop = acc + (accw - opc);
                 if (elect_one()) {
                     if (!abl_mm) {
                         if (ru == 0) issue_fwd(acc, ux, sw + m.soff[0], m.hid, m.in);
-                        else if (ru < m.nl) issue_fwd(acc, uh + (ru - 1) * abytes, sw + m.soff[ru], m.hid, m.hid);
-                        else if (ru == m.nl) issue_bwd_dx(acc, ugo, sw + m.soff[m.nl], m.hid, m.out);
+                        else if (ru < m.nl) {
+                            if (opc) issue_fwd_ts(acc, aop, sw + m.soff[ru], m.hid, m.hid);
+                            else issue_fwd(acc, uh + (ru - 1) * abytes, sw + m.soff[ru], m.hid, m.hid);
+                        } else if (ru == m.nl) issue_bwd_dx(acc, ugo, sw + m.soff[m.nl], m.hid, m.out);
                         else {
                             const uint32_t l = 2 * m.nl - ru;
-                            if (l > 0) issue_bwd_dx(acc, uh + l * abytes, sw + m.soff[l], m.hid, m.hid);
-                            else if (calc_dx) issue_bwd_dx(acc, uh, sw + m.soff[0], m.in, m.hid);
+                            if (l > 0) {
+                                if (opc) issue_bwd_dx_ts(acc, aop, sw + m.soff[l], m.hid, m.hid);
+                                else issue_bwd_dx(acc, uh + l * abytes, sw + m.soff[l], m.hid, m.hid);
+                            } else if (calc_dx) {
+                                if (opc) issue_bwd_dx_ts(acc, aop, sw + m.soff[0], m.in, m.hid);
+                                else issue_bwd_dx(acc, uh, sw + m.soff[0], m.in, m.hid);
+                            }
                         }
                     }
                     mma_commit(&s_done[pu]);
@@ -1045,7 +1072,9 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     phase ^= 1u;
                     fence_after_sync();
                     if (wp == 0) NGP_TR(2 + p, 0x400u | l);
-                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0, GACT ? m.act : 0u);
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP)
+                        epi_relu_to_tile<STEP>(trow, sh + l * abytes, row, c0, GACT ? m.act : 0u, atm && l + 1 < m.nl, arow);
+                    if (atm) tmem_st_wait();
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
@@ -1066,7 +1095,9 @@ __global__ void __launch_bounds__(64 + 128 * 6) k_ffmlp_bwd_mp(const __half *__r
                     fence_after_sync();
                     if (wp == 0) NGP_TR(2 + p, 0x600u | (uint32_t)l);
                     uint8_t *h = sh + (uint32_t)l * abytes;
-                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP) epi_mask_to_tile<STEP>(trow, h, h, row, c0, GACT ? m.act : 0u);
+                    for (uint32_t c0 = cg * cw; c0 < (cg + 1u) * cw; c0 += STEP)
+                        epi_mask_to_tile<STEP>(trow, h, h, row, c0, GACT ? m.act : 0u, atm && (l > 0 || calc_dx), arow);
+                    if (atm) tmem_st_wait();
                     fence_proxy_async();
                     fence_before_sync();
                     __syncwarp();
@@ -1390,6 +1421,18 @@ int run_backward(const char *fn, const void *grad, const void *inputs, const voi
         if (m.wbytes + 2048 < kMaxSmem) np = (uint32_t)((kMaxSmem - 2048 - m.wbytes) / per_pipe);  // 2 KB: static shared + alignment
         if (dwcols < 512) { if (np > (512 - dwcols) / accw) np = (512 - dwcols) / accw; } else np = 0;
         if (np > 4) np = 4;
+        // operand columns in tensor memory for the K = 64 layer products (see the kernel): hidden 64, ReLU, self-issuing pipelines.
+        // ffmlp_bwd_tmem: 0 off, 1 when it costs no pipeline, 2 even if the 32 extra columns per pipeline cost one
+        const int nis = get_option("ffmlp_bwd_issuers", 3);  // 1 one central issuer, 2 two (layer products / weight gradients), 3 pipelines issue their own layer products
+        const int tm_opt = get_option("ffmlp_bwd_tmem", 0);
+        uint32_t opc = 0;
+        if (hidden_dim == 64 && activation == 0 && nis >= 3 && tm_opt > 0 && dwcols < 512) {
+            const uint32_t np_t = (512 - dwcols) / (accw + 32u);
+            if (np_t >= np || (tm_opt >= 2 && np_t >= 2)) {
+                opc = 32;
+                if (np > np_t) np = np_t;
+            }
+        }
         // ns threads share a row's epilogue (latency); 64 + 128 * np * ns <= 832 threads keeps 72 registers per thread
         uint32_t ns = hidden_dim >= 64 ? 2u : 1u;
         const int ns_opt = get_option("ffmlp_bwd_split", 0);
@@ -1405,12 +1448,12 @@ int run_backward(const char *fn, const void *grad, const void *inputs, const voi
         if (np > ntiles) np = ntiles;
         if (variant != 0 && (np >= 2 || (variant == 1 && np >= 1))) {
             const size_t smem_mp = m.wbytes + np * per_pipe;
-            const int nis = get_option("ffmlp_bwd_issuers", 3);  // 1 one central issuer, 2 two (layer products / weight gradients), 3 pipelines issue their own layer products
             int dual = (nis != 1 ? 1 : 0) | (nis >= 3 ? 2 : 0);
+            const uint32_t pw = accw + opc;  // TMEM columns per pipeline
 #ifdef NGP_FFMLP_DEBUG  // developer builds only: timing ablations that produce WRONG results are not reachable from the shipped library
             dual |= get_option("ffmlp_ablate", 0) << 4;
 #endif
-            const uint32_t cols_mp = tmem_cols_pow2(np * accw + dwcols);
+            const uint32_t cols_mp = tmem_cols_pow2(np * pw + dwcols);
             uint32_t grid_mp = div_round_up(ntiles, np);
             if (grid_mp > (uint32_t)sm_count()) grid_mp = (uint32_t)sm_count();
             if (io_mode == 2) {
@@ -1418,7 +1461,7 @@ int run_backward(const char *fn, const void *grad, const void *inputs, const voi
                 if (rc != NGP_OK) return rc;
                 NGP_PROF("k_ffmlp_bwd_mp_color", st);
                 k_ffmlp_bwd_mp<float, 64, false, 2><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const float *)weights, (__half *)grad_inputs,
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, pw, dual, batch_limit(), io, opc);
                 NGP_CHECK_LAUNCH();
                 return NGP_OK;
             }
@@ -1428,9 +1471,9 @@ int run_backward(const char *fn, const void *grad, const void *inputs, const voi
         if (rc != NGP_OK) return rc;                                                                                         \
         NGP_PROF("k_ffmlp_bwd_mp", st);                                                                                      \
         if (m.act) k_ffmlp_bwd_mp<WT_, HID_, true, 0><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);   \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, pw, dual, batch_limit(), io, opc);   \
         else k_ffmlp_bwd_mp<WT_, HID_, false, 0><<<grid_mp, 64 + 128 * np * ns, smem_mp, st>>>((const __half *)grad, (const __half *)inputs, (const WT_ *)weights, (__half *)grad_inputs, \
-                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, accw, dual, batch_limit(), io);   \
+                                                        (float *)workspace, grad_weights, gf32, m, ntiles, cols_mp, calc_grad_inputs, np, ns, pw, dual, batch_limit(), io, opc);   \
     }
 #define NGP_BWDMP_HID(WT_)                                         \
     switch (hidden_dim) {                                          \

@@ -146,18 +146,24 @@ __device__ __noinline__ void epi_act_to_tile(uint32_t taddr, uint8_t *tiles, uin
         *reinterpret_cast<uint4 *>(t + (((c8 + (j >> 3)) ^ (row & 7u)) << 4)) = u;
     }
 }
+// to_tm: ALSO store the fp16 row piece into tensor memory at a_row + col0 / 2 (two K elements per 32-bit column, row = lane):
+// the A operand of the next layer product when that product reads A from TMEM (CW == 32 only: one tcgen05.st.x16)
 template <int CW>
-__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0, uint32_t act = 0u) {
+__device__ __forceinline__ void epi_relu_to_tile(uint32_t taddr, uint8_t *tiles, uint32_t row, uint32_t col0, uint32_t act = 0u,
+                                                 bool to_tm = false, uint32_t a_row = 0u) {
     if (act != 0u) { epi_act_to_tile<CW>(taddr, tiles, row, col0, act); return; }
     float v[CW];
     tmem_ldN<CW>(taddr + col0, v);
     uint8_t *t = tiles + (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
     const uint32_t c8 = (col0 & 63u) >> 3;
+    uint32_t p[CW / 2];
 #pragma unroll
-    for (int j = 0; j < CW; j += 8) {
-        uint4 u;
-        u.x = relu2(v[j], v[j + 1]); u.y = relu2(v[j + 2], v[j + 3]); u.z = relu2(v[j + 4], v[j + 5]); u.w = relu2(v[j + 6], v[j + 7]);
-        *reinterpret_cast<uint4 *>(t + (((c8 + (j >> 3)) ^ (row & 7u)) << 4)) = u;
+    for (int j = 0; j < CW / 2; ++j) p[j] = relu2(v[2 * j], v[2 * j + 1]);
+#pragma unroll
+    for (int j = 0; j < CW; j += 8)
+        *reinterpret_cast<uint4 *>(t + (((c8 + (j >> 3)) ^ (row & 7u)) << 4)) = make_uint4(p[j >> 1], p[(j >> 1) + 1], p[(j >> 1) + 2], p[(j >> 1) + 3]);
+    if constexpr (CW == 32) {
+        if (to_tm) tmem_st16(a_row + (col0 >> 1), p);
     }
 }
 
@@ -189,12 +195,13 @@ __device__ __noinline__ void epi_dact_to_tile(uint32_t taddr, const uint8_t *act
 }
 template <int CW>
 __device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *act_tiles, uint8_t *tiles, uint32_t row, uint32_t col0,
-                                                 uint32_t act = 0u) {
+                                                 uint32_t act = 0u, bool to_tm = false, uint32_t a_row = 0u) {
     if (act != 0u) { epi_dact_to_tile<CW>(taddr, act_tiles, tiles, row, col0, act); return; }
     float v[CW];
     tmem_ldN<CW>(taddr + col0, v);
     const uint32_t base = (col0 >> 6) * kActTileBytes + row * kTileRowBytes;
     const uint32_t c8 = (col0 & 63u) >> 3;
+    uint32_t p[CW / 2];
 #pragma unroll
     for (int j = 0; j < CW; j += 8) {
         const uint32_t o = base + (((c8 + (j >> 3)) ^ (row & 7u)) << 4);
@@ -203,6 +210,10 @@ __device__ __forceinline__ void epi_mask_to_tile(uint32_t taddr, const uint8_t *
         u.x = mask2(v[j], v[j + 1], a.x); u.y = mask2(v[j + 2], v[j + 3], a.y);
         u.z = mask2(v[j + 4], v[j + 5], a.z); u.w = mask2(v[j + 6], v[j + 7], a.w);
         *reinterpret_cast<uint4 *>(tiles + o) = u;
+        p[j >> 1] = u.x; p[(j >> 1) + 1] = u.y; p[(j >> 1) + 2] = u.z; p[(j >> 1) + 3] = u.w;
+    }
+    if constexpr (CW == 32) {
+        if (to_tm) tmem_st16(a_row + (col0 >> 1), p);
     }
 }
 // acc[row, 0..n) -> fp16 -> global row (n % 16 == 0; 32 B per 16 columns, consecutive rows are contiguous)
