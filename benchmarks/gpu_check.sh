@@ -1,8 +1,8 @@
 set -x
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_ffmlp.py tests/test_gpu_nerf_step.py tests/test_gpu_sdf_step.py -m gpu -x -q > gpurun_out/pytest_a.log 2>&1; tail -12 gpurun_out/pytest_a.log
-for o in 1 0 2 1 0 2; do timeout 200 python bench.py --only --no-cpu-baseline --opt ffmlp_bwd_tmem=$o 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); ks=d['kernels']; s=d['config']['samples_per_step_per_gpu']
-a=ks['k_ffmlp_bwd_mp_color']['us_per_launch']; b=ks['k_ffmlp_bwd_mp']['us_per_launch']
-print('BTM=$o ms/step', round(d['ms_per_step'],4), 'bwd colour us', round(a,1), 'sigma us', round(b,1), 'samples', s, 'ps/sample', round(a*1e6/s,1), round(b*1e6/s,1))"; done
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_a.log 2>&1; tail -4 gpurun_out/pytest_a.log
+( time timeout 400 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err ) 2> gpurun_out/bench_default.time; tail -3 gpurun_out/bench_default.err; cat gpurun_out/bench_default.time
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+python benchmarks/step_prof.py 1 > gpurun_out/plain2.log 2>&1 && ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"k_grid_fwd_v3|k_grid_bwd_v3|k_ffmlp|k_nerf_nets|k_march_train_count|k_adam" -o gpurun_out/r2_step_full_v2 python benchmarks/step_prof.py 1 > gpurun_out/ncu2.log 2>&1
+tail -3 gpurun_out/ncu2.log
+python benchmarks/step_prof.py 2 > gpurun_out/plain.log 2>&1 && ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r2_step_launches.csv python benchmarks/step_prof.py 2 > gpurun_out/ncu1.log 2>&1

@@ -52,7 +52,9 @@ def launches(csv_path, bench_json, out_md, title="training step"):
            "Shares must agree, not absolutes.", "",
            "| kernel | launches/step | ncu us/step | ncu share | live us/step | live share |", "|---|---|---|---|---|---|"]
     for k in sorted(tot, key=lambda k: -tot[k]):
-        lv = live.get(k)
+        # bench.py names the fused instances of a kernel by role (k_ffmlp_bwd_mp_color ...); the profiler sees one template name
+        match = [v for kk, v in live.items() if kk == k or kk.startswith(k + "_")]
+        lv = sum(match) if match else None
         out.append(f"| `{k}` | {cnt[k] / nsteps:.2f} | {tot[k] / nsteps:.1f} | {100 * tot[k] / total:.1f} % | "
                    + (f"{lv:.1f} | {100 * lv / live_total:.1f} % |" if lv is not None else " | |"))
     out.append(f"| total | | {total / nsteps:.1f} | | {live_total:.1f} | |")
