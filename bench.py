@@ -709,7 +709,9 @@ class SDFWorkload:
         import torch
         from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
         self.torch, self.dev = torch, dev
-        self.tr = SDFTrainer(batch=self.B, device=dev, world_size=world, use_graph=not self.args.no_graph)
+        self.tr = SDFTrainer(batch=self.B, device=dev, world_size=world, use_graph=not self.args.no_graph,
+                             grad_chunks=getattr(self.args, "sdf_chunks", 0) or None,
+                             **({} if getattr(self.args, "sdf_bin_bits", -1) < 0 else {"bin_bits": self.args.sdf_bin_bits}))
         self.batches = [sample_sdf_batch(self.B, dev, seed=100 * rank + i) for i in range(4)]
         self.batches_host = [(p.cpu().pin_memory(), y.cpu().pin_memory()) for p, y in self.batches]
         self.i = 0
@@ -725,6 +727,8 @@ class SDFWorkload:
              "l2": getattr(self, "l2_note", ""), "points_per_gpu": self.B}
         if hasattr(self, "tr"):
             c["last_loss"] = self.tr.loss()
+            c["table_gradient_level_ranges"] = self.tr._level_ranges()
+            c["batch_binned_by_morton_bits"] = self.tr.bin_bits
         return c
 
     def step_device(self):
@@ -945,6 +949,8 @@ def main():
     ap.add_argument("--adam-blocks", type=int, default=5, help="nerf_train: k_adam blocks per SM while it runs beside the marcher")
     ap.add_argument("--no-overlap", action="store_true", help="nerf_train: optimizer(n) strictly before march(n+1) (default: side by side on two streams)")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=INT", help="ngp_set_option before setup (kernel A/B tests; development only)")
+    ap.add_argument("--sdf-chunks", type=int, default=0, help="sdf: level ranges of the pipelined table-gradient all-reduce (0 = trainer default: 4 when N > 1)")
+    ap.add_argument("--sdf-bin-bits", type=int, default=-1, help="sdf: Morton binning of the batch, 0 = off, 5..7 (-1 = trainer default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--only", action="store_true", help="the named workload alone: no `workloads` block with the other BASELINE configs (N=1) "
                                                         "and no single-GPU leg at the global batch (N>1)")

@@ -75,12 +75,18 @@ NGP_API long long ngp_launch_count(void);
  *                 load them (D = 3, C = 2 fast kernels only: NGP_EUNSUPPORTED otherwise).  <= 0: inputs in [0, 1].
  *   flags       : NGP_OPT_* below.
  *   grid_cap_blocks_per_sm : > 0 caps the grid of ngp_adam_step at that many blocks per SM (grid-stride), so that the
- *                 HBM-bound optimizer can share the SMs with another stream's kernels; 0 = one block per 1024 items. */
+ *                 HBM-bound optimizer can share the SMs with another stream's kernels; 0 = one block per 1024 items.
+ *   level_begin, level_end : ngp_grid_encode_backward only.  level_end > 0: accumulate the table gradient of levels
+ *                 [level_begin, level_end) alone (multiples of 4, D = 3, C = 2 fast kernels: NGP_EUNSUPPORTED otherwise;
+ *                 grad_inputs must be NULL).  A caller that all-reduces the table gradient across GPUs issues the
+ *                 backward as a few level ranges, finest first, and starts the collective of each range while the next
+ *                 one is still being accumulated (nerf/sdf_trainer.py).  Both 0 = all levels in one call. */
 typedef struct ngp_call_opts {
     const int32_t *batch_limit;
     float input_bound;
     uint32_t flags;
     int32_t grid_cap_blocks_per_sm;
+    uint32_t level_begin, level_end;
 } ngp_call_opts;
 /* dy_dx of ngp_grid_encode_forward with linear interpolation: the reference initialises `float pos_deriv[D] = {1.0f}`
  * (gridencoder.cu:143), i.e. only d = 0 gets a non-zero input derivative.  DEFAULT = the reference's values, bit for
@@ -269,6 +275,15 @@ NGP_API int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, c
 /* SDF regression loss (sdf/utils.py:217-225, loss.py:7-15 mape_loss, mean over B): h [B,16] f16 (column 0 = prediction),
  * target [B] f32 -> *loss_out += loss, grad_h [B,16] f16 (scaled by *loss_scale) */
 NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts);
+/* Spatial binning of an unordered batch (no counterpart in the reference, whose SDF batches stay in the random order of
+ * sdf/provider.py:60-90): points [B,3] f32 in [-bound, bound]^3 and an optional per-point payload values [B] f32 are
+ * COPIED to points_out / values_out in the order of the Morton code of a (2^bits)^3 cube grid, bits in {5, 6, 7}; points
+ * of one cube stay in arbitrary order.  The permutation is not returned: the caller's loss is a mean over the batch.
+ * workspace: ngp_bin_points_workspace(B, bits) bytes, 16-byte aligned, ZERO-FILLED before the first call (every call
+ * leaves its histogram zeroed again).  Four launches (histogram with slot ranks, block sums, exclusive scan, scatter). */
+NGP_API int ngp_bin_points(const float *points, const float *values, uint32_t B, float bound, uint32_t bits, void *workspace, size_t workspace_bytes,
+                   float *points_out, float *values_out, void *stream);
+NGP_API size_t ngp_bin_points_workspace(uint32_t B, uint32_t bits);
 NGP_API int ngp_step_begin(float *state, float beta1, float beta2, void *stream);
 NGP_API int ngp_step_end(float *state, void *stream);
 /* sets state.found_inf when any gradient is inf/nan: g16 = n16 halves (n16 % 8 == 0), g32 = n32 floats (n32 % 4 == 0) */

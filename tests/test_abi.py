@@ -48,7 +48,7 @@ def test_library_is_sm100a_only_and_has_no_cpu_fallback():
     out = subprocess.run(["cuobjdump", "-lelf", ngp_abi.LIB_PATH], capture_output=True, text=True).stdout
     archs = set(re.findall(r"sm_\d+a?", out))
     assert archs == {"sm_100a"}, archs
-    assert ngp_abi.lib.ngp_abi_version() == 1
+    assert ngp_abi.lib.ngp_abi_version() == 2
     assert ngp_abi.get_option("hashgrid_fwd_variant") == -1
     with pytest.raises(ngp_abi.NgpError, match="unknown option"):
         ngp_abi.set_option("no_such_option", 1)

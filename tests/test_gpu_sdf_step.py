@@ -64,3 +64,109 @@ def test_sdf_training_converges(graph):
     p, y = sample_sdf_batch(1 << 14, "cuda", seed=99)
     err = (tr.predict(p) - y).abs().mean()
     assert float(err) < 0.05, float(err)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.half])
+@pytest.mark.parametrize("coarse", [0, 1])
+def test_grid_backward_by_level_ranges_equals_one_call(dtype, coarse):
+    """ngp_call_opts.level_begin / level_end: the table gradient accumulated range by range (finest first, as the SDF
+    pipeline issues it) is the gradient of one call over every level, up to the order of the atomic additions."""
+    import ngp_abi as abi
+    import gridencoder
+    B, L = 50000, 16
+    enc = gridencoder.GridEncoder(num_levels=L, log2_hashmap_size=15, desired_resolution=2048)
+    off_h = np.ascontiguousarray(enc.offsets.numpy().astype(np.int32))
+    off = enc.offsets.cuda()
+    T = int(off_h[-1])
+    g = torch.Generator().manual_seed(3)
+    x = (torch.rand(B, 3, generator=g) * 2 - 1).cuda()
+    grad = torch.randn(B, 2 * L, generator=g).cuda().to(dtype).contiguous()
+    code = abi.DTYPE_F32 if dtype == torch.float32 else abi.DTYPE_F16
+    flags = abi.OPT_GRID_BWD_SMEM_COARSE if coarse else 0
+    S = float(np.log2(enc.per_level_scale))
+
+    def run(out, **kw):
+        return abi.lib.ngp_grid_encode_backward(grad.data_ptr(), x.data_ptr(), None, off.data_ptr(), off_h.ctypes.data, out.data_ptr(), B, 3, 2, L, S,
+                                                enc.base_resolution, None, None, 0, 0, 0, code, abi.LAYOUT_BLC, abi.stream(),
+                                                abi.call_opts(input_bound=1.0, flags=flags, **kw))
+    whole, parts = torch.zeros(T, 2, dtype=dtype, device="cuda"), torch.zeros(T, 2, dtype=dtype, device="cuda")
+    assert run(whole) == 0
+    for lb, le in [(12, 16), (4, 12), (0, 4)]:
+        before = parts.clone()
+        assert run(parts, level_begin=lb, level_end=le) == 0, abi.lib.ngp_last_error().decode()
+        touched = (parts != before).any(dim=1).nonzero().flatten()
+        assert touched.numel() > 0 and int(touched.min()) >= off_h[lb] and int(touched.max()) < off_h[le]  # nothing outside the range
+    torch.cuda.synchronize()
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert _rel(parts.float(), whole.float()) < tol
+    assert run(parts, level_begin=2, level_end=8) != 0 and "multiples of 4" in abi.lib.ngp_last_error().decode()
+    assert run(parts, level_begin=8, level_end=20) != 0
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_sdf_pipelined_table_gradient_equals_the_one_call_step(graph):
+    """SDFTrainer(grad_chunks=4) -- the multi-GPU schedule (grid backward by level range, collective of a finished range on
+    a side stream), here with one rank so the collectives are no-ops -- trains like grad_chunks=1."""
+    from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
+    B = 1 << 15
+    a = SDFTrainer(batch=B, use_graph=graph, log2_hashmap_size=15, lr=1e-3, grad_chunks=1)
+    b = SDFTrainer(batch=B, use_graph=graph, log2_hashmap_size=15, lr=1e-3, grad_chunks=4)
+    assert b._level_ranges() == [(12, 16), (8, 12), (4, 8), (0, 4)] and a._level_ranges() == [(0, 16)]
+    batches = [sample_sdf_batch(B, "cuda", seed=s) for s in range(3)]
+    la, lb = [], []
+    for i in range(12):
+        a.train_step(*batches[i % 3]); b.train_step(*batches[i % 3])
+        la.append(a.loss()); lb.append(b.loss())
+        if i == 0:
+            assert _rel(b.g16.float(), a.g16.float()) < 2e-2 and _rel(b.g32, a.g32) < 1e-3
+    assert np.isfinite(lb).all() and np.allclose(la, lb, rtol=2e-2), (la, lb)
+    # (the table itself is not compared: Adam turns the sign of a rounding-level gradient into a full +-lr update)
+    assert _rel(b.mlp_w, a.mlp_w) < 2e-2
+    assert lb[-1] < lb[0]
+
+
+@pytest.mark.parametrize("bits", [5, 6, 7])
+def test_bin_points_is_a_morton_ordered_permutation(bits):
+    """ngp_bin_points: the output is the input batch, payload attached, in non-decreasing Morton order of the (2^bits)^3 grid;
+    the histogram part of the workspace is zero again afterwards (the next call starts from it)."""
+    import ngp_abi as abi
+    from nerf.sdf_trainer import sample_sdf_batch
+    B = 100003
+    p, y = sample_sdf_batch(B, "cuda", seed=5)
+    p[17] = float("nan")  # lands in cell 0 of its axis, does not crash
+    p[:, 0][100:200] = 1.0  # the upper face belongs to the last cell
+    ws = torch.zeros(int(abi.lib.ngp_bin_points_workspace(B, bits)), dtype=torch.uint8, device="cuda")
+    po, yo = torch.empty_like(p), torch.empty_like(y)
+    for _ in range(2):  # the second call relies on the zeroed histogram
+        po.fill_(-7.0)
+        assert abi.lib.ngp_bin_points(p.data_ptr(), y.data_ptr(), B, 1.0, bits, ws.data_ptr(), ws.numel(), po.data_ptr(), yo.data_ptr(), abi.stream()) == 0
+        torch.cuda.synchronize()
+        assert int(ws[:4 << (3 * bits)].view(torch.int32).abs().sum()) == 0
+        R = 1 << bits
+        c = ((po.nan_to_num(nan=-1.0) + 1) * 0.5).clamp(0, 1).mul(R).long().clamp(max=R - 1)
+        key = torch.zeros(B, dtype=torch.long, device="cuda")
+        for bit in range(bits):
+            for d in range(3):
+                key |= ((c[:, d] >> bit) & 1) << (3 * bit + d)
+        assert bool((key[1:] >= key[:-1]).all())
+
+        def rows(a, b):  # sortable view of (point, payload) rows; NaN -> a fixed number
+            m = torch.cat([a.nan_to_num(nan=123.0), b[:, None]], 1).cpu().numpy()
+            return m[np.lexsort(m.T[::-1])]
+        assert np.array_equal(rows(p, y), rows(po, yo))
+    assert abi.lib.ngp_bin_points(p.data_ptr(), None, B, 1.0, 4, ws.data_ptr(), ws.numel(), po.data_ptr(), None, abi.stream()) != 0
+
+
+def test_sdf_binned_step_equals_the_unordered_step():
+    """bin_bits only changes the ORDER of the batch inside the step: loss and gradients are those of the unordered step."""
+    from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
+    B = 1 << 16
+    a = SDFTrainer(batch=B, use_graph=False, log2_hashmap_size=15, bin_bits=0)
+    b = SDFTrainer(batch=B, use_graph=False, log2_hashmap_size=15, bin_bits=7)
+    p, y = sample_sdf_batch(B, "cuda", seed=2)
+    for t in (a, b):
+        t.points.copy_(p); t.sdfs.copy_(y)
+        t._forward_backward()
+    torch.cuda.synchronize()
+    assert abs(float(a.state[7]) - float(b.state[7])) < 1e-4 * max(1.0, abs(float(a.state[7])))
+    assert _rel(b.g32, a.g32) < 1e-3 and _rel(b.g16.float(), a.g16.float()) < 2e-2

@@ -99,6 +99,7 @@ const int *batch_limit() { return t_opts ? reinterpret_cast<const int *>(t_opts-
 float input_bound() { return (t_opts && t_opts->input_bound > 0.f) ? t_opts->input_bound : 0.f; }
 uint32_t call_flags() { return t_opts ? t_opts->flags : 0u; }
 int grid_cap_blocks_per_sm() { return t_opts ? t_opts->grid_cap_blocks_per_sm : 0; }
+void level_range(uint32_t &begin, uint32_t &end) { begin = t_opts ? t_opts->level_begin : 0u; end = t_opts ? t_opts->level_end : 0u; }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -117,7 +118,7 @@ int sm_count() {
 extern "C" {
 
 const char *ngp_last_error(void) { return ngp::g_err; }
-int ngp_abi_version(void) { return 1; }
+int ngp_abi_version(void) { return 2; }  // 2: ngp_call_opts grew level_begin / level_end
 
 int ngp_set_option(const char *key, int value) {
     if (!key) return NGP_EINVAL;

@@ -23,6 +23,7 @@ const int *batch_limit();        // opts->batch_limit (device int) or nullptr
 float input_bound();             // opts->input_bound if > 0, else 0: the grid kernels map [-bound, bound] -> [0, 1] themselves
 uint32_t call_flags();           // opts->flags (NGP_OPT_*)
 int grid_cap_blocks_per_sm();    // opts->grid_cap_blocks_per_sm
+void level_range(uint32_t &begin, uint32_t &end);  // opts->level_begin / level_end (0, 0 = every level)
 
 // Effective batch of a per-sample kernel: min(B, *limit * mult) when a device-side limit is set.  The launch is
 // still sized for B; blocks past the limit exit at once.  `limit` was written by an earlier kernel on the stream.

@@ -143,8 +143,14 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
     if ((variant == -1 || variant == 3) && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
         const uint32_t ng = L / 4;
-        const bool mix = get_option("hashgrid_v3_mix_bwd", 1) && (ng == 1 || ng == 2 || ng == 4 || ng == 8);
-        const dim3 gr = mix ? dim3(div_round_up(B, 256u / ng), 1, 1) : dim3(div_round_up(B, 256u), ng, 1);
+        // ngp_call_opts.level_begin / level_end: this call accumulates a range of level groups only (blockIdx.y-major launch)
+        uint32_t lb = 0, le = 0;
+        level_range(lb, le);
+        const bool ranged = le > 0;
+        if (ranged && (lb % 4 || le % 4 || lb >= le || le > L)) { set_error("grid_encode_backward: level range [%u, %u) must be multiples of 4 inside [0, %u]", lb, le, L); return NGP_EINVAL; }
+        const uint32_t ngc = ranged ? (le - lb) / 4 : ng, lg_first = ranged ? lb / 4 : 0;  // level groups of this launch
+        const bool mix = get_option("hashgrid_v3_mix_bwd", 1) && (ngc == 1 || ngc == 2 || ngc == 4 || ngc == 8);
+        const dim3 gr = mix ? dim3(div_round_up(B, 256u / ngc), 1, 1) : dim3(div_round_up(B, 256u), ngc, 1);
         const int minb = get_option("hashgrid_v3_minb_bwd", -1);
         const bool occ6 = minb < 0 ? false : minb >= 6;
         const int red4 = get_option("hashgrid_bwd_red4", 2);
@@ -152,11 +158,15 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         // thousand coarse cells and the L2 atomic unit serialises same-address reductions.  The levels that fit are
         // accumulated in shared memory instead (fp32, one flush per block).  Ray-ordered samples keep them in the warp
         // reduction (runs of equal cells collapse before they reach L2).
+        // Shared-memory atomics are no faster per operation than the L2 unit (ATOMS: 2 cycles per lane and SM, i.e. ~140 G/s
+        // over 148 SMs; an exact fixed-point variant on the native integer ATOMS.ADD with levels cut into slabs measured
+        // 204 us for levels 0-1 against 101 + 92 us here): what pays is FEWER reductions, which is what ngp_bin_points +
+        // the warp reduction give the SDF step (nerf/sdf_trainer.py bin_bits).
         uint32_t skip = 0;
-        if (call_flags() & NGP_OPT_GRID_BWD_SMEM_COARSE) {
+        if ((call_flags() & NGP_OPT_GRID_BWD_SMEM_COARSE) && lb == 0) {
             size_t smem = 0;
             const uint32_t ns = plan_smem_levels<T>(offsets_host, L, B, 2 * sizeof(float), &smem);
-            if (ns > 0) {
+            if (ns > 0 && (!ranged || ns <= le)) {
                 NGP_CHECK_CUDA(cudaFuncSetAttribute(k_grid_bwd_d3c2_smem<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLevelBudget));
 
                 const uint32_t per_sm = smem <= 100 * 1024 ? 2 : 1;
@@ -172,14 +182,16 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         NGP_PROF("k_grid_bwd_v3", st);
         const int un_opt = get_option("hashgrid_v3_unroll_bwd", -1);
         const bool unroll = un_opt > 0;  // default: one loop body (A/B in one run: -13 % per ray-ordered sample, no difference on unordered points)
-#define NGP_BWD_V3(MINB, MIX) { if (unroll) k_grid_bwd_v3<T, MINB, MIX, true><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit()); \
-                                else k_grid_bwd_v3<T, MINB, MIX, false><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit()); }
+#define NGP_BWD_V3(MINB, MIX) { if (unroll) k_grid_bwd_v3<T, MINB, MIX, true><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit(), lg_first, ngc); \
+                                else k_grid_bwd_v3<T, MINB, MIX, false><<<gr, 256, 0, st>>>(grad, inputs, offsets, g_emb, B, L, S, H, gridtype, ac, interp, layout, warp_agg, red4, skip, input_bound(), batch_limit(), lg_first, ngc); }
         if (mix) { if (occ6) NGP_BWD_V3(6, true) else NGP_BWD_V3(4, true) }
         else { if (occ6) NGP_BWD_V3(6, false) else NGP_BWD_V3(4, false) }
 #undef NGP_BWD_V3
         NGP_CHECK_LAUNCH();
         return NGP_OK;
     }
+    { uint32_t lb = 0, le = 0; level_range(lb, le);
+      if (le > 0) { set_error("grid_encode_backward: ngp_call_opts.level_end needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; } }
     if (input_bound() > 0.f) { set_error("grid_encode_backward: ngp_call_opts.input_bound needs the v3 kernels (L %% 4 == 0, 32-byte aligned buffers)"); return NGP_EUNSUPPORTED; }
     if (variant == 2 && L % 4 == 0 && ((uintptr_t)g_emb & 31) == 0 && ((uintptr_t)grad & 31) == 0) {
         const int warp_agg = get_option("hashgrid_bwd_warp_agg", 1);
@@ -283,6 +295,14 @@ int ngp_grid_encode_backward(const void *grad, const float *inputs, const void *
     if (input_bound() > 0.f && !(fast && !dy_dx && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
         set_error("grid_encode_backward: ngp_call_opts.input_bound is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
         return NGP_EUNSUPPORTED;
+    }
+    {
+        uint32_t lb = 0, le = 0;
+        level_range(lb, le);
+        if (le > 0 && !(fast && !dy_dx && (dtype == NGP_DTYPE_F32 || dtype == NGP_DTYPE_F16))) {
+            set_error("grid_encode_backward: ngp_call_opts.level_end is only supported by the D=3, C=2 fast kernels (no dy_dx, offsets_host given)");
+            return NGP_EUNSUPPORTED;
+        }
     }
     int rc;
     switch (dtype) {

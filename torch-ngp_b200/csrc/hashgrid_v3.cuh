@@ -170,15 +170,16 @@ __device__ __forceinline__ float2 gather_hashed(const T *__restrict__ tab, const
 //                samples: whole warps share a few cells) and fine-level warps (bound by the one L1-miss request per
 //                clock an SM can send to L2), so both limits are worked on at the same time instead of in turn.
 template <bool MIX>
-__device__ __forceinline__ void map_thread(uint32_t L, uint32_t &b, uint32_t &l0) {
+__device__ __forceinline__ void map_thread(uint32_t L, uint32_t &b, uint32_t &l0, uint32_t lg_first = 0, uint32_t ng_call = 0) {
     if (MIX) {
-        const uint32_t ng = L >> 2, warp = threadIdx.x >> 5;
+        // ng_call: level groups of THIS launch (a call over a level range, ngp_call_opts.level_begin / level_end); 0 = all of them
+        const uint32_t ng = ng_call ? ng_call : L >> 2, warp = threadIdx.x >> 5;
         const uint32_t grp = warp & (ng - 1u), sub = warp / ng;
         b = blockIdx.x * (256u / ng) + sub * 32u + (threadIdx.x & 31u);
-        l0 = grp * 4u;
+        l0 = (grp + lg_first) * 4u;
     } else {
         b = blockIdx.x * blockDim.x + threadIdx.x;
-        l0 = blockIdx.y * 4u;
+        l0 = (blockIdx.y + lg_first) * 4u;  // lg_first: a call over a level range (ngp_call_opts.level_begin)
     }
 }
 template <bool MIX>
@@ -278,11 +279,12 @@ template <typename T, int MINB, bool MIX, bool UNROLL>
 __global__ void __launch_bounds__(256, MINB) k_grid_bwd_v3(const T *__restrict__ grad, const float *__restrict__ inputs,
                                                      const int *__restrict__ offsets, T *__restrict__ grad_grid, uint32_t B, uint32_t L,
                                                      float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
-                                                     int layout, int warp_agg, int red4, uint32_t skip, float in_bound, const int *__restrict__ limit) {
+                                                     int layout, int warp_agg, int red4, uint32_t skip, float in_bound, const int *__restrict__ limit,
+                                                     uint32_t lg_first, uint32_t ng_call) {
     const uint32_t Bs = B;  // LBC row stride: the caller's B, not the device-side limit
     B = eff_batch(B, limit);
     uint32_t b, l0;
-    map_thread<MIX>(L, b, l0);
+    map_thread<MIX>(L, b, l0, lg_first, ng_call);
     __shared__ lv3_t s_lv[MIX ? 32 : 4];
     const lv3_t *my_lv = block_levels<MIX>(s_lv, offsets, L, l0, S, H, gridtype, align_corners);
     float x0 = 0.f, x1 = 0.f, x2 = 0.f;

@@ -345,6 +345,104 @@ __global__ void __launch_bounds__(256) k_packbits_mean(const float4 *__restrict_
     bitfield32[n] = bits;
 }
 
+// ---- spatial binning of an UNORDERED batch (the SDF step; sdf/provider.py hands out surface / uniform samples in random order) ----
+// With random order every (point, level) is its own L2 reduction in the table-gradient kernel, and on the coarse levels
+// thousands of them meet in the same entries: the L2 atomic unit serialises per address (measured on 2^20 torus samples:
+// 59-92 us per coarse level against 29 us for a fine one, half of the whole backward in levels 0-3).  The loss is a mean
+// over the batch, so the order of its points is free: one counting sort by the Morton code of a 2^bits cube grid puts the
+// points of a cell next to each other, and the segmented warp reduction of k_grid_bwd_v3 -- written for samples marched
+// along a ray -- then merges them before they reach L2; the gathers of the forward pass become L1 hits the same way.
+__device__ __forceinline__ uint32_t spread3_10(uint32_t v) {  // 10 bits -> every third bit
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_bin_hist(const float *__restrict__ points, uint32_t B, float bound, uint32_t bits, uint32_t *__restrict__ hist,
+                                                  uint32_t *__restrict__ key, uint32_t *__restrict__ rank) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const float R = (float)(1u << bits), inv = 0.5f / bound;
+    uint32_t c[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float u = fminf(fmaxf((points[3 * (size_t)b + d] + bound) * inv, 0.f), 1.f);  // NaN -> 0
+        c[d] = min((1u << bits) - 1u, (uint32_t)(u * R));
+    }
+    const uint32_t k = spread3_10(c[0]) | (spread3_10(c[1]) << 1) | (spread3_10(c[2]) << 2);
+    key[b] = k;
+    rank[b] = atomicAdd(hist + k, 1u);  // my slot inside the bin
+}
+
+// 8192 bins per block: sum them
+__global__ void __launch_bounds__(1024) k_bin_blocksum(const uint32_t *__restrict__ hist, uint32_t *__restrict__ partial) {
+    __shared__ uint32_t s_w[32];
+    const uint4 *h4 = reinterpret_cast<const uint4 *>(hist) + ((size_t)blockIdx.x * 1024 + threadIdx.x) * 2;
+    const uint4 a = h4[0], b = h4[1];
+    uint32_t v = a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;
+    v = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31u) == 0u) s_w[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = __reduce_add_sync(0xffffffffu, s_w[threadIdx.x]);
+        if (threadIdx.x == 0) partial[blockIdx.x] = v;
+    }
+}
+
+// exclusive prefix sum of the histogram -> start[]; the histogram is left zeroed for the next call
+__global__ void __launch_bounds__(1024) k_bin_scan(uint32_t *__restrict__ hist, const uint32_t *__restrict__ partial, uint32_t *__restrict__ start) {
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_base;
+    uint32_t before = 0;
+    for (uint32_t i = threadIdx.x; i < blockIdx.x; i += blockDim.x) before += partial[i];
+    before = __reduce_add_sync(0xffffffffu, before);
+    if ((threadIdx.x & 31u) == 0u) s_w[threadIdx.x >> 5] = before;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const uint32_t t = __reduce_add_sync(0xffffffffu, s_w[threadIdx.x]);
+        if (threadIdx.x == 0) s_base = t;
+    }
+    __syncthreads();
+    const uint32_t base = s_base;
+    uint4 *h4 = reinterpret_cast<uint4 *>(hist) + ((size_t)blockIdx.x * 1024 + threadIdx.x) * 2;
+    const uint4 a = h4[0], b = h4[1];
+    h4[0] = make_uint4(0u, 0u, 0u, 0u);
+    h4[1] = make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t mine = a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;
+    uint32_t inc = mine;  // inclusive scan over the warp
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, d);
+        if ((threadIdx.x & 31u) >= (uint32_t)d) inc += u;
+    }
+    __syncthreads();  // s_w is reused
+    if ((threadIdx.x & 31u) == 31u) s_w[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) wbase += s_w[w];
+    uint32_t e = base + wbase + inc - mine;
+    uint4 o0, o1;
+    o0.x = e; e += a.x; o0.y = e; e += a.y; o0.z = e; e += a.z; o0.w = e; e += a.w;
+    o1.x = e; e += b.x; o1.y = e; e += b.y; o1.z = e; e += b.z; o1.w = e;
+    uint4 *s4 = reinterpret_cast<uint4 *>(start) + ((size_t)blockIdx.x * 1024 + threadIdx.x) * 2;
+    s4[0] = o0;
+    s4[1] = o1;
+}
+
+__global__ void __launch_bounds__(256) k_bin_scatter(const float *__restrict__ points, const float *__restrict__ values, uint32_t B,
+                                                     const uint32_t *__restrict__ key, const uint32_t *__restrict__ rank,
+                                                     const uint32_t *__restrict__ start, float *__restrict__ points_out, float *__restrict__ values_out) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint32_t dst = start[key[b]] + rank[b];
+    points_out[3 * (size_t)dst] = points[3 * (size_t)b];
+    points_out[3 * (size_t)dst + 1] = points[3 * (size_t)b + 1];
+    points_out[3 * (size_t)dst + 2] = points[3 * (size_t)b + 2];
+    if (values) values_out[dst] = values[b];
+}
+
 }  // namespace
 }  // namespace ngp
 
@@ -428,6 +526,31 @@ int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *lo
     { NGP_PROF("k_sdf_loss", st); k_sdf_loss<<<NGP_GRID1(B)>>>((const uint4 *)h, target, B, loss_scale, (uint4 *)grad_h, loss_out, batch_limit()); }
     NGP_CHECK_LAUNCH();
     return NGP_OK;
+}
+
+int ngp_bin_points(const float *points, const float *values, uint32_t B, float bound, uint32_t bits, void *workspace, size_t workspace_bytes,
+                   float *points_out, float *values_out, void *stream) {
+    using namespace ngp;
+    if (B == 0) return NGP_OK;
+    NGP_CHECK_ARG(points && points_out && workspace && (values == nullptr) == (values_out == nullptr), "bin_points: null pointer argument");
+    NGP_CHECK_ARG(bits >= 5 && bits <= 7 && bound > 0.f, "bin_points: bits must be 5, 6 or 7 (got %u) and bound > 0", bits);
+    NGP_CHECK_ARG(points != points_out, "bin_points: the copy is not in place");
+    const size_t nbins = (size_t)1 << (3 * bits), nblk = nbins / 8192;
+    NGP_CHECK_ARG(workspace_bytes >= ngp_bin_points_workspace(B, bits) && ((uintptr_t)workspace & 15) == 0,
+                  "bin_points: workspace needs %zu bytes, 16-byte aligned", ngp_bin_points_workspace(B, bits));
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t *hist = (uint32_t *)workspace, *start = hist + nbins, *partial = start + nbins, *key = partial + ((nblk + 3) & ~(size_t)3), *rank = key + B;
+    { NGP_PROF("k_bin_hist", st); k_bin_hist<<<NGP_GRID1(B)>>>(points, B, bound, bits, hist, key, rank); }
+    { NGP_PROF("k_bin_blocksum", st); k_bin_blocksum<<<(uint32_t)nblk, 1024, 0, st>>>(hist, partial); }
+    { NGP_PROF("k_bin_scan", st); k_bin_scan<<<(uint32_t)nblk, 1024, 0, st>>>(hist, partial, start); }
+    { NGP_PROF("k_bin_scatter", st); k_bin_scatter<<<NGP_GRID1(B)>>>(points, values, B, key, rank, start, points_out, values_out); }
+    NGP_CHECK_LAUNCH();
+    return NGP_OK;
+}
+
+size_t ngp_bin_points_workspace(uint32_t B, uint32_t bits) {
+    const size_t nbins = (size_t)1 << (3 * bits), nblk = nbins / 8192;
+    return (2 * nbins + ((nblk + 3) & ~(size_t)3) + 2 * (size_t)B) * sizeof(uint32_t);
 }
 
 int ngp_step_begin(float *state, float beta1, float beta2, void *stream) {

@@ -25,15 +25,17 @@ COMPACT_STATIC_MAX_N = 4194304  # NGP_COMPACT_STATIC_MAX_N
 class CallOpts(ctypes.Structure):
     """ngp_call_opts (include/ngp_b200.h): per-call options, passed by pointer as the last argument of the per-sample
     entry points (None = defaults).  Nothing here is process-wide."""
-    _fields_ = [("batch_limit", _vp), ("input_bound", _f32), ("flags", _u32), ("grid_cap_blocks_per_sm", ctypes.c_int32)]
+    _fields_ = [("batch_limit", _vp), ("input_bound", _f32), ("flags", _u32), ("grid_cap_blocks_per_sm", ctypes.c_int32),
+                ("level_begin", _u32), ("level_end", _u32)]
 
 
 _op = ctypes.POINTER(CallOpts)
 
 
-def call_opts(batch_limit=None, input_bound=0.0, flags=0, grid_cap_blocks_per_sm=0):
+def call_opts(batch_limit=None, input_bound=0.0, flags=0, grid_cap_blocks_per_sm=0, level_begin=0, level_end=0):
     """-> a CallOpts to pass as `opts` (ctypes converts it to a pointer); batch_limit: int32 device tensor or None."""
-    return CallOpts(None if batch_limit is None else batch_limit.data_ptr(), float(input_bound), int(flags), int(grid_cap_blocks_per_sm))
+    return CallOpts(None if batch_limit is None else batch_limit.data_ptr(), float(input_bound), int(flags), int(grid_cap_blocks_per_sm),
+                    int(level_begin), int(level_end))
 
 # name -> (restype, argtypes): mirrors include/ngp_b200.h one to one (tests/test_abi.py checks the
 # header against this table and against the symbols the .so exports).
@@ -87,6 +89,8 @@ SIGNATURES = {
     "ngp_found_inf": (_int, [_vp, _sz, _vp, _sz, _vp, _vp]),
     "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _f32, _vp, _op]),
     "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _op]),
+    "ngp_bin_points": (_int, [_vp, _vp, _u32, _f32, _u32, _vp, _sz, _vp, _vp, _vp]),
+    "ngp_bin_points_workspace": (_sz, [_u32, _u32]),
     "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
     "ngp_density_ema": (_int, [_vp, _vp, _f32, _u32, _vp, _vp]),
     "ngp_packbits_mean": (_int, [_vp, _u32, _vp, ctypes.c_double, _f32, _vp, _vp]),
