@@ -710,7 +710,8 @@ class SDFWorkload:
         from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
         self.torch, self.dev = torch, dev
         self.tr = SDFTrainer(batch=self.B, device=dev, world_size=world, use_graph=not self.args.no_graph,
-                             grad_chunks=getattr(self.args, "sdf_chunks", 0) or None,
+                             grad_chunks=getattr(self.args, "sdf_chunks", 0) or 1,
+                             overlap_optimizer=False if self.args.no_overlap else None,
                              **({} if getattr(self.args, "sdf_bin_bits", -1) < 0 else {"bin_bits": self.args.sdf_bin_bits}))
         self.batches = [sample_sdf_batch(self.B, dev, seed=100 * rank + i) for i in range(4)]
         self.batches_host = [(p.cpu().pin_memory(), y.cpu().pin_memory()) for p, y in self.batches]
@@ -729,6 +730,7 @@ class SDFWorkload:
             c["last_loss"] = self.tr.loss()
             c["table_gradient_level_ranges"] = self.tr._level_ranges()
             c["batch_binned_by_morton_bits"] = self.tr.bin_bits
+            c["optimizer_deferred_beside_next_binning"] = self.tr.overlap_optimizer
         return c
 
     def step_device(self):
@@ -764,6 +766,22 @@ class SDFWorkload:
         n = abi.launch_count() - n0
         self.tr.use_graph = saved
         return n
+
+    def extras(self, steps, world):
+        """N > 1: CUDA-event timeline of the side stream (all-reduce + optimizer of step n) against the binning of batch n+1 on
+        the main stream -- every rank runs the steps (collective), rank 0 reports its own events."""
+        if world == 1 or not self.tr.overlap_optimizer:
+            return {}
+        self.tr.overlap_events = []
+        for _ in range(12):
+            self.step_device()
+        self.torch.cuda.synchronize()
+        ev, self.tr.overlap_events = self.tr.overlap_events[2:], None
+        f = lambda i, j: sum(e[i].elapsed_time(e[j]) for e in ev) / len(ev) * 1e3
+        return {"collective": {"allreduce_plus_optimizer_us": f(2, 3), "binning_beside_it_us": f(0, 1), "joined_us": f(0, 4),
+                               "exposed_us": f(0, 4) - f(0, 1),
+                               "note": "side stream: NCCL all-reduce of the fp16 table gradient + fp32 MLP gradients, found_inf, Adam; main stream: "
+                                       "ngp_bin_points of the next batch; exposed = joined - binning"}}
 
     def roofline(self, prof, peaks, steps):
         tr, B = self.tr, self.B

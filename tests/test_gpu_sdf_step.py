@@ -120,6 +120,7 @@ def test_sdf_pipelined_table_gradient_equals_the_one_call_step(graph):
         if i == 0:
             assert _rel(b.g16.float(), a.g16.float()) < 2e-2 and _rel(b.g32, a.g32) < 1e-3
     assert np.isfinite(lb).all() and np.allclose(la, lb, rtol=2e-2), (la, lb)
+    a.flush(); b.flush()
     # (the table itself is not compared: Adam turns the sign of a rounding-level gradient into a full +-lr update)
     assert _rel(b.mlp_w, a.mlp_w) < 2e-2
     assert lb[-1] < lb[0]
@@ -170,3 +171,23 @@ def test_sdf_binned_step_equals_the_unordered_step():
     torch.cuda.synchronize()
     assert abs(float(a.state[7]) - float(b.state[7])) < 1e-4 * max(1.0, abs(float(a.state[7])))
     assert _rel(b.g32, a.g32) < 1e-3 and _rel(b.g16.float(), a.g16.float()) < 2e-2
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_sdf_deferred_optimizer_equals_the_immediate_one(graph):
+    """overlap_optimizer: Adam of step n runs on a side stream beside the binning of batch n+1 -- same updates, same order."""
+    from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
+    B = 1 << 15
+    a = SDFTrainer(batch=B, use_graph=graph, log2_hashmap_size=15, lr=1e-3, overlap_optimizer=False)
+    b = SDFTrainer(batch=B, use_graph=graph, log2_hashmap_size=15, lr=1e-3, overlap_optimizer=True)
+    batches = [sample_sdf_batch(B, "cuda", seed=s) for s in range(3)]
+    la, lb = [], []
+    for i in range(10):
+        a.train_step(*batches[i % 3]); b.train_step(*batches[i % 3])
+        la.append(a.loss()); lb.append(b.loss())
+    assert b._pending and not a._pending
+    b.flush()
+    assert not b._pending and abs(b.loss() - lb[-1]) < 1e-6  # the value moved from the accumulator to the last-loss slot
+    assert np.isfinite(lb).all() and np.allclose(la, lb, rtol=2e-2), (la, lb)
+    assert _rel(b.mlp_w, a.mlp_w) < 2e-2
+    assert 0 < int(b.state[0:1].view(torch.int32)) == int(a.state[0:1].view(torch.int32)) <= 10  # optimizer steps taken (overflow skips included)

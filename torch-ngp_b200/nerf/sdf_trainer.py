@@ -17,7 +17,7 @@ from .trainer import _ST_LAST_LOSS, _ST_LOSS, _ST_SCALE, _ST_LR, _ST_LR0, _ST_DE
 
 class SDFTrainer:
     def __init__(self, batch=1 << 20, device="cuda", lr=1e-4, weight_decay=1e-6, loss_scale=65536.0, growth_interval=2000, world_size=1, seed=0,
-                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=None, bin_bits=7, coarse_smem=None):
+                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=1, bin_bits=7, coarse_smem=None, overlap_optimizer=None):
         self.dev = dev = torch.device(device)
         self.B, self.world, self.use_graph = int(batch), world_size, use_graph
         self.beta1, self.beta2, self.eps, self.wd = 0.9, 0.99, 1e-15, weight_decay
@@ -26,7 +26,7 @@ class SDFTrainer:
         # side stream all-reduces the range that is done while the next one is still being accumulated -- the step has no
         # marcher to hide the collective behind (nerf/trainer.py), so only the last, smallest range (the dense coarse
         # levels: 13 % of the table) stays exposed.  grad_chunks = 1: one backward call, then the two all-reduces.
-        self.grad_chunks = int(grad_chunks) if grad_chunks is not None else (4 if world_size > 1 else 1)
+        self.grad_chunks = int(grad_chunks or 1)
         enc = _gridencoder.GridEncoder(num_levels=16, log2_hashmap_size=log2_hashmap_size, desired_resolution=2048)
         self.L, self.C, self.base_resolution = enc.num_levels, enc.level_dim, enc.base_resolution
         self.S = float(np.log2(enc.per_level_scale))
@@ -69,7 +69,14 @@ class SDFTrainer:
             self.bin_ws = torch.zeros(int(abi.lib.ngp_bin_points_workspace(B, self.bin_bits)), dtype=torch.uint8, device=dev)
         else:
             self.pts, self.tgt = self.points, self.sdfs
-        self._graph = None
+        self._graph, self._graphs, self._side, self._ev = False, {}, None, None
+        self._pending, self._reduced = False, False
+        # Deferred optimizer: all-reduce + Adam of step n run on a side stream beside the binning of batch n+1.  Default: with
+        # several ranks only -- on one GPU Adam (HBM-bound) and the binning kernels slow each other down by what the overlap
+        # saves (measured: bin 75 -> 135 us, Adam 72 -> 99 us when run side by side).
+        self.overlap_optimizer = world_size > 1 if overlap_optimizer is None else bool(overlap_optimizer)
+        self.adam_blocks_per_sm = 0  # > 0: Adam's grid is capped so that it shares the SMs with the binning kernels (nerf/trainer.py)
+        self.overlap_events = None   # a list: (side start, side end, main after bin, main after join) events per step, for the timeline
         self.global_step = 0
 
     def _level_ranges(self):
@@ -79,12 +86,20 @@ class SDFTrainer:
         cuts = list(range(0, self.L, per)) + [self.L]
         return [(cuts[i], cuts[i + 1]) for i in range(len(cuts) - 1)][::-1]
 
+    def _bin(self):
+        """phase "bin": needs the batch only -- with a deferred optimizer it runs beside the previous step's all-reduce + Adam"""
+        if self.bin_bits:
+            _ck(abi.lib.ngp_bin_points(self.points.data_ptr(), self.sdfs.data_ptr(), self.B, 1.0, self.bin_bits, self.bin_ws.data_ptr(),
+                                       self.bin_ws.numel(), self.pts.data_ptr(), self.tgt.data_ptr(), abi.stream()))
+
     def _forward_backward(self, grid_backward=True):
+        self._bin()
+        self._samples(grid_backward)
+
+    def _samples(self, grid_backward=True):
+        """phase "samples": forward, loss, backward (needs the parameters of the previous optimizer step)"""
         s, lib, B = abi.stream(), abi.lib, self.B
         _ck(lib.ngp_step_begin(self.state.data_ptr(), self.beta1, self.beta2, s))
-        if self.bin_bits:
-            _ck(lib.ngp_bin_points(self.points.data_ptr(), self.sdfs.data_ptr(), B, 1.0, self.bin_bits, self.bin_ws.data_ptr(), self.bin_ws.numel(),
-                                   self.pts.data_ptr(), self.tgt.data_ptr(), s))
         # encoder(x, bound=1): (x + 1) / 2, applied by the grid kernels as they load the points (ngp_call_opts.input_bound)
         _ck(lib.ngp_grid_encode_forward(self.pts.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
                                         self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
@@ -105,99 +120,153 @@ class SDFTrainer:
                                          None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s,
                                          abi.call_opts(input_bound=1.0, flags=abi.OPT_GRID_BWD_SMEM_COARSE if self.coarse_smem else 0, level_begin=level_begin, level_end=level_end)))
 
-    def _step_pipelined(self):
-        """forward + MLP backward (one graph), then per level range: grid backward on the main stream | all-reduce of the
-        finished range on the side stream; the optimizer (one graph) waits for the last range."""
-        import torch.distributed as dist
-        main = torch.cuda.current_stream()
-        if getattr(self, "_side", None) is None:
-            self._side = torch.cuda.Stream()
-            self._ev = [torch.cuda.Event() for _ in range(1 + self.L // 4)]
-        reduce_ = self.world > 1 and dist.is_available() and dist.is_initialized()
-        if self.use_graph and getattr(self, "_g_head", None) is None:
-            self._forward_backward(grid_backward=False)  # first call eager: lazy initialisation happens outside the capture
-            self._g_head = False
-        elif self.use_graph:
-            if self._g_head is False:
-                torch.cuda.synchronize()
-                self._g_head, self._g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-                with torch.cuda.graph(self._g_head):
-                    self._forward_backward(grid_backward=False)
-                with torch.cuda.graph(self._g_opt):
-                    self._optimizer_step()
-                # the two captures only recorded the launches: this step still has to run them
-            self._g_head.replay()
+    # ---- phases of a step; graph replays once captured -------------------------------------------------------------------
+    def _run(self, what):
+        if self.use_graph and self._graph:
+            self._graphs[what].replay()
         else:
-            self._forward_backward(grid_backward=False)
+            {"bin": self._bin, "samples": self._samples, "head": lambda: self._samples(False), "opt": self._optimizer_step}[what]()
+
+    def _dist(self):
+        import torch.distributed as dist
+        return dist if (self.world > 1 and dist.is_available() and dist.is_initialized()) else None
+
+    def _backward(self):
+        """Phase "samples".  grad_chunks > 1: the grid backward is issued per level range, finest first, and the side stream
+        all-reduces a finished range while the main stream accumulates the next one; the optimizer then finds the gradients
+        reduced (self._reduced) and only has to wait for the side stream."""
+        if self.grad_chunks <= 1:
+            self._run("samples")
+            self._reduced = False
+            return
+        main, dist = torch.cuda.current_stream(), self._dist()
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        if self._ev is None:
+            self._ev = [torch.cuda.Event() for _ in range(1 + self.L // 4)]
+        self._run("head")  # forward, loss, MLP backward
         self._ev[0].record(main)
-        off = self.offsets_host
-        ranges = self._level_ranges()
+        off, ranges = self.offsets_host, self._level_ranges()
         for i, (lb, le) in enumerate(ranges):
             self._grid_backward(lb, le)
             self._ev[i + 1].record(main)
+        if dist:
+            from .parallel import gradient_group
+            group = gradient_group()
         with torch.cuda.stream(self._side):
             self._side.wait_event(self._ev[0])
-            if reduce_:
-                dist.all_reduce(self.g32.view(-1))
+            if dist:
+                dist.all_reduce(self.g32.view(-1), group=group)
             for i, (lb, le) in enumerate(ranges):
                 self._side.wait_event(self._ev[i + 1])
-                if reduce_:
-                    dist.all_reduce(self.g16[int(off[lb]):int(off[le])].view(-1))
-        main.wait_stream(self._side)
-        if self.use_graph and self._g_head not in (None, False):
-            self._g_opt.replay()
-        else:
-            self._optimizer_step()
+                if dist:
+                    dist.all_reduce(self.g16[int(off[lb]):int(off[le])].view(-1), group=group)
+        self._reduced = True
+
+    def _apply(self):
+        """all-reduce (unless the chunked backward has queued it already) + optimizer, on the current stream"""
+        if self.world > 1 and not self._reduced:
+            from .parallel import allreduce_gradients
+            allreduce_gradients(self.g16, self.g32)
+        self._run("opt")
+
+    def flush(self):
+        """Apply the deferred optimizer step, if any, on the current stream.  With several ranks this is a COLLECTIVE call
+        (the all-reduce of the pending gradients): every rank has to make it."""
+        if self._pending:
+            if self._side is not None:
+                torch.cuda.current_stream().wait_stream(self._side)
+            self._apply()
+            self._pending = False
 
     def _optimizer_step(self):
         s, lib = abi.stream(), abi.lib
         _ck(lib.ngp_found_inf(self.g16.data_ptr(), self.n16, self.g32.data_ptr(), self.n32, self.state.data_ptr(), s))
         _ck(lib.ngp_adam_step(self.params.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.g16.data_ptr(), self.g32.data_ptr(),
                               self.table16.data_ptr(), self.n16, self.n32, self.state.data_ptr(), self.beta1, self.beta2, self.eps, float(self.world),
-                              self.wd, s, None))
+                              self.wd, s, abi.call_opts(grid_cap_blocks_per_sm=self.adam_blocks_per_sm) if self.adam_blocks_per_sm else None))
         _ck(lib.ngp_step_end(self.state.data_ptr(), s))
 
-    def _step_eager(self):
-        self._forward_backward()
-        if self.world > 1:
-            from .parallel import allreduce_gradients
-            allreduce_gradients(self.g16, self.g32)
-        self._optimizer_step()
+    def _step(self):
+        main = torch.cuda.current_stream()
+        if not self.overlap_optimizer:
+            self.flush()
+            self._run("bin")
+            self._backward()
+            self._pending = True
+            self.flush()
+            return
+        # deferred optimizer: all-reduce + Adam of step n-1 on the side stream, beside the binning of batch n (which needs
+        # the batch only); forward / backward of step n wait for both
+        if self._pending:
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            self._side.wait_stream(main)  # the gradients of the previous step
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if self.overlap_events is not None else None
+            if ev:
+                ev[0].record(main)
+            self._run("bin")
+            if ev:
+                ev[1].record(main)
+            with torch.cuda.stream(self._side):
+                if ev:
+                    ev[2].record(self._side)
+                self._apply()
+                if ev:
+                    ev[3].record(self._side)
+            main.wait_stream(self._side)
+            if ev:
+                ev[4].record(main)
+                self.overlap_events.append(ev)
+            self._pending = False
+        else:
+            self._run("bin")
+        self._backward()
+        self._pending = True
+
+    def _capture(self):
+        """One eager step on a side stream (lazy kernel attributes, NCCL communicators), then the phases are captured.  The
+        all-reduce stays outside the graphs."""
+        stream = torch.cuda.Stream()
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            saved, self.use_graph = self.use_graph, False
+            self._bin()
+            self._backward()
+            self._pending = True
+            self.flush()
+            self.use_graph = saved
+        torch.cuda.current_stream().wait_stream(stream)
+        torch.cuda.synchronize()
+        phases = {"bin": self._bin, "samples": self._samples, "opt": self._optimizer_step}
+        if self.grad_chunks > 1:
+            phases["head"] = lambda: self._samples(False)
+        self._graphs = {}
+        for name, fn in phases.items():
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            self._graphs[name] = g
+        self._graph = True
 
     def train_step(self, points=None, sdfs=None):
-        """points [B,3] in [-1,1], sdfs [B] (device or pinned host tensors); None keeps the current batch buffers."""
+        """points [B,3] in [-1,1], sdfs [B] (device or pinned host tensors); None keeps the current batch buffers.
+        With overlap_optimizer (default) the optimizer step of this call is applied at the start of the next one, or by flush()."""
         if points is not None:  # host batches travel on a side stream while the previous step computes (nerf/feed.py)
             if getattr(self, "_feed", None) is None:
                 from .feed import HostFeed
                 self._feed = HostFeed(self.dev)
             self._feed.stage((self.points, self.sdfs), (points, sdfs))
-        if self.grad_chunks > 1:
-            self._step_pipelined()
-        elif self.use_graph and self._graph is None:
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                self._step_eager()
-            torch.cuda.current_stream().wait_stream(side)
-            torch.cuda.synchronize()
-            self._g_fb, self._g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self._g_fb):
-                self._forward_backward()
-            with torch.cuda.graph(self._g_opt):
-                self._optimizer_step()
-            self._graph = True
-        elif self.use_graph:
-            self._g_fb.replay()
-            if self.world > 1:
-                from .parallel import allreduce_gradients
-                allreduce_gradients(self.g16, self.g32)
-            self._g_opt.replay()
+        if self.use_graph and not self._graph:
+            self.flush()
+            self._capture()  # its eager step is this call's step
         else:
-            self._step_eager()
+            self._step()
         self.global_step += 1
 
     def loss(self):
-        return float(self.state[_ST_LAST_LOSS].item())
+        """Loss of the last step.  While its optimizer step is pending the value is still in the accumulator slot."""
+        return float(self.state[_ST_LOSS if self._pending else _ST_LAST_LOSS].item())
 
     def loss_async(self):
         """Enqueue the device -> host copy of the last step's loss into pinned memory; returns a function that waits for THAT copy
@@ -205,7 +274,8 @@ class SDFTrainer:
         ring = self.__dict__.setdefault("_loss_ring", {"i": 0, "buf": torch.zeros(8, dtype=torch.float32).pin_memory(),
                                                         "ev": [torch.cuda.Event() for _ in range(8)]})
         i = ring["i"] = (ring["i"] + 1) % 8
-        ring["buf"][i:i + 1].copy_(self.state[_ST_LAST_LOSS:_ST_LAST_LOSS + 1], non_blocking=True)
+        slot = _ST_LOSS if self._pending else _ST_LAST_LOSS
+        ring["buf"][i:i + 1].copy_(self.state[slot:slot + 1], non_blocking=True)
         ev = ring["ev"][i]
         ev.record()
 
@@ -216,6 +286,7 @@ class SDFTrainer:
 
     @torch.no_grad()
     def predict(self, points):
+        self.flush()
         n = points.shape[0]
         x01, enc, h = torch.empty(n, 3, device=self.dev), torch.empty(n, 32, dtype=torch.half, device=self.dev), torch.empty(n, 16, dtype=torch.half, device=self.dev)
         s = abi.stream()
