@@ -710,7 +710,7 @@ class SDFWorkload:
         from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
         self.torch, self.dev = torch, dev
         self.tr = SDFTrainer(batch=self.B, device=dev, world_size=world, use_graph=not self.args.no_graph,
-                             grad_chunks=getattr(self.args, "sdf_chunks", 0) or 1,
+                             grad_chunks=getattr(self.args, "sdf_chunks", 0) or None,
                              overlap_optimizer=False if self.args.no_overlap else None,
                              **({} if getattr(self.args, "sdf_bin_bits", -1) < 0 else {"bin_bits": self.args.sdf_bin_bits}))
         self.batches = [sample_sdf_batch(self.B, dev, seed=100 * rank + i) for i in range(4)]
@@ -843,7 +843,8 @@ def timed_region(wl, steps, world, flush):
         wl.step_device()
         b.record()
     barrier_sync(world)
-    return sum(a.elapsed_time(b) for a, b in ev) / steps
+    wl.last_step_ms = [a.elapsed_time(b) for a, b in ev]
+    return sum(wl.last_step_ms) / steps
 
 
 def e2e_region(wl, steps, world):
@@ -901,6 +902,10 @@ def measure(wl, args, rank, world, dev, peaks, steps, warmup, cpu_baseline=True,
         sampler.start()
     n0 = abi.launch_count()
     ms_local = timed_region(wl, steps, world, flush)
+    per_step = sorted(wl.last_step_ms)
+    step_ms = {"median": per_step[len(per_step) // 2], "min": per_step[0], "max": per_step[-1],
+               "note": "per-step device durations of the timed region on rank 0 (ms_per_step is their mean, max over ranks); a step that "
+                       "contains host work with read-backs (nerf_train: the density-grid update every 16th step) shows up as the max"}
     launches = (abi.launch_count() - n0) / steps
     if hasattr(wl, "launches_per_step") and wl.launches_per_step.__func__ is not HashGridWorkload.launches_per_step:
         launches = wl.launches_per_step()
@@ -935,7 +940,7 @@ def measure(wl, args, rank, world, dev, peaks, steps, warmup, cpu_baseline=True,
             "dtype": wl.dtype, "data": "synthetic", "config": wl.config(world),
             "e2e": {"value": units / (ms_e2e * 1e-3) * scale, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
                     "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": ms_e2e},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "gpu_launches": launches, "clocks": clocks, "step_ms": step_ms, "roofline": roof,
             "kernels": {k: {"launches_per_step": c / steps, "us_per_launch": t / c * 1e3} for k, (c, t) in sorted(prof.items())}}
     if hasattr(wl, "step_algorithmic_bytes"):
         a = wl.step_algorithmic_bytes()

@@ -11,36 +11,11 @@ stripes (row_stripes) -- stripes balance the load, since the rows that cross the
 import torch
 
 
-_GRADIENT_GROUP = {}
-
-
-def gradient_group():
-    """The process group of the gradient all-reduces: all ranks, NCCL kernels on a HIGH-PRIORITY stream.  The trainers run
-    the collective on a side stream beside kernels that fill every SM (the marcher of the next step, the grid backward of
-    the next level range); at default priority the blocks of the all-reduce kernel wait behind the thousands of queued
-    blocks of that kernel and the collective only starts in its tail.  Created once per process by the first call -- a
-    collective call itself, made by every rank at its first all-reduce.  gloo (CPU tests) and failures: the default group."""
-    import os
-    import torch.distributed as dist
-    if "g" not in _GRADIENT_GROUP:
-        g = None
-        if dist.get_backend() == "nccl" and os.environ.get("NGP_GRADIENT_GROUP_PRIORITY", "1") != "0":
-            try:
-                opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
-                g = dist.new_group(pg_options=opts)
-            except Exception:  # an older torch without the option: the default group is correct, only slower under load
-                g = None
-        _GRADIENT_GROUP["g"] = g
-    return _GRADIENT_GROUP["g"]
-
-
 def allreduce_gradients(g16, g32, group=None):
     """Sum the flat gradient buffers over the ranks, in place.  g16: fp16 table gradient, g32: fp32 MLP gradients."""
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
-    if group is None:
-        group = gradient_group()
     dist.all_reduce(g16.view(-1), group=group)
     dist.all_reduce(g32.view(-1), group=group)
 

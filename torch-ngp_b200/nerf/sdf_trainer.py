@@ -17,7 +17,7 @@ from .trainer import _ST_LAST_LOSS, _ST_LOSS, _ST_SCALE, _ST_LR, _ST_LR0, _ST_DE
 
 class SDFTrainer:
     def __init__(self, batch=1 << 20, device="cuda", lr=1e-4, weight_decay=1e-6, loss_scale=65536.0, growth_interval=2000, world_size=1, seed=0,
-                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=1, bin_bits=7, coarse_smem=None, overlap_optimizer=None):
+                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=None, bin_bits=7, coarse_smem=None, overlap_optimizer=None):
         self.dev = dev = torch.device(device)
         self.B, self.world, self.use_graph = int(batch), world_size, use_graph
         self.beta1, self.beta2, self.eps, self.wd = 0.9, 0.99, 1e-15, weight_decay
@@ -26,7 +26,7 @@ class SDFTrainer:
         # side stream all-reduces the range that is done while the next one is still being accumulated -- the step has no
         # marcher to hide the collective behind (nerf/trainer.py), so only the last, smallest range (the dense coarse
         # levels: 13 % of the table) stays exposed.  grad_chunks = 1: one backward call, then the two all-reduces.
-        self.grad_chunks = int(grad_chunks or 1)
+        self.grad_chunks = int(grad_chunks) if grad_chunks else (2 if world_size > 1 else 1)
         enc = _gridencoder.GridEncoder(num_levels=16, log2_hashmap_size=log2_hashmap_size, desired_resolution=2048)
         self.L, self.C, self.base_resolution = enc.num_levels, enc.level_dim, enc.base_resolution
         self.S = float(np.log2(enc.per_level_scale))
@@ -70,7 +70,7 @@ class SDFTrainer:
         else:
             self.pts, self.tgt = self.points, self.sdfs
         self._graph, self._graphs, self._side, self._ev = False, {}, None, None
-        self._pending, self._reduced = False, False
+        self._pending, self._reduced, self._grads_ev, self._join_ev = False, False, None, None
         # Deferred optimizer: all-reduce + Adam of step n run on a side stream beside the binning of batch n+1.  Default: with
         # several ranks only -- on one GPU Adam (HBM-bound) and the binning kernels slow each other down by what the overlap
         # saves (measured: bin 75 -> 135 us, Adam 72 -> 99 us when run side by side).
@@ -150,17 +150,14 @@ class SDFTrainer:
         for i, (lb, le) in enumerate(ranges):
             self._grid_backward(lb, le)
             self._ev[i + 1].record(main)
-        if dist:
-            from .parallel import gradient_group
-            group = gradient_group()
         with torch.cuda.stream(self._side):
             self._side.wait_event(self._ev[0])
             if dist:
-                dist.all_reduce(self.g32.view(-1), group=group)
+                dist.all_reduce(self.g32.view(-1))
             for i, (lb, le) in enumerate(ranges):
                 self._side.wait_event(self._ev[i + 1])
                 if dist:
-                    dist.all_reduce(self.g16[int(off[lb]):int(off[le])].view(-1), group=group)
+                    dist.all_reduce(self.g16[int(off[lb]):int(off[le])].view(-1))
         self._reduced = True
 
     def _apply(self):
@@ -201,7 +198,9 @@ class SDFTrainer:
         if self._pending:
             if self._side is None:
                 self._side = torch.cuda.Stream()
-            self._side.wait_stream(main)  # the gradients of the previous step
+            # the side stream waits for the gradients of the previous step -- for THAT event, not for everything queued on the
+            # main stream since: a host batch staged by this call (nerf/feed.py) is waited for by the binning, not by the collective
+            self._side.wait_event(self._grads_ev)
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if self.overlap_events is not None else None
             if ev:
                 ev[0].record(main)
@@ -215,6 +214,9 @@ class SDFTrainer:
                 if ev:
                     ev[3].record(self._side)
             main.wait_stream(self._side)
+            if self._join_ev is None:
+                self._join_ev = torch.cuda.Event()
+            self._join_ev.record(main)  # the next host batch starts its copy after the collective (nerf/feed.py `after`)
             if ev:
                 ev[4].record(main)
                 self.overlap_events.append(ev)
@@ -222,6 +224,9 @@ class SDFTrainer:
         else:
             self._run("bin")
         self._backward()
+        if self._grads_ev is None:
+            self._grads_ev = torch.cuda.Event()
+        self._grads_ev.record(main)
         self._pending = True
 
     def _capture(self):
@@ -256,7 +261,7 @@ class SDFTrainer:
             if getattr(self, "_feed", None) is None:
                 from .feed import HostFeed
                 self._feed = HostFeed(self.dev)
-            self._feed.stage((self.points, self.sdfs), (points, sdfs))
+            self._feed.stage((self.points, self.sdfs), (points, sdfs), after=self._join_ev)
         if self.use_graph and not self._graph:
             self.flush()
             self._capture()  # its eager step is this call's step
