@@ -1,7 +1,6 @@
-# scratch helper for one gpurun call (rewritten per run)
+# scratch helper for one gpurun call (rewritten per run): full validation on one GPU
 set -x
 mkdir -p gpurun_out
-for i in 1 2 3; do
-  timeout 200 python bench.py --only --no-cpu-baseline 2>/dev/null > gpurun_out/nt_$i.json; python -c "
-import json;d=json.load(open('gpurun_out/nt_$i.json'));print(d['ms_per_step'], d['step_ms']['median'], d['step_ms']['min'], d['step_ms']['max'])"
-done
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+timeout 400 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; tail -2 gpurun_out/bench_default.err; cut -c1-200 gpurun_out/bench_default.json

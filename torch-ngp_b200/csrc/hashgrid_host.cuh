@@ -153,7 +153,7 @@ int bwd_d3c2(const T *grad, const float *inputs, const int *offsets, const int *
         const dim3 gr = mix ? dim3(div_round_up(B, 256u / ngc), 1, 1) : dim3(div_round_up(B, 256u), ngc, 1);
         const int minb = get_option("hashgrid_v3_minb_bwd", -1);
         const bool occ6 = minb < 0 ? false : minb >= 6;
-        const int red4 = get_option("hashgrid_bwd_red4", 2);
+        const int red4 = (call_flags() & NGP_OPT_GRID_BWD_GROUP_RED) ? 1 : get_option("hashgrid_bwd_red4", 2);
         // Unordered points (NGP_OPT_GRID_BWD_SMEM_COARSE; the SDF step, configs[0]): every point lands in one of a few
         // thousand coarse cells and the L2 atomic unit serialises same-address reductions.  The levels that fit are
         // accumulated in shared memory instead (fp32, one flush per block).  Ray-ordered samples keep them in the warp

@@ -118,7 +118,7 @@ class SDFTrainer:
         _ck(lib.ngp_grid_encode_backward(self.g_enc.data_ptr(), self.pts.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(),
                                          self.offsets_host.ctypes.data, self.g16.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None,
                                          None, 0, 0, 0, abi.DTYPE_F16, abi.LAYOUT_BLC, s,
-                                         abi.call_opts(input_bound=1.0, flags=abi.OPT_GRID_BWD_SMEM_COARSE if self.coarse_smem else 0, level_begin=level_begin, level_end=level_end)))
+                                         abi.call_opts(input_bound=1.0, flags=(abi.OPT_GRID_BWD_SMEM_COARSE if self.coarse_smem else 0) | (abi.OPT_GRID_BWD_GROUP_RED if self.bin_bits else 0), level_begin=level_begin, level_end=level_end)))
 
     # ---- phases of a step; graph replays once captured -------------------------------------------------------------------
     def _run(self, what):

@@ -18,7 +18,7 @@ LAYOUT_LBC, LAYOUT_BLC = 0, 1
 
 _u32, _f32, _int, _sz, _vp = ctypes.c_uint32, ctypes.c_float, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p
 
-OPT_EXACT_INPUT_GRAD, OPT_GRID_BWD_SMEM_COARSE = 1, 2
+OPT_EXACT_INPUT_GRAD, OPT_GRID_BWD_SMEM_COARSE, OPT_GRID_BWD_GROUP_RED = 1, 2, 4
 COMPACT_STATIC_MAX_N = 4194304  # NGP_COMPACT_STATIC_MAX_N
 
 
