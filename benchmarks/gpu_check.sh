@@ -1,6 +1,6 @@
-# scratch helper for one gpurun call (rewritten per run): full validation on one GPU
+# scratch helper for one gpurun call (rewritten per run): SDF step at N GPUs, final defaults
 set -x
+N=${1:-2}
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-timeout 400 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; tail -2 gpurun_out/bench_default.err; cut -c1-200 gpurun_out/bench_default.json
+timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29561 bench.py --gpus $N --workload sdf --only --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/sdf_final_n$N.json 2> gpurun_out/sdf_final_n$N.err
+tail -1 gpurun_out/sdf_final_n$N.err | cut -c1-300; cut -c1-200 gpurun_out/sdf_final_n$N.json
