@@ -22,10 +22,11 @@ class SDFTrainer:
         self.B, self.world, self.use_graph = int(batch), world_size, use_graph
         self.beta1, self.beta2, self.eps, self.wd = 0.9, 0.99, 1e-15, weight_decay
         self.nl, self.hid = num_layers, hidden_dim
-        # Table-gradient pipeline (world_size > 1): the grid backward runs as `grad_chunks` level ranges, finest first, and a
-        # side stream all-reduces the range that is done while the next one is still being accumulated -- the step has no
-        # marcher to hide the collective behind (nerf/trainer.py), so only the last, smallest range (the dense coarse
-        # levels: 13 % of the table) stays exposed.  grad_chunks = 1: one backward call, then the two all-reduces.
+        # Table-gradient pipeline (default with world_size > 1: two ranges): the grid backward runs as `grad_chunks` level
+        # ranges, finest first, and a side stream all-reduces the range that is done while the next one is still being
+        # accumulated -- the step has no marcher to hide the collective behind (nerf/trainer.py).  Measured:
+        # 2 ranges 1.2% faster than 1 on 2 and on 8 GPUs, 4 ranges slower; the first range's collective overlaps the second
+        # range's backward only partly (the backward keeps every SM full).  grad_chunks = 1: one backward call, then the all-reduces.
         self.grad_chunks = int(grad_chunks) if grad_chunks else (2 if world_size > 1 else 1)
         enc = _gridencoder.GridEncoder(num_levels=16, log2_hashmap_size=log2_hashmap_size, desired_resolution=2048)
         self.L, self.C, self.base_resolution = enc.num_levels, enc.level_dim, enc.base_resolution
