@@ -1,5 +1,6 @@
-# scratch helper for one gpurun call (rewritten per run): memcheck of the binning kernels and the level-range backward
+# scratch helper for one gpurun call (rewritten per run): full validation on one GPU
 set -x
 mkdir -p gpurun_out
-timeout 400 compute-sanitizer --tool memcheck --error-exitcode 7 python -m pytest tests/test_gpu_sdf_step.py -x -q -k "bin_points or level_ranges or binned_step" > gpurun_out/sanitizer_sdf.log 2>&1
-echo "rc=$?"; tail -6 gpurun_out/sanitizer_sdf.log
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+timeout 400 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; tail -2 gpurun_out/bench_default.err; cut -c1-200 gpurun_out/bench_default.json

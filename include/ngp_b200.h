@@ -280,6 +280,11 @@ NGP_API int ngp_nerf_color_backward(const float *grad_rgbs, const float *rgbs, c
 /* SDF regression loss (sdf/utils.py:217-225, loss.py:7-15 mape_loss, mean over B): h [B,16] f16 (column 0 = prediction),
  * target [B] f32 -> *loss_out += loss, grad_h [B,16] f16 (scaled by *loss_scale) */
 NGP_API int ngp_sdf_loss(const void *h, const float *target, uint32_t B, const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts);
+/* The SDF net's forward (sdf/netowrk_ff.py:43-50: FFMLP 32 -> 64 x num_layers -> 1, padded to 16) and ngp_sdf_loss in ONE launch for the
+ * training step: the prediction never leaves the SM, the kernel writes grad_h [B,16] f16 (bit-identical to ngp_ffmlp_forward +
+ * ngp_sdf_loss) and accumulates the loss into *loss_out.  enc [B,32] f16, fp32 parameters in FFMLP's layout. */
+NGP_API int ngp_sdf_forward_loss(const void *enc, const void *weights, int weights_dtype, const float *target, uint32_t B, uint32_t num_layers,
+                         const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts);
 /* Spatial binning of an unordered batch (no counterpart in the reference, whose SDF batches stay in the random order of
  * sdf/provider.py:60-90): points [B,3] f32 in [-bound, bound]^3 and an optional per-point payload values [B] f32 are
  * COPIED to points_out / values_out in the order of the Morton code of a (2^bits)^3 cube grid, bits in {5, 6, 7}; points

@@ -191,3 +191,23 @@ def test_sdf_deferred_optimizer_equals_the_immediate_one(graph):
     assert np.isfinite(lb).all() and np.allclose(la, lb, rtol=2e-2), (la, lb)
     assert _rel(b.mlp_w, a.mlp_w) < 2e-2
     assert 0 < int(b.state[0:1].view(torch.int32)) == int(a.state[0:1].view(torch.int32)) <= 10  # optimizer steps taken (overflow skips included)
+
+
+@pytest.mark.parametrize("B", [1 << 14, 70001])
+def test_sdf_forward_and_loss_in_one_launch_equal_the_two_kernels(B):
+    """ngp_sdf_forward_loss: the gradient row it writes is bit-identical to ngp_ffmlp_forward + ngp_sdf_loss, the loss agrees up to
+    the order of its additions, and so does everything downstream."""
+    from nerf.sdf_trainer import SDFTrainer, sample_sdf_batch
+    a = SDFTrainer(batch=B, use_graph=False, log2_hashmap_size=15, fused_loss=False, bin_bits=0)
+    b = SDFTrainer(batch=B, use_graph=False, log2_hashmap_size=15, fused_loss=True, bin_bits=0)
+    assert b.fused_loss and not a.fused_loss
+    p, y = sample_sdf_batch(B, "cuda", seed=4)
+    for t in (a, b):
+        t.points.copy_(p); t.sdfs.copy_(y)
+        t.g_h.fill_(7.0)
+        t._forward_backward()
+    torch.cuda.synchronize()
+    assert torch.equal(a.g_h.view(torch.int16), b.g_h.view(torch.int16))
+    la, lb = float(a.state[7]), float(b.state[7])
+    assert abs(la - lb) < 1e-5 * max(1.0, abs(la)) and lb > 0
+    assert _rel(b.g32, a.g32) < 1e-3 and _rel(b.g16.float(), a.g16.float()) < 2e-2

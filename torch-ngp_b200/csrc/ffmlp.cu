@@ -75,6 +75,9 @@ struct nerf_io_t {
     const float *grad_rgbs;    // IO 2 backward in [M,3]
     const float *grad_sigmas;  // IO 2 backward in [M]
     float density_scale;
+    const float *target;       // IO 3 (SDF regression): [B] f32
+    const float *loss_scale;   // IO 3: device scalar or nullptr
+    float *loss_out;           // IO 3: device scalar, accumulated into
 };
 __device__ __forceinline__ float half_round(float v) { return __half2float(__float2half_rn(v)); }
 
@@ -403,10 +406,13 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd_tm(const __half *__restrict_
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_bar[8];
+    __shared__ float s_loss;   // IO 3
+    float loss_acc = 0.f;      // IO 3: this thread's rows
     const uint32_t Beff = eff_batch(m.B, limit);
     ntiles = min(ntiles, div_round_up(Beff, kTileRows));
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
     const uint32_t np = blockDim.x >> 7, pipe = tid >> 7, row = tid & 127u;
+    if (IO == 3 && tid == 0) s_loss = 0.f;
     uint8_t *sw = smem;
     stage_weights<WT>(sw, w, m, tid, blockDim.x);
     if (warp == 0) tmem_alloc(&s_tmem, tmem_cols);
@@ -472,6 +478,21 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd_tm(const __half *__restrict_
         fence_after_sync();
         if constexpr (IO == 0) {
             epi_to_global(trow, y + (size_t)grow * m.out, 0, m.out, ok);
+        } else if constexpr (IO == 3) {
+            // SDF regression (nerf_step.cu k_sdf_loss, same expressions): the prediction is the fp16 value the plain forward would
+            // have stored in column 0; what leaves the SM is the loss gradient row, not the output row
+            float v[16];
+            tmem_ld16(trow, v);
+            if (ok) {
+                const float pred = half_round(v[0]);
+                const float yt = io.target[grow];
+                const float wgt = 1.0f / (fabsf(yt) + 1e-2f), d = pred - yt;
+                loss_acc += fabsf(d) * wgt;
+                const float s = io.loss_scale ? *io.loss_scale : 1.0f;
+                const float g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+                reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[0] = make_uint4(pack2(s * g * wgt / (float)Beff, 0.f), 0u, 0u, 0u);
+                reinterpret_cast<uint4 *>(y + (size_t)grow * 16u)[1] = make_uint4(0u, 0u, 0u, 0u);
+            }
         } else {
             float v[16];
             tmem_ld16(trow, v);
@@ -485,8 +506,14 @@ __global__ void __launch_bounds__(1024) k_ffmlp_fwd_tm(const __half *__restrict_
             }
         }
     }
+    if constexpr (IO == 3) {  // one global atomic per CTA
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
+        if ((tid & 31u) == 0u && loss_acc != 0.f) atomicAdd(&s_loss, loss_acc);
+    }
     fence_before_sync();
     __syncthreads();
+    if (IO == 3 && tid == 0 && s_loss != 0.f) atomicAdd(io.loss_out, s_loss / (float)Beff);
     if (warp == 0) tmem_dealloc(s_tmem, tmem_cols);
 }
 
@@ -1280,7 +1307,7 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
     {                                                                                                                        \
         rc = set_smem(k_ffmlp_fwd_tm<WT_, HID_, G_, IO_>, smem_t);                                                           \
         if (rc != NGP_OK) return rc;                                                                                         \
-        NGP_PROF(IO_ == 1 ? "k_ffmlp_fwd_tm_sigma" : "k_ffmlp_fwd_tm", st);                                                  \
+        NGP_PROF(IO_ == 1 ? "k_ffmlp_fwd_tm_sigma" : (IO_ == 3 ? "k_ffmlp_fwd_tm_sdf_loss" : "k_ffmlp_fwd_tm"), st);                                                  \
         k_ffmlp_fwd_tm<WT_, HID_, G_, IO_><<<grid_t, 128 * npt, smem_t, st>>>((const __half *)inputs, (const WT_ *)weights, (__half *)outputs, m, ntiles, cols_t, accw, pcols, batch_limit(), io); \
     }
 #define NGP_FWDTM_CASE(WT_, HID_) { if (m.act) NGP_FWDTM_LAUNCH(WT_, HID_, true, 0) else NGP_FWDTM_LAUNCH(WT_, HID_, false, 0) }
@@ -1291,6 +1318,7 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
         default: NGP_FWDTM_CASE(WT_, 64) break;                  \
     }
             if (io_mode == 1) NGP_FWDTM_LAUNCH(float, 64, false, 1)
+            else if (io_mode == 3) NGP_FWDTM_LAUNCH(float, 64, false, 3)
             else if (wdtype == NGP_DTYPE_F16) NGP_FWDTM_HID(__half) else NGP_FWDTM_HID(float)
 #undef NGP_FWDTM_HID
 #undef NGP_FWDTM_CASE
@@ -1299,6 +1327,7 @@ int run_forward(const char *fn, const void *inputs, const void *weights, int wdt
             return NGP_OK;
         }
     }
+    if (io_mode == 3) { set_error("%s: the fused SDF loss exists for the tensor-memory forward only (option ffmlp_fwd_tmem = 1)", fn); return NGP_EUNSUPPORTED; }
     if (io_mode) {  // one tile layout, one width: two instantiations
         rc = io_mode == 1 ? set_smem(k_ffmlp_fwd<float, 64, false, 1>, smem) : set_smem(k_ffmlp_fwd<float, 64, false, 2>, smem);
         if (rc != NGP_OK) return rc;
@@ -1535,6 +1564,18 @@ int ngp_nerf_sigma_forward(const void *enc, const void *weights, int weights_dty
     io.sigmas = sigmas;
     io.density_scale = density_scale;
     return ngp::run_forward("nerf_sigma_forward", enc, weights, weights_dtype, M, 32, 16, 64, num_layers, 0, 6, nullptr, h, stream, 1, &io);
+}
+
+int ngp_sdf_forward_loss(const void *enc, const void *weights, int weights_dtype, const float *target, uint32_t B, uint32_t num_layers,
+                         const float *loss_scale, void *grad_h, float *loss_out, void *stream, const ngp_call_opts *opts) {
+    ngp::opts_scope _os(opts);
+    if (B == 0) return NGP_OK;
+    if (!(target && grad_h && loss_out)) { ngp::set_error("sdf_forward_loss: null pointer argument"); return NGP_EINVAL; }
+    ngp::nerf_io_t io{};
+    io.target = target;
+    io.loss_scale = loss_scale;
+    io.loss_out = loss_out;
+    return ngp::run_forward("sdf_forward_loss", enc, weights, weights_dtype, B, 32, 16, 64, num_layers, 0, 6, nullptr, grad_h, stream, 3, &io);
 }
 
 int ngp_nerf_color_forward(const float *dirs, const void *h, const void *weights, int weights_dtype, uint32_t M, uint32_t num_layers, float *rgbs,

@@ -17,11 +17,13 @@ from .trainer import _ST_LAST_LOSS, _ST_LOSS, _ST_SCALE, _ST_LR, _ST_LR0, _ST_DE
 
 class SDFTrainer:
     def __init__(self, batch=1 << 20, device="cuda", lr=1e-4, weight_decay=1e-6, loss_scale=65536.0, growth_interval=2000, world_size=1, seed=0,
-                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=None, bin_bits=7, coarse_smem=None, overlap_optimizer=None):
+                 use_graph=True, num_layers=3, hidden_dim=64, log2_hashmap_size=19, grad_chunks=None, bin_bits=7, coarse_smem=None, overlap_optimizer=None, fused_loss=True):
         self.dev = dev = torch.device(device)
         self.B, self.world, self.use_graph = int(batch), world_size, use_graph
         self.beta1, self.beta2, self.eps, self.wd = 0.9, 0.99, 1e-15, weight_decay
         self.nl, self.hid = num_layers, hidden_dim
+        # fused_loss: the net's forward and the loss in one launch (ngp_sdf_forward_loss; hidden 64 only): the prediction stays on the SM
+        self.fused_loss = bool(fused_loss) and hidden_dim == 64
         # Table-gradient pipeline (default with world_size > 1: two ranges): the grid backward runs as `grad_chunks` level
         # ranges, finest first, and a side stream all-reduces the range that is done while the next one is still being
         # accumulated -- the step has no marcher to hide the collective behind (nerf/trainer.py).  Measured:
@@ -105,9 +107,13 @@ class SDFTrainer:
         _ck(lib.ngp_grid_encode_forward(self.pts.data_ptr(), self.table16.data_ptr(), self.offsets.data_ptr(), self.offsets_host.ctypes.data,
                                         self.enc.data_ptr(), B, 3, self.C, self.L, self.S, self.base_resolution, None, 0, 0, 0, abi.DTYPE_F16,
                                         abi.LAYOUT_BLC, s, abi.call_opts(input_bound=1.0)))
-        _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s, None))
-        _ck(lib.ngp_sdf_loss(self.h.data_ptr(), self.tgt.data_ptr(), B, self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(),
-                             self.state[_ST_LOSS:].data_ptr(), s, None))
+        if self.fused_loss:
+            _ck(lib.ngp_sdf_forward_loss(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, self.tgt.data_ptr(), B, self.nl,
+                                         self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(), self.state[_ST_LOSS:].data_ptr(), s, None))
+        else:
+            _ck(lib.ngp_ffmlp_forward(self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, B, 32, 16, self.hid, self.nl, 0, 6, None, self.h.data_ptr(), s, None))
+            _ck(lib.ngp_sdf_loss(self.h.data_ptr(), self.tgt.data_ptr(), B, self.state[_ST_SCALE:].data_ptr(), self.g_h.data_ptr(),
+                                 self.state[_ST_LOSS:].data_ptr(), s, None))
         _ck(lib.ngp_ffmlp_backward(self.g_h.data_ptr(), self.enc.data_ptr(), self.mlp_w.data_ptr(), abi.DTYPE_F32, None, B, 32, 16, self.hid, self.nl, 0, 6, 1,
                                    None, self.g_enc.data_ptr(), self.g32.data_ptr(), abi.DTYPE_F32, self.mlp_ws.data_ptr(), self.mlp_ws.numel(), s, None))
         if grid_backward:

@@ -89,6 +89,7 @@ SIGNATURES = {
     "ngp_found_inf": (_int, [_vp, _sz, _vp, _sz, _vp, _vp]),
     "ngp_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _f32, _f32, _f32, _f32, _f32, _vp, _op]),
     "ngp_sdf_loss": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _op]),
+    "ngp_sdf_forward_loss": (_int, [_vp, _vp, _int, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _op]),
     "ngp_bin_points": (_int, [_vp, _vp, _u32, _f32, _u32, _vp, _sz, _vp, _vp, _vp]),
     "ngp_bin_points_workspace": (_sz, [_u32, _u32]),
     "ngp_cast_f16": (_int, [_vp, _vp, _sz, _vp]),
