@@ -51,6 +51,7 @@ extern "C" {
 #define NGP_LAYOUT_BLC 1
 
 NGP_API const char *ngp_last_error(void);
+/* 2 since ngp_call_opts carries level_begin / level_end (a caller built against version 1 passes a shorter struct: check this first) */
 NGP_API int ngp_abi_version(void);
 /* Development knobs used by bench/tests to A/B kernel VARIANTS that compute the same results (e.g. "hashgrid_fwd_variant",
  * "march_variant") and to switch the per-launch event profile on; unknown keys -> NGP_EINVAL.  Nothing that changes
