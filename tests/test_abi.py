@@ -136,3 +136,29 @@ def test_nerf_network_registers_the_reference_state_dict_keys():
     assert net.step_counter.dtype.is_floating_point is False and tuple(net.step_counter.shape) == (16, 2)
     src = inspect.getsource(nerf.NeRFNetwork.forward) + inspect.getsource(nerf.NeRFNetwork.density)
     assert "density_scale" not in src
+
+
+def test_call_opts_struct_matches_header(tmp_path):
+    """ngp_call_opts crosses the boundary by pointer: the ctypes mirror must have the header's fields in the header's order, and
+    the C compiler's size and offsets (a probe compiled against include/ngp_b200.h)."""
+    import ctypes
+    import ngp_abi
+    src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    body = re.search(r"typedef\s+struct\s+ngp_call_opts\s*\{(.*?)\}\s*ngp_call_opts\s*;", src, flags=re.S).group(1)
+    fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if decl:
+            fields += re.findall(r"(\w+)\s*(?:,|$)", decl)  # the last identifier of every declarator
+    assert fields == [n for n, _ in ngp_abi.CallOpts._fields_], (fields, ngp_abi.CallOpts._fields_)
+    probe = tmp_path / "probe.c"
+    probe.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "ngp_b200.h"\nint main(void) { printf("%zu", sizeof(ngp_call_opts));\n'
+                     + "".join(f'printf(" %zu", offsetof(ngp_call_opts, {f}));\n' for f in fields) + "return 0; }\n")
+    exe = tmp_path / "probe"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(probe), "-o", str(exe)])
+    nums = [int(x) for x in subprocess.check_output([str(exe)], text=True).split()]
+    assert nums[0] == ctypes.sizeof(ngp_abi.CallOpts)
+    assert nums[1:] == [getattr(ngp_abi.CallOpts, f).offset for f in fields]
+    # the option flags of the header and of the ctypes module agree
+    for name, val in re.findall(r"#define\s+NGP_(OPT_\w+)\s+(\d+)u", src):
+        assert getattr(ngp_abi, name) == int(val), name
